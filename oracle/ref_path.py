@@ -1,0 +1,354 @@
+"""CPU ORACLE -- test infrastructure, never imported by the product package.
+
+numpy / torch-CPU front end for ``oracle/librpc_oracle.so`` (see rpc_oracle.c for the parity
+status of each piece) plus restatements of the Python-level glue of the reference path:
+
+* ``voxelize_batch``      -- mmdet3d ``Det3DDataPreprocessor.voxelize`` (SURVEY 8a row a-U1; consumed
+                             at /root/reference/models/detectors/adversarial_voxelnet.py:66-71)
+* ``perturber_bounds``    -- the per-channel scale / clamp table of
+                             /root/reference/models/adversarial/voxel_perturber.py:209-256, 333-359
+* ``perturber_forward``   -- ``VoxelPerturber.forward`` (voxel_perturber.py:120-321) in torch-CPU ops,
+                             pinned against the real class by tests/golden/perturber_*.npz
+* ``extract_feat_ref``    -- flatten / mask / perturb / scatter-back / HardSimpleVFE of
+                             adversarial_voxelnet.py:81-137 and adversarial_centerpoint.py:68-102
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this module.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB: Optional[ctypes.CDLL] = None
+
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+
+
+def build(force: bool = False) -> str:
+    """Compile rpc_oracle.c with gcc (oracle/Makefile).  Building the checker is not using it."""
+    so = os.path.join(_HERE, "librpc_oracle.so")
+    src = os.path.join(_HERE, "rpc_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
+    return so
+
+
+def lib() -> ctypes.CDLL:
+    global _LIB
+    if _LIB is None:
+        L = ctypes.CDLL(build())
+        c_int, c_vp = ctypes.c_int, ctypes.c_void_p
+        L.orc_grid_size.argtypes = [_f32p, _f32p, _i32p]
+        L.orc_dynamic_voxelize.argtypes = [_f32p, c_int, c_int, _f32p, _f32p, _i32p]
+        L.orc_hard_voxelize.argtypes = [_f32p, c_int, c_int, _f32p, _f32p, c_int, c_int, c_int,
+                                        _f32p, _i32p, _i32p, c_vp, c_vp]
+        L.orc_hard_voxelize.restype = c_int
+        L.orc_vfe_mean_fwd.argtypes = [_f32p, _i32p, c_int, c_int, c_int, c_int, _f32p]
+        L.orc_vfe_mean_bwd.argtypes = [_f32p, _i32p, c_int, c_int, c_int, c_int, _f32p]
+        L.orc_valid_mask.argtypes = [_f32p, _i32p, c_int, c_int, c_int, c_int, _u8p]
+        L.orc_valid_mask.restype = c_int
+        L.orc_perturb_apply.argtypes = [_f32p, _f32p, _f32p, _f32p, c_int, c_int, _f32p, c_vp]
+        L.orc_perturb_bwd.argtypes = [_f32p, _f32p, _f32p, _f32p, c_int, c_int, _f32p]
+        L.orc_perturb_losses.argtypes = [_f32p, c_int, c_int, _f64p]
+        L.orc_dynamic_scatter_mean.argtypes = [_f32p, _i32p, c_int, c_int, _f32p, _i32p, _i32p, _i32p]
+        L.orc_dynamic_scatter_mean.restype = c_int
+        L.orc_dynamic_scatter_mean_bwd.argtypes = [_f32p, _i32p, _i32p, c_int, c_int, _f32p]
+        L.orc_step_fused.argtypes = [_f32p, _f32p, c_int, c_int, _f32p, _f32p, _f32p, _f32p, c_int,
+                                     c_int, c_int, c_int, _f32p, _f32p, _f32p, _i32p, _i32p, _i32p,
+                                     _i32p, _f32p, _f32p]
+        L.orc_step_fused.restype = c_int
+        _LIB = L
+    return _LIB
+
+
+def _f32(a) -> np.ndarray:
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float32))
+
+
+def grid_size(voxel_size, pcr) -> np.ndarray:
+    g = np.zeros(3, np.int32)
+    lib().orc_grid_size(_f32(voxel_size), _f32(pcr), g)
+    return g  # (gx, gy, gz)
+
+
+def dynamic_voxelize(points: np.ndarray, voxel_size, pcr) -> np.ndarray:
+    points = _f32(points)
+    N, C = points.shape
+    coors = np.zeros((N, 3), np.int32)
+    lib().orc_dynamic_voxelize(points, N, C, _f32(voxel_size), _f32(pcr), coors)
+    return coors
+
+
+def hard_voxelize(points: np.ndarray, voxel_size, pcr, max_points: int, max_voxels: int,
+                  table_mode: int = 1, with_maps: bool = False):
+    """-> (voxels[M,P,C], coors[M,3] zyx, num_points[M]) [+ point2voxel[N], point2slot[N]]"""
+    points = _f32(points)
+    N, C = points.shape
+    voxels = np.empty((max_voxels, max_points, C), np.float32)
+    coors = np.empty((max_voxels, 3), np.int32)
+    npts = np.empty((max_voxels,), np.int32)
+    p2v = np.empty((N,), np.int32)
+    p2s = np.empty((N,), np.int32)
+    M = lib().orc_hard_voxelize(points, N, C, _f32(voxel_size), _f32(pcr), max_points, max_voxels,
+                                table_mode, voxels, coors, npts, p2v.ctypes.data, p2s.ctypes.data)
+    if M < 0:
+        raise MemoryError("oracle hard_voxelize allocation failed")
+    out = (voxels[:M].copy(), coors[:M].copy(), npts[:M].copy())
+    return out + (p2v, p2s) if with_maps else out
+
+
+def vfe_mean_fwd(voxels: np.ndarray, num_points: np.ndarray, num_features: Optional[int] = None):
+    voxels = _f32(voxels)
+    M, P, C = voxels.shape
+    F = C if num_features is None else num_features
+    out = np.empty((M, F), np.float32)
+    lib().orc_vfe_mean_fwd(voxels, np.ascontiguousarray(num_points, np.int32), M, P, C, F, out)
+    return out
+
+
+def vfe_mean_bwd(grad_out: np.ndarray, num_points: np.ndarray, P: int, C: int):
+    grad_out = _f32(grad_out)
+    M, F = grad_out.shape
+    g = np.empty((M, P, C), np.float32)
+    lib().orc_vfe_mean_bwd(grad_out, np.ascontiguousarray(num_points, np.int32), M, P, C, F, g)
+    return g
+
+
+def valid_mask(voxels: np.ndarray, num_points: np.ndarray, mode: str = "rowsum") -> np.ndarray:
+    voxels = _f32(voxels)
+    M, P, C = voxels.shape
+    mask = np.zeros((M * P,), np.uint8)
+    lib().orc_valid_mask(voxels, np.ascontiguousarray(num_points, np.int32), M, P, C,
+                         {"rowsum": 0, "count": 1}[mode], mask)
+    return mask.astype(bool)
+
+
+def perturb_apply(x: np.ndarray, raw: np.ndarray, eb, fb) -> Tuple[np.ndarray, np.ndarray]:
+    x, raw = _f32(x), _f32(raw)
+    K, C = x.shape
+    y = np.empty_like(x)
+    p = np.empty_like(x)
+    lib().orc_perturb_apply(x, raw, _f32(eb), _f32(fb), K, C, y, p.ctypes.data)
+    return y, p
+
+
+def perturb_bwd(grad_p: np.ndarray, raw: np.ndarray, eb, fb) -> np.ndarray:
+    grad_p, raw = _f32(grad_p), _f32(raw)
+    K, C = raw.shape
+    g = np.empty_like(raw)
+    lib().orc_perturb_bwd(grad_p, raw, _f32(eb), _f32(fb), K, C, g)
+    return g
+
+
+def perturb_losses(p: np.ndarray) -> Dict[str, float]:
+    p = _f32(p)
+    out = np.zeros(4, np.float64)
+    lib().orc_perturb_losses(p, p.shape[0], p.shape[1], out)
+    return dict(l2_norm=out[0], intensity_loss=out[1], bias_loss=out[2], imbalance_loss=out[3])
+
+
+def dynamic_scatter_mean(points: np.ndarray, coors: np.ndarray):
+    """one sample: -> (feats[M,C], out_coors[M,3], map[N], count[M])"""
+    points = _f32(points)
+    N, C = points.shape
+    coors = np.ascontiguousarray(coors, np.int32)
+    feats = np.empty((max(N, 1), C), np.float32)
+    oc = np.empty((max(N, 1), 3), np.int32)
+    mp = np.empty((N,), np.int32)
+    cnt = np.empty((max(N, 1),), np.int32)
+    M = lib().orc_dynamic_scatter_mean(points, coors, N, C, feats, oc, mp, cnt)
+    if M < 0:
+        raise MemoryError
+    return feats[:M].copy(), oc[:M].copy(), mp, cnt[:M].copy()
+
+
+def dynamic_scatter_mean_bwd(grad_feats: np.ndarray, mp: np.ndarray, cnt: np.ndarray) -> np.ndarray:
+    grad_feats = _f32(grad_feats)
+    N, C = mp.shape[0], grad_feats.shape[1]
+    g = np.empty((N, C), np.float32)
+    gf = grad_feats if grad_feats.shape[0] else np.zeros((1, C), np.float32)
+    lib().orc_dynamic_scatter_mean_bwd(gf, np.ascontiguousarray(mp, np.int32),
+                                       np.ascontiguousarray(cnt if cnt.size else np.ones(1), np.int32),
+                                       N, C, g)
+    return g
+
+
+class StepBuffers:
+    """Caller-owned scratch for ``step_fused`` so that the timed region holds no numpy allocs."""
+
+    def __init__(self, N: int, C: int, P: int, V: int, F: int):
+        self.perturbed = np.empty((N, C), np.float32)
+        self.voxels = np.empty((V, P, C), np.float32)
+        self.coors = np.empty((V, 3), np.int32)
+        self.num_points = np.empty((V,), np.int32)
+        self.p2v = np.empty((N,), np.int32)
+        self.p2s = np.empty((N,), np.int32)
+        self.feats = np.empty((V, F), np.float32)
+        self.grad_raw = np.empty((N, C), np.float32)
+
+
+def step_fused(points, raw, eb, fb, voxel_size, pcr, P, V, F, grad_feats, table_mode=0,
+               buf: Optional[StepBuffers] = None):
+    """north-star order for ONE sweep (perturb -> hard voxelize -> VFE mean -> backward).
+    Returns (M, buf).  ``grad_feats`` is [V,F] (rows >= M ignored)."""
+    points, raw = _f32(points), _f32(raw)
+    N, C = points.shape
+    buf = buf or StepBuffers(N, C, P, V, F)
+    M = lib().orc_step_fused(points, raw, N, C, _f32(eb), _f32(fb), _f32(voxel_size), _f32(pcr), P, V,
+                             F, table_mode, _f32(grad_feats), buf.perturbed, buf.voxels, buf.coors,
+                             buf.num_points, buf.p2v, buf.p2s, buf.feats, buf.grad_raw)
+    if M < 0:
+        raise MemoryError
+    return M, buf
+
+
+# ------------------------------------------------------------------------------------------------
+# Python-level glue of the reference path
+# ------------------------------------------------------------------------------------------------
+def voxelize_batch(points_list: Sequence[np.ndarray], voxel_size, pcr, max_points: int,
+                   max_voxels: int, voxel_type: str = "hard", table_mode: int = 1) -> Dict[str, np.ndarray]:
+    """mmdet3d Det3DDataPreprocessor.voxelize restated (SURVEY 8a a-U1): per-sample voxel_layer,
+    batch index padded in front of coors, concatenation, voxel_centers."""
+    vs, lo = _f32(voxel_size), _f32(pcr)[:3]
+    if voxel_type == "hard":
+        vox, coo, num, cen = [], [], [], []
+        for i, pts in enumerate(points_list):
+            v, c, n = hard_voxelize(pts, voxel_size, pcr, max_points, max_voxels, table_mode)
+            cen.append((c[:, [2, 1, 0]].astype(np.float32) + np.float32(0.5)) * vs + lo)
+            coo.append(np.concatenate([np.full((c.shape[0], 1), i, np.int32), c], axis=1))
+            vox.append(v)
+            num.append(n)
+        return dict(voxels=np.concatenate(vox), coors=np.concatenate(coo),
+                    num_points=np.concatenate(num), voxel_centers=np.concatenate(cen).astype(np.float32))
+    if voxel_type == "dynamic":
+        coo = []
+        for i, pts in enumerate(points_list):
+            c = dynamic_voxelize(pts, voxel_size, pcr)
+            coo.append(np.concatenate([np.full((c.shape[0], 1), i, np.int32), c], axis=1))
+        return dict(voxels=np.concatenate([_f32(p) for p in points_list]), coors=np.concatenate(coo))
+    raise ValueError(voxel_type)
+
+
+def perturber_bounds(C: int, training: bool, sensor_error_bound: float = 0.2):
+    """(error_bounds eb[C], final_bounds fb[C]) exactly as voxel_perturber.py:209-256 / 333-359
+    builds them, in fp32 torch arithmetic order."""
+    import torch
+
+    seb = sensor_error_bound
+    eb = torch.ones(C) * seb
+    if C == 4:
+        if not training:
+            eb *= 2.5 * ((2.0 + 1.5 + 1.2) / 3.0)
+            eb[:3] *= 2.0
+            eb[3] = 1.5
+        else:
+            eb *= 0.8
+            eb[:3] *= 1.3
+            eb[3] = 0.2
+    elif C > 4:
+        eb[4:] = 0.0
+    fb = torch.ones(C) * seb
+    if C == 4:
+        if not training:
+            fb = fb * 5.0
+            fb[:3] *= 5.0
+            fb[3] = 2.0
+        else:
+            fb = fb * 0.9
+            fb[:3] *= 1.2
+            fb[3] = 0.1
+    elif C > 4:
+        fb[4:] = 0.0
+    else:
+        raise UnboundLocalError("final_bounds (reference crashes for C < 4, voxel_perturber.py:357)")
+    return eb.numpy().copy(), fb.numpy().copy()
+
+
+def perturber_forward(model, attention, x, training: bool, sensor_error_bound: float = 0.2):
+    """VoxelPerturber.forward restated with torch-CPU ops (voxel_perturber.py:150-321).
+    ``model`` / ``attention`` are torch modules holding the weights (train/eval mode already set).
+    Returns (perturbed, loss_dict, perturbations)."""
+    import torch
+
+    C = x.shape[1]
+    if torch.isnan(x).any():
+        return x, torch.tensor(0.0), None
+    scale = torch.std(x, dim=0, keepdim=True) + 1e-6
+    if torch.isnan(scale).any() or torch.isinf(scale).any():
+        scale = torch.ones_like(scale)
+    xn = torch.clamp(x / scale, -10.0, 10.0)
+    raw = model(xn)
+    if torch.isnan(raw).any():
+        return x, torch.tensor(0.0), None
+    if attention is not None:
+        raw = raw * attention(xn)
+    eb, fb = perturber_bounds(C, training, sensor_error_bound)
+    eb, fb = torch.from_numpy(eb), torch.from_numpy(fb)
+    p = raw * eb.view(1, -1)
+    if torch.isnan(p).any():
+        return x, torch.tensor(0.0), None
+    p = torch.clamp(p, -fb.view(1, -1), fb.view(1, -1))
+    if torch.isnan(p).any():
+        p = torch.nan_to_num(p, nan=0.0)
+    l2 = torch.norm(p, p=2, dim=1).mean()
+    y = x + p
+    inten = p[:, 3].abs().mean() if C >= 4 else torch.tensor(0.0)
+    bias = p.mean(dim=0).abs().mean()
+    imb = p.std(dim=0).std()
+    return y, dict(l2_norm=l2, intensity_loss=inten, bias_loss=bias, imbalance_loss=imb), p
+
+
+def extract_feat_ref(voxels, num_points, adversary: Optional[Callable], num_features: Optional[int] = None,
+                     mask_mode: str = "rowsum"):
+    """adversarial_voxelnet.py:81-137 on torch-CPU tensors: view(-1,C) -> valid mask -> adversary on
+    the valid rows -> gradient-connected copy + masked scatter-back -> HardSimpleVFE mean.
+    Returns (voxel_features[M,F], loss_dict or None, perturbed_voxels[M,P,C], valid_mask)."""
+    import torch
+
+    M, P, C = voxels.shape
+    v2 = voxels.view(-1, C)
+    if mask_mode == "rowsum":
+        mask = v2.sum(dim=1) != 0
+    else:
+        mask = (torch.arange(P).view(1, P) < num_points.view(-1, 1)).reshape(-1)
+    loss_dict = None
+    pert = voxels
+    if adversary is not None and int(mask.sum()) > 0:
+        y, loss_dict = adversary(v2[mask])
+        out = v2 + torch.zeros_like(v2)
+        out[mask] = y
+        pert = out.view(M, P, C)
+    F = C if num_features is None else num_features
+    feats = (pert[:, :, :F].sum(dim=1) / num_points.type_as(pert).view(-1, 1)).contiguous()
+    return feats, loss_dict, pert, mask
+
+
+def build_mlp(C: int, hidden: Sequence[int], state: Optional[Dict[str, np.ndarray]] = None):
+    """The perturber's two networks with the layer list of voxel_perturber.py:82-112 (BN eps 1e-3,
+    momentum 0.1 as set at :461-462); ``state`` = {'model.0.weight': ..., 'attention.0.weight': ...}."""
+    import torch
+    from torch import nn
+
+    h = list(hidden)
+    dims = [C, h[0], h[1], h[2], h[1], h[0]]
+    layers: List[nn.Module] = []
+    for a, b in zip(dims[:-1], dims[1:]):
+        layers += [nn.Linear(a, b), nn.BatchNorm1d(b, eps=1e-3, momentum=0.1), nn.ReLU(inplace=True)]
+    layers += [nn.Linear(h[0], C), nn.Tanh()]
+    model = nn.Sequential(*layers)
+    attention = nn.Sequential(nn.Linear(C, max(C // 2, 1)), nn.ReLU(inplace=True),
+                              nn.Linear(max(C // 2, 1), 1), nn.Sigmoid())
+    if state is not None:
+        model.load_state_dict({k[len("model."):]: torch.from_numpy(np.asarray(v))
+                               for k, v in state.items() if k.startswith("model.")})
+        attention.load_state_dict({k[len("attention."):]: torch.from_numpy(np.asarray(v))
+                                   for k, v in state.items() if k.startswith("attention.")})
+    return model, attention
