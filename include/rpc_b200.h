@@ -1,0 +1,139 @@
+/*
+ * rpc_b200.h -- C-ABI of the B200 (sm_100a) hot path of temex12/RobustPointClouds:
+ *   perturb (scale, clamp, add)  ->  hard / dynamic voxelization  ->  HardSimpleVFE mean
+ *   -> backward to the per-point raw perturbation.
+ *
+ * Drop-in boundary.  Every entry point takes plain pointers and sizes, a CUDA stream
+ * as `void*` (a `cudaStream_t`), returns an `int` status (0 = OK, <0 = error, see rpc_strerror),
+ * never throws, never allocates, never synchronises the host, and launches a fixed topology of
+ * kernels, so a sequence of calls is CUDA-graph capturable.  Pointers marked [dev] are device
+ * memory owned by the caller for the duration of the stream-ordered call; pointers marked [host]
+ * are read on the host before the call returns (their values are baked into kernel parameters).
+ *
+ * What each entry point replaces on the reference side:
+ *   rpc_voxelize_hard      mmcv `_ext.hard_voxelize_forward` as driven by mmdet3d
+ *                          `Det3DDataPreprocessor.voxelize` (whole batch in one call, batch index
+ *                          already in coors[:,0]); consumed at
+ *                          /root/reference/models/detectors/adversarial_voxelnet.py:66-71 and
+ *                          /root/reference/models/detectors/adversarial_centerpoint.py:62,191
+ *   rpc_voxelize_dynamic   mmcv `_ext.dynamic_voxelize_forward` (same call sites, dynamic mode)
+ *   rpc_vfe_mean_fwd/bwd   mmdet3d `HardSimpleVFE.forward` and its autograd, called at
+ *                          adversarial_voxelnet.py:135-137, adversarial_centerpoint.py:100-102
+ *   rpc_valid_rows         the padding mask + boolean gather of adversarial_voxelnet.py:86-90
+ *   rpc_perturb_rows_fwd/bwd   VoxelPerturber's scale/clamp/add tail
+ *                          (/root/reference/models/adversarial/voxel_perturber.py:256,357-365,285)
+ *                          fused with the masked scatter-back (adversarial_voxelnet.py:113-117) and
+ *                          the VFE mean: the reference-order composition
+ *   rpc_step_fwd/bwd       the north-star order: perturb -> hard voxelize -> VFE mean, and the
+ *                          gradient back to the raw per-point perturbation
+ *   rpc_dynamic_scatter_mean_fwd/bwd   mmcv DynamicScatter(mean) for the dynamic configuration
+ */
+#ifndef RPC_B200_H_
+#define RPC_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RPC_ABI_VERSION 1
+#define RPC_MAX_BATCH 32      /* sweeps per call */
+#define RPC_MAX_CHANNELS 8    /* features per point, 3..8 */
+
+enum {
+    RPC_OK = 0,
+    RPC_ERR_NULL = -1,        /* a required pointer is NULL */
+    RPC_ERR_CONFIG = -2,      /* C, P, V, voxel size or range invalid */
+    RPC_ERR_BATCH = -3,       /* B outside 1..RPC_MAX_BATCH or a negative point count */
+    RPC_ERR_WORKSPACE = -4,   /* workspace smaller than rpc_workspace_bytes() */
+    RPC_ERR_CUDA = -5,        /* a CUDA launch failed (cudaGetLastError) */
+    RPC_ERR_TOO_LARGE = -6,   /* point count or grid does not fit 31-bit indices */
+    RPC_ERR_ALIGN = -7        /* a pointer is not 16-byte aligned */
+};
+
+/* mirrors mmcv Voxelization(voxel_size, point_cloud_range, max_num_points, max_voxels) */
+typedef struct rpc_voxel_cfg {
+    float voxel_size[3];      /* (vx, vy, vz) */
+    float pcr[6];             /* (x_lo, y_lo, z_lo, x_hi, y_hi, z_hi) */
+    int32_t max_points;       /* P, >= 1 (hard) */
+    int32_t max_voxels;       /* V per sweep, >= 1 (hard) */
+    int32_t C;                /* features per point, 3..RPC_MAX_CHANNELS */
+    int32_t F;                /* HardSimpleVFE num_features, 1..C */
+} rpc_voxel_cfg;
+
+/* per-channel bounds of VoxelPerturber (voxel_perturber.py:209-256 eb, :333-359 fb) */
+typedef struct rpc_perturb_cfg {
+    float eb[RPC_MAX_CHANNELS];   /* p = raw * eb[c] */
+    float fb[RPC_MAX_CHANNELS];   /* p = clamp(p, -fb[c], +fb[c]); NaN -> 0 */
+} rpc_perturb_cfg;
+
+int rpc_abi_version(void);
+const char *rpc_strerror(int status);
+
+/* grid[d] = round((hi-lo)/vs) in fp32, d = x,y,z (mmcv voxelization.cpp) */
+int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3]);
+
+/* bytes of scratch rpc_voxelize_hard / rpc_step_fwd / rpc_dynamic_scatter_mean_fwd need for a batch of B sweeps
+ * with n_per_sample[b] points each; 0 on invalid arguments */
+size_t rpc_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
+/* rows of the voxel outputs the caller must provide: sum_b min(n_b, V) */
+int64_t rpc_voxel_capacity(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
+
+/*
+ * Hard voxelization of a batch of B sweeps (points of all sweeps concatenated, sweep b holding
+ * n_per_sample[b] rows), optionally of the PERTURBED points x + clamp(raw*eb, +-fb) when `raw`
+ * and `pc` are non-NULL.  Outputs are compact and concatenated in sweep order, exactly what
+ * Det3DDataPreprocessor.voxelize returns after torch.cat:
+ *   voxels      [cap, P, C] f32   rows >= voxel_total are not written; unused slots are 0.0
+ *   coors       [cap, 4]   i32    (batch, z, y, x)
+ *   num_points  [cap]      i32
+ *   voxel_num   [B + 1]    i32    per-sweep voxel counts, then their total      (device memory)
+ *   point2voxel [ntotal]   i32    global voxel row of each input point, -1 if not stored (may be NULL)
+ *   point2slot  [ntotal]   i32    slot 0..P-1 of each input point, -1 if not stored (may be NULL)
+ *   feats       [cap, F]   f32    HardSimpleVFE mean of the rows (may be NULL)
+ * Voxel order = order of the first point of each cell; slot order = point order; first P kept;
+ * cells first seen after V voxels exist are refused (mmcv hard_voxelize_forward_cpu semantics).
+ */
+int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points /*[dev]*/,
+                      const int32_t *n_per_sample /*[host]*/, int B,
+                      const float *raw /*[dev] or NULL*/, const rpc_perturb_cfg *pc /*[host] or NULL*/,
+                      float *voxels, int32_t *coors, int32_t *num_points, int32_t *voxel_num,
+                      int32_t *point2voxel, int32_t *point2slot, float *feats,
+                      void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * Backward of the fused step (rpc_voxelize_hard with raw + feats), per input point i:
+ *   g[c] = grad_feats[v, c] / num_points[v] when point i was stored in voxel v = point2voxel[i]
+ *          (c < F), else 0
+ *   grad_raw[i, c] = (-fb[c] <= raw[i,c]*eb[c] <= fb[c]) ? g[c] * eb[c] : 0
+ * which is autograd through HardSimpleVFE (adversarial_voxelnet.py:135-137), the masked
+ * scatter-back (:113-114) and VoxelPerturber's clamp and scale (voxel_perturber.py:256,357-359).
+ * With raw == NULL the gradient w.r.t. the point features (g) is written instead.
+ */
+int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats /*[cap,F]*/,
+                 const int32_t *num_points, const int32_t *point2voxel, const float *raw,
+                 const rpc_perturb_cfg *pc /*[host]*/, int64_t ntotal, float *grad_raw /*[ntotal,C]*/,
+                 void *stream);
+
+/* dynamic voxelization: coors [ntotal, ncol]; ncol == 4: (batch, z, y, x) rows as
+ * Det3DDataPreprocessor.voxelize returns them, ncol == 3: (z, y, x) as the Voxelization module
+ * returns them; the three cell columns are all -1 for a dropped point (mmcv CPU rule).
+ * `raw`/`pc` as above. */
+int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
+                         const int32_t *n_per_sample /*[host]*/, int B, const float *raw,
+                         const rpc_perturb_cfg *pc, int32_t *coors, int ncol, void *stream);
+
+/* HardSimpleVFE: out[m, c] = sum_k voxels[m, k, c] / num_points[m], c < F, slots summed in order.
+ * m_dev (device int32, may be NULL) bounds the rows at run time: only min(M, *m_dev) rows are done. */
+int rpc_vfe_mean_fwd(const float *voxels, const int32_t *num_points, int64_t M, int P, int C, int F,
+                     const int32_t *m_dev, float *out, void *stream);
+/* its autograd: grad_voxels[m, k, c] = grad_out[m, c] / num_points[m] (every slot), 0 for c >= F */
+int rpc_vfe_mean_bwd(const float *grad_out, const int32_t *num_points, int64_t M, int P, int C, int F,
+                     const int32_t *m_dev, float *grad_voxels, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RPC_B200_H_ */

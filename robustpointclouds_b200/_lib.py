@@ -1,0 +1,107 @@
+"""ctypes binding of ``librpc_b200.so`` (the C-ABI declared in ``include/rpc_b200.h``).
+
+The library is the product: there is no CPU or PyTorch fallback.  If it has not been built
+(``python -c "import __graft_entry__ as g; g.build()"`` or ``make -C robustpointclouds_b200/csrc``)
+importing this module raises, and every op that needs a kernel raises when handed a non-CUDA tensor.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional, Sequence
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librpc_b200.so")
+
+RPC_MAX_BATCH = 32
+RPC_MAX_CHANNELS = 8
+
+# every symbol include/rpc_b200.h declares (tests check the header against this list and the .so)
+SYMBOLS = (
+    "rpc_abi_version", "rpc_strerror", "rpc_grid_size", "rpc_workspace_bytes", "rpc_voxel_capacity",
+    "rpc_voxelize_hard", "rpc_step_bwd", "rpc_voxelize_dynamic", "rpc_vfe_mean_fwd", "rpc_vfe_mean_bwd",
+)
+
+
+class VoxelCfg(ctypes.Structure):
+    """``rpc_voxel_cfg``: mirrors mmcv ``Voxelization(voxel_size, point_cloud_range, max_num_points,
+    max_voxels)`` plus the point width C and HardSimpleVFE's ``num_features`` F."""
+    _fields_ = [("voxel_size", ctypes.c_float * 3), ("pcr", ctypes.c_float * 6),
+                ("max_points", ctypes.c_int32), ("max_voxels", ctypes.c_int32),
+                ("C", ctypes.c_int32), ("F", ctypes.c_int32)]
+
+    @classmethod
+    def make(cls, voxel_size: Sequence[float], pcr: Sequence[float], max_points: int, max_voxels: int,
+             C: int, F: Optional[int] = None) -> "VoxelCfg":
+        c = cls()
+        c.voxel_size[:] = [float(v) for v in voxel_size]
+        c.pcr[:] = [float(v) for v in pcr]
+        c.max_points, c.max_voxels, c.C, c.F = int(max_points), int(max_voxels), int(C), int(F or C)
+        return c
+
+
+class PerturbCfg(ctypes.Structure):
+    """``rpc_perturb_cfg``: per-channel scale ``eb`` and clamp ``fb`` of VoxelPerturber."""
+    _fields_ = [("eb", ctypes.c_float * RPC_MAX_CHANNELS), ("fb", ctypes.c_float * RPC_MAX_CHANNELS)]
+
+    @classmethod
+    def make(cls, eb: Sequence[float], fb: Sequence[float]) -> "PerturbCfg":
+        c = cls()
+        for i, (a, b) in enumerate(zip(eb, fb)):
+            c.eb[i], c.fb[i] = float(a), float(b)
+        return c
+
+
+class RpcError(RuntimeError):
+    def __init__(self, status: int, where: str):
+        self.status = status
+        super().__init__(f"{where}: {strerror(status)} (status {status})")
+
+
+_lib: Optional[ctypes.CDLL] = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build the sm_100a kernels first "
+            "(make -C robustpointclouds_b200/csrc, or __graft_entry__.build()). "
+            "There is no CPU fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i32, i64, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t
+    cfgp, pcp = ctypes.POINTER(VoxelCfg), ctypes.POINTER(PerturbCfg)
+    i32p = ctypes.POINTER(ctypes.c_int32)
+    L.rpc_abi_version.restype = i32
+    L.rpc_strerror.restype = ctypes.c_char_p
+    L.rpc_strerror.argtypes = [i32]
+    L.rpc_grid_size.argtypes = [cfgp, i32p]
+    L.rpc_workspace_bytes.restype = sz
+    L.rpc_workspace_bytes.argtypes = [cfgp, i32, i32p]
+    L.rpc_voxel_capacity.restype = i64
+    L.rpc_voxel_capacity.argtypes = [cfgp, i32, i32p]
+    L.rpc_voxelize_hard.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
+    L.rpc_step_bwd.argtypes = [cfgp, vp, vp, vp, vp, pcp, i64, vp, vp]
+    L.rpc_voxelize_dynamic.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, i32, vp]
+    L.rpc_vfe_mean_fwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
+    L.rpc_vfe_mean_bwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
+    for name in SYMBOLS:
+        getattr(L, name)                      # AttributeError if the .so is stale
+    _lib = L
+    return L
+
+
+def strerror(status: int) -> str:
+    return lib().rpc_strerror(int(status)).decode()
+
+
+def check(status: int, where: str) -> None:
+    if status != 0:
+        raise RpcError(status, where)
+
+
+def counts(n_per_sample: Sequence[int]):
+    arr = (ctypes.c_int32 * len(n_per_sample))(*[int(n) for n in n_per_sample])
+    return arr

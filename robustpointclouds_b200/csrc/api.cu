@@ -1,0 +1,351 @@
+// api.cu -- the C-ABI of include/rpc_b200.h: argument validation, workspace carving, launches.
+// No allocation, no host synchronisation, fixed launch topology per call (CUDA-graph capturable).
+#include <math.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "dynamic.cuh"
+#include "vfe.cuh"
+#include "voxelize_hard.cuh"
+
+using namespace rpc;
+
+namespace {
+
+constexpr int kNumSM = 148;                       // B200
+constexpr size_t kAlign = 256;
+inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+int check_cfg(const rpc_voxel_cfg *cfg, bool hard)
+{
+    if (!cfg) return RPC_ERR_NULL;
+    if (cfg->C < 3 || cfg->C > RPC_MAX_CHANNELS) return RPC_ERR_CONFIG;
+    if (cfg->F < 1 || cfg->F > cfg->C) return RPC_ERR_CONFIG;
+    for (int d = 0; d < 3; ++d) {
+        if (!(cfg->voxel_size[d] > 0.0f)) return RPC_ERR_CONFIG;
+        if (!(cfg->pcr[3 + d] > cfg->pcr[d])) return RPC_ERR_CONFIG;
+    }
+    if (hard && (cfg->max_points < 1 || cfg->max_voxels < 1)) return RPC_ERR_CONFIG;
+    return RPC_OK;
+}
+
+// grid[d] = round((hi - lo) / vs) evaluated in fp32 (mmcv voxelization.cpp)
+int make_grid(const rpc_voxel_cfg *cfg, GridDesc *gd)
+{
+    int64_t cells = 1;
+    for (int d = 0; d < 3; ++d) {
+        volatile float diff = cfg->pcr[3 + d] - cfg->pcr[d];
+        volatile float q = diff / cfg->voxel_size[d];
+        const float g = roundf(q);
+        if (!(g >= 1.0f) || g > 2147483647.0f) return RPC_ERR_CONFIG;
+        gd->lo[d] = cfg->pcr[d];
+        gd->vs[d] = cfg->voxel_size[d];
+        gd->g[d] = (int)g;
+        gd->gf[d] = (float)gd->g[d];
+        cells *= gd->g[d];
+        if (cells > 0x7FFFFFFELL) return RPC_ERR_TOO_LARGE;
+    }
+    gd->P = cfg->max_points; gd->V = cfg->max_voxels; gd->C = cfg->C; gd->F = cfg->F;
+    return RPC_OK;
+}
+
+struct Plan {                                     // host-side layout of one batched call
+    BatchDesc bd;
+    int64_t ntotal, ntiles, tab_total, cap;
+    size_t o_keys, o_first, o_vid, o_hslot, o_tiles, o_slots, o_voff, bytes;
+};
+
+int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
+{
+    if (!n) return RPC_ERR_NULL;
+    if (B < 1 || B > RPC_MAX_BATCH) return RPC_ERR_BATCH;
+    memset(pl, 0, sizeof(*pl));
+    pl->bd.B = B;
+    int64_t pts = 0, tiles = 0, tab = 0, cap = 0;
+    for (int b = 0; b < B; ++b) {
+        if (n[b] < 0) return RPC_ERR_BATCH;
+        pl->bd.pt_begin[b] = (int)pts;
+        pl->bd.tile_begin[b] = (int)tiles;
+        int lg = 5;
+        while ((int64_t(1) << lg) < 2 * (int64_t)n[b]) ++lg;
+        pl->bd.tab_off[b] = (uint32_t)tab;
+        pl->bd.tab_mask[b] = (uint32_t)((int64_t(1) << lg) - 1);
+        pl->bd.tab_shift[b] = 32 - lg;
+        tab += int64_t(1) << lg;
+        pts += n[b];
+        tiles += (n[b] + kTile - 1) / kTile;
+        cap += n[b] < cfg->max_voxels ? n[b] : cfg->max_voxels;
+        if (pts > 0x7FFFFFF0LL || tab > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
+    }
+    pl->bd.pt_begin[B] = (int)pts;
+    pl->bd.tile_begin[B] = (int)tiles;
+    pl->ntotal = pts; pl->ntiles = tiles; pl->tab_total = tab; pl->cap = cap;
+    if (cap * (int64_t)cfg->max_points > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
+    size_t o = 0;
+    pl->o_keys = o;  o += align_up(4 * (size_t)tab);      // keys and first are contiguous:
+    pl->o_first = o; o += align_up(4 * (size_t)tab);      // one 0xFF fill initialises both
+    pl->o_vid = o;   o += align_up(4 * (size_t)tab);
+    pl->o_hslot = o; o += align_up(4 * (size_t)pts);
+    pl->o_tiles = o; o += align_up(4 * (size_t)(tiles + 1));
+    pl->o_slots = o; o += align_up(4 * (size_t)cap * cfg->max_points);
+    pl->o_voff = o;  o += align_up(4 * (size_t)(B + 1));
+    pl->bytes = o;
+    return RPC_OK;
+}
+
+HardWs carve(const Plan &pl, void *workspace)
+{
+    char *w = static_cast<char *>(workspace);
+    HardWs ws;
+    ws.keys = reinterpret_cast<uint32_t *>(w + pl.o_keys);
+    ws.first = reinterpret_cast<uint32_t *>(w + pl.o_first);
+    ws.vid = reinterpret_cast<int *>(w + pl.o_vid);
+    ws.hslot = reinterpret_cast<int *>(w + pl.o_hslot);
+    ws.tile_count = reinterpret_cast<int *>(w + pl.o_tiles);
+    ws.slots = reinterpret_cast<int *>(w + pl.o_slots);
+    ws.voff = reinterpret_cast<int *>(w + pl.o_voff);
+    return ws;
+}
+
+void fill_perturb(const rpc_voxel_cfg *cfg, const rpc_perturb_cfg *pc, PerturbDesc *pd)
+{
+    memset(pd, 0, sizeof(*pd));
+    if (pc)
+        for (int c = 0; c < cfg->C; ++c) { pd->eb[c] = pc->eb[c]; pd->fb[c] = pc->fb[c]; }
+}
+
+inline bool misaligned(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
+
+// rows of voxels per CTA in the gather / mean kernels: the [VB,P,C] tile must fit shared memory
+int pick_vb(int P, int C, size_t *smem)
+{
+    const size_t row = (size_t)P * C * sizeof(float) + sizeof(int);
+    size_t vb = (64 * 1024) / row;
+    if (vb > 64) vb = 64;
+    vb &= ~size_t(3);
+    if (vb < 4) {
+        vb = 4;
+        if (vb * row > 200 * 1024) return 0;
+    }
+    *smem = vb * row;
+    return (int)vb;
+}
+
+template <int C>
+int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const float *points,
+                const float *raw, float *voxels, int32_t *coors, int32_t *num_points,
+                int32_t *voxel_num, int32_t *p2v, int32_t *p2s, float *feats, HardWs ws,
+                cudaStream_t st)
+{
+    const int nt = (int)pl.ntiles;
+    size_t smem = 0;
+    const int VB = pick_vb(gd.P, C, &smem);
+    if (!VB) return RPC_ERR_CONFIG;
+    // keys = kEmpty, first = 0xFFFFFFFF (contiguous)
+    if (cudaMemsetAsync(ws.keys, 0xFF, (pl.o_vid - pl.o_keys), st) != cudaSuccess) return RPC_ERR_CUDA;
+    if (nt > 0) {
+        if (raw) k_cell_hash<C, true><<<nt, kThreads, 0, st>>>(points, raw, gd, pl.bd, pd, ws, p2v, p2s);
+        else     k_cell_hash<C, false><<<nt, kThreads, 0, st>>>(points, raw, gd, pl.bd, pd, ws, p2v, p2s);
+        k_count_firsts<<<nt, kThreads, 0, st>>>(pl.bd, ws);
+    }
+    k_scan_tiles<<<1, kScanThreads, 0, st>>>(pl.bd, ws, gd.V, voxel_num);
+    if (nt > 0 && pl.cap > 0) {
+        k_assign_voxels<<<nt, kThreads, 0, st>>>(gd, pl.bd, ws, coors);
+        if (gd.P > 1) k_rank_in_voxel<<<nt, kThreads, 0, st>>>(pl.bd, ws, gd.P);
+        int64_t blocks = (pl.cap + VB - 1) / VB;
+        if (blocks > kNumSM * 8) blocks = kNumSM * 8;
+        auto kern = raw ? k_gather_mean<C, true> : k_gather_mean<C, false>;
+        if (smem > 48 * 1024 &&
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return RPC_ERR_CUDA;
+        kern<<<(int)blocks, kThreads, smem, st>>>(points, raw, pd, ws, pl.bd.B, gd.P, gd.F, VB, voxels,
+                                                  num_points, feats, p2v, p2s);
+    }
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+}  // namespace
+
+// =========================================================================================== C-ABI
+extern "C" {
+
+#define RPC_API __attribute__((visibility("default")))
+
+RPC_API int rpc_abi_version(void) { return RPC_ABI_VERSION; }
+
+RPC_API const char *rpc_strerror(int status)
+{
+    switch (status) {
+        case RPC_OK: return "ok";
+        case RPC_ERR_NULL: return "required pointer is NULL";
+        case RPC_ERR_CONFIG: return "invalid voxel configuration (C, F, P, V, voxel_size or range)";
+        case RPC_ERR_BATCH: return "batch size outside 1..32 or negative point count";
+        case RPC_ERR_WORKSPACE: return "workspace too small (see rpc_workspace_bytes)";
+        case RPC_ERR_CUDA: return "CUDA launch failed";
+        case RPC_ERR_TOO_LARGE: return "point count, table or grid exceeds 31-bit indexing";
+        case RPC_ERR_ALIGN: return "pointer not 16-byte aligned";
+        default: return "unknown status";
+    }
+}
+
+RPC_API int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3])
+{
+    if (!grid) return RPC_ERR_NULL;
+    int st = check_cfg(cfg, false);
+    if (st) return st;
+    GridDesc gd;
+    st = make_grid(cfg, &gd);
+    if (st) return st;
+    grid[0] = gd.g[0]; grid[1] = gd.g[1]; grid[2] = gd.g[2];
+    return RPC_OK;
+}
+
+RPC_API size_t rpc_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
+{
+    Plan pl;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return 0;
+    return pl.bytes;
+}
+
+RPC_API int64_t rpc_voxel_capacity(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
+{
+    Plan pl;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return -1;
+    return pl.cap;
+}
+
+RPC_API int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points,
+                              const int32_t *n_per_sample, int B, const float *raw,
+                              const rpc_perturb_cfg *pc, float *voxels, int32_t *coors,
+                              int32_t *num_points, int32_t *voxel_num, int32_t *point2voxel,
+                              int32_t *point2slot, float *feats, void *workspace,
+                              size_t workspace_bytes, void *stream)
+{
+    int st = check_cfg(cfg, true);
+    if (st) return st;
+    GridDesc gd;
+    if ((st = make_grid(cfg, &gd))) return st;
+    Plan pl;
+    if ((st = make_plan(cfg, B, n_per_sample, &pl))) return st;
+    if (!voxel_num || !workspace) return RPC_ERR_NULL;
+    if (pl.ntotal > 0 && !points) return RPC_ERR_NULL;
+    if (pl.cap > 0 && (!voxels || !coors || !num_points)) return RPC_ERR_NULL;
+    if (raw && !pc) return RPC_ERR_NULL;
+    if (workspace_bytes < pl.bytes) return RPC_ERR_WORKSPACE;
+    if (misaligned(points) || misaligned(raw) || misaligned(voxels) || misaligned(coors) ||
+        misaligned(workspace) || misaligned(feats))
+        return RPC_ERR_ALIGN;
+    PerturbDesc pd;
+    fill_perturb(cfg, pc, &pd);
+    HardWs ws = carve(pl, workspace);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (cfg->C) {
+#define RPC_CASE(CC)                                                                              \
+    case CC: return launch_hard<CC>(gd, pl, pd, points, raw, voxels, coors, num_points, voxel_num, \
+                                    point2voxel, point2slot, feats, ws, s);
+        RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+#undef RPC_CASE
+    }
+    return RPC_ERR_CONFIG;
+}
+
+RPC_API int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats,
+                         const int32_t *num_points, const int32_t *point2voxel, const float *raw,
+                         const rpc_perturb_cfg *pc, int64_t ntotal, float *grad_raw, void *stream)
+{
+    int st = check_cfg(cfg, false);
+    if (st) return st;
+    if (ntotal < 0 || ntotal > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
+    if (ntotal == 0) return RPC_OK;
+    if (!grad_feats || !num_points || !point2voxel || !grad_raw) return RPC_ERR_NULL;
+    if (raw && !pc) return RPC_ERR_NULL;
+    if (misaligned(grad_feats) || misaligned(raw) || misaligned(grad_raw)) return RPC_ERR_ALIGN;
+    PerturbDesc pd;
+    fill_perturb(cfg, pc, &pd);
+    int64_t blocks = (ntotal + kThreads - 1) / kThreads;
+    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (cfg->C) {
+#define RPC_CASE(CC)                                                                               \
+    case CC:                                                                                       \
+        k_step_bwd<CC><<<(int)blocks, kThreads, 0, s>>>(grad_feats, num_points, point2voxel, raw, pd, \
+                                                        ntotal, cfg->F, grad_raw);                 \
+        break;
+        RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+#undef RPC_CASE
+        default: return RPC_ERR_CONFIG;
+    }
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_vfe_mean_fwd(const float *voxels, const int32_t *num_points, int64_t M, int P, int C,
+                             int F, const int32_t *m_dev, float *out, void *stream)
+{
+    if (P < 1 || C < 1 || F < 1 || F > C || M < 0) return RPC_ERR_CONFIG;
+    if (M == 0) return RPC_OK;
+    if (!voxels || !num_points || !out) return RPC_ERR_NULL;
+    if (misaligned(voxels)) return RPC_ERR_ALIGN;
+    size_t smem = 0;
+    const int VB = pick_vb(P, C, &smem);
+    if (!VB) return RPC_ERR_CONFIG;
+    if (smem > 48 * 1024 &&
+        cudaFuncSetAttribute(k_vfe_mean_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+        return RPC_ERR_CUDA;
+    int64_t blocks = (M + VB - 1) / VB;
+    if (blocks > kNumSM * 8) blocks = kNumSM * 8;
+    k_vfe_mean_fwd<<<(int)blocks, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(
+        voxels, num_points, M, m_dev, P, C, F, VB, out);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_vfe_mean_bwd(const float *grad_out, const int32_t *num_points, int64_t M, int P, int C,
+                             int F, const int32_t *m_dev, float *grad_voxels, void *stream)
+{
+    if (P < 1 || C < 1 || F < 1 || F > C || M < 0) return RPC_ERR_CONFIG;
+    if (M == 0) return RPC_OK;
+    if (!grad_out || !num_points || !grad_voxels) return RPC_ERR_NULL;
+    int64_t blocks = (M * P * C + kThreads - 1) / kThreads;
+    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
+    k_vfe_mean_bwd<<<(int)blocks, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        grad_out, num_points, M, m_dev, P, C, F, grad_voxels);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
+                                 const int32_t *n_per_sample, int B, const float *raw,
+                                 const rpc_perturb_cfg *pc, int32_t *coors, int ncol, void *stream)
+{
+    int st = check_cfg(cfg, false);
+    if (st) return st;
+    if (ncol != 3 && ncol != 4) return RPC_ERR_CONFIG;
+    GridDesc gd;
+    if ((st = make_grid(cfg, &gd))) return st;
+    rpc_voxel_cfg c2 = *cfg;
+    c2.max_points = 1; c2.max_voxels = 1;
+    Plan pl;
+    if ((st = make_plan(&c2, B, n_per_sample, &pl))) return st;
+    if (pl.ntotal == 0) return RPC_OK;
+    if (!points || !coors) return RPC_ERR_NULL;
+    if (raw && !pc) return RPC_ERR_NULL;
+    if (misaligned(points) || misaligned(raw) || misaligned(coors)) return RPC_ERR_ALIGN;
+    PerturbDesc pd;
+    fill_perturb(cfg, pc, &pd);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int nt = (int)pl.ntiles;
+#define RPC_LAUNCH(CC, PP, NC) \
+    k_dynamic_voxelize<CC, PP, NC><<<nt, kThreads, 0, s>>>(points, raw, gd, pl.bd, pd, coors)
+#define RPC_CASE(CC)                                                              \
+    case CC:                                                                      \
+        if (raw) { if (ncol == 4) RPC_LAUNCH(CC, true, 4); else RPC_LAUNCH(CC, true, 3); }   \
+        else     { if (ncol == 4) RPC_LAUNCH(CC, false, 4); else RPC_LAUNCH(CC, false, 3); } \
+        break;
+    switch (cfg->C) {
+        RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+        default: return RPC_ERR_CONFIG;
+    }
+#undef RPC_CASE
+#undef RPC_LAUNCH
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+}  // extern "C"

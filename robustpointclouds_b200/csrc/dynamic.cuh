@@ -1,0 +1,40 @@
+// dynamic.cuh -- dynamic voxelization (per-point cell coordinates; mmcv dynamic_voxelize_forward,
+// CPU rule: all three columns are -1 for a dropped point) for a batch of sweeps.
+#pragma once
+#include "common.cuh"
+#include "voxelize_hard.cuh"
+
+namespace rpc {
+
+// coors row = (batch, z, y, x) when NCOL == 4 (what Det3DDataPreprocessor.voxelize returns after
+// padding the batch index), (z, y, x) when NCOL == 3 (what the Voxelization module returns).
+template <int C, bool PERTURB, int NCOL>
+__global__ void __launch_bounds__(kThreads)
+k_dynamic_voxelize(const float *__restrict__ pts, const float *__restrict__ raw,
+                   const __grid_constant__ GridDesc gd, const __grid_constant__ BatchDesc bd,
+                   const __grid_constant__ PerturbDesc pd, int *__restrict__ coors)
+{
+    const int tile = blockIdx.x;
+    const int b = tile_to_sweep(bd, tile);
+    const int begin = bd.pt_begin[b] + (tile - bd.tile_begin[b]) * kTile;
+    const int end = min(begin + kTile, bd.pt_begin[b + 1]);
+#pragma unroll
+    for (int k = 0; k < kTile / kThreads; ++k) {
+        const int i = begin + k * kThreads + threadIdx.x;
+        if (i >= end) break;
+        float x, y, z;
+        load_xyz<C, PERTURB>(pts, raw, pd, i, x, y, z);
+        int cx = axis_cell(x, gd.lo[0], gd.vs[0], gd.gf[0]);
+        int cy = axis_cell(y, gd.lo[1], gd.vs[1], gd.gf[1]);
+        int cz = axis_cell(z, gd.lo[2], gd.vs[2], gd.gf[2]);
+        if ((cx | cy | cz) < 0) cx = cy = cz = -1;
+        if constexpr (NCOL == 4) {
+            reinterpret_cast<int4 *>(coors)[i] = make_int4(b, cz, cy, cx);
+        } else {
+            int *o = coors + (int64_t)i * 3;
+            o[0] = cz; o[1] = cy; o[2] = cx;
+        }
+    }
+}
+
+}  // namespace rpc

@@ -1,0 +1,188 @@
+"""Tensor-level entry points over the C-ABI: PyTorch owns device memory and streams, the kernels in
+``librpc_b200.so`` do the work.  No op here has a CPU or eager-PyTorch fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import PerturbCfg, VoxelCfg
+
+
+def _need_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("robustpointclouds_b200 ops run on CUDA tensors only (sm_100a kernels; "
+                               "there is no CPU fallback)")
+        dev = t.device
+    return dev
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream(dev: torch.device) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def grid_size(cfg: VoxelCfg) -> Tuple[int, int, int]:
+    g = (ctypes.c_int32 * 3)()
+    _lib.check(_lib.lib().rpc_grid_size(ctypes.byref(cfg), g), "rpc_grid_size")
+    return g[0], g[1], g[2]
+
+
+@dataclass
+class HardVoxels:
+    """Outputs of one batched hard voxelization, sized at capacity (sum_b min(n_b, V)) rows; only the
+    first ``voxel_num[-1]`` rows are defined.  ``voxel_num`` lives on the device ([B+1]: per sweep,
+    then the total) so that nothing here forces a host sync."""
+    voxels: torch.Tensor
+    coors: torch.Tensor
+    num_points: torch.Tensor
+    voxel_num: torch.Tensor
+    point2voxel: Optional[torch.Tensor]
+    point2slot: Optional[torch.Tensor]
+    feats: Optional[torch.Tensor]
+    capacity: int
+
+    def total(self) -> int:
+        """number of voxels (host sync)"""
+        return int(self.voxel_num[-1].item())
+
+
+class Workspace:
+    """Grow-only scratch buffer per device, reused across calls (stream-ordered use only)."""
+
+    def __init__(self) -> None:
+        self._buf = {}
+
+    def get(self, nbytes: int, dev: torch.device) -> torch.Tensor:
+        b = self._buf.get(dev)
+        if b is None or b.numel() < nbytes:
+            b = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+            self._buf[dev] = b
+        return b
+
+
+_default_ws = Workspace()
+
+
+def hard_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelCfg,
+                  raw: Optional[torch.Tensor] = None, bounds: Optional[PerturbCfg] = None,
+                  want_feats: bool = False, want_maps: bool = False,
+                  out: Optional[HardVoxels] = None, workspace: Optional[torch.Tensor] = None) -> HardVoxels:
+    """``rpc_voxelize_hard``: B sweeps concatenated in ``points`` [sum n_b, C]; ``raw`` [sum n_b, C] +
+    ``bounds`` voxelize the perturbed points x + clamp(raw*eb, +-fb) instead."""
+    dev = _need_cuda(points, raw)
+    points = _f32c(points)
+    if points.dim() != 2 or points.shape[1] != cfg.C:
+        raise ValueError(f"points must be [N, {cfg.C}], got {tuple(points.shape)}")
+    if sum(n_per_sample) != points.shape[0]:
+        raise ValueError("n_per_sample does not add up to the number of rows")
+    if raw is not None:
+        raw = _f32c(raw)
+        if raw.shape != points.shape or bounds is None:
+            raise ValueError("raw must match points and come with bounds")
+    L = _lib.lib()
+    B = len(n_per_sample)
+    n_arr = _lib.counts(n_per_sample)
+    cap = L.rpc_voxel_capacity(ctypes.byref(cfg), B, n_arr)
+    if cap < 0:
+        raise _lib.RpcError(-2, "rpc_voxel_capacity")
+    nbytes = L.rpc_workspace_bytes(ctypes.byref(cfg), B, n_arr)
+    ws = workspace if workspace is not None else _default_ws.get(nbytes, dev)
+    N, P, C, F = points.shape[0], cfg.max_points, cfg.C, cfg.F
+    if out is None:
+        i32 = dict(dtype=torch.int32, device=dev)
+        out = HardVoxels(
+            voxels=torch.empty((cap, P, C), dtype=torch.float32, device=dev),
+            coors=torch.empty((cap, 4), **i32), num_points=torch.empty((cap,), **i32),
+            voxel_num=torch.empty((B + 1,), **i32),
+            point2voxel=torch.empty((N,), **i32) if want_maps else None,
+            point2slot=torch.empty((N,), **i32) if want_maps else None,
+            feats=torch.empty((cap, F), dtype=torch.float32, device=dev) if want_feats else None,
+            capacity=int(cap))
+    st = L.rpc_voxelize_hard(ctypes.byref(cfg), _ptr(points), n_arr, B, _ptr(raw),
+                             ctypes.byref(bounds) if bounds is not None else None,
+                             _ptr(out.voxels), _ptr(out.coors), _ptr(out.num_points), _ptr(out.voxel_num),
+                             _ptr(out.point2voxel), _ptr(out.point2slot), _ptr(out.feats),
+                             ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(st, "rpc_voxelize_hard")
+    return out
+
+
+def step_bwd(grad_feats: torch.Tensor, num_points: torch.Tensor, point2voxel: torch.Tensor,
+             cfg: VoxelCfg, raw: Optional[torch.Tensor] = None, bounds: Optional[PerturbCfg] = None,
+             out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``rpc_step_bwd``: gradient of the voxel means w.r.t. the raw per-point perturbation [N, C]
+    (or w.r.t. the point features when ``raw`` is None)."""
+    dev = _need_cuda(grad_feats, num_points, point2voxel, raw)
+    grad_feats = _f32c(grad_feats)
+    N = point2voxel.shape[0]
+    if raw is not None:
+        raw = _f32c(raw)
+    if out is None:
+        out = torch.empty((N, cfg.C), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_step_bwd(ctypes.byref(cfg), _ptr(grad_feats), _ptr(num_points), _ptr(point2voxel),
+                                 _ptr(raw), ctypes.byref(bounds) if bounds is not None else None,
+                                 N, _ptr(out), _stream(dev))
+    _lib.check(st, "rpc_step_bwd")
+    return out
+
+
+def dynamic_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelCfg,
+                     raw: Optional[torch.Tensor] = None, bounds: Optional[PerturbCfg] = None,
+                     ncol: int = 4) -> torch.Tensor:
+    """``rpc_voxelize_dynamic``: per-point (batch, z, y, x) (ncol 4) or (z, y, x) (ncol 3); dropped
+    points get -1 in all three cell columns."""
+    dev = _need_cuda(points, raw)
+    points = _f32c(points)
+    if raw is not None:
+        raw = _f32c(raw)
+    coors = torch.empty((points.shape[0], ncol), dtype=torch.int32, device=dev)
+    st = _lib.lib().rpc_voxelize_dynamic(ctypes.byref(cfg), _ptr(points), _lib.counts(n_per_sample),
+                                         len(n_per_sample), _ptr(raw),
+                                         ctypes.byref(bounds) if bounds is not None else None,
+                                         _ptr(coors), ncol, _stream(dev))
+    _lib.check(st, "rpc_voxelize_dynamic")
+    return coors
+
+
+def vfe_mean_fwd(voxels: torch.Tensor, num_points: torch.Tensor, num_features: int,
+                 m_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    dev = _need_cuda(voxels, num_points)
+    voxels = _f32c(voxels)
+    num_points = num_points.to(torch.int32).contiguous()
+    M, P, C = voxels.shape
+    out = torch.empty((M, num_features), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_vfe_mean_fwd(_ptr(voxels), _ptr(num_points), M, P, C, num_features, _ptr(m_dev),
+                                     _ptr(out), _stream(dev))
+    _lib.check(st, "rpc_vfe_mean_fwd")
+    return out
+
+
+def vfe_mean_bwd(grad_out: torch.Tensor, num_points: torch.Tensor, P: int, C: int,
+                 m_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    dev = _need_cuda(grad_out, num_points)
+    grad_out = _f32c(grad_out)
+    num_points = num_points.to(torch.int32).contiguous()
+    M, F = grad_out.shape
+    g = torch.empty((M, P, C), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_vfe_mean_bwd(_ptr(grad_out), _ptr(num_points), M, P, C, F, _ptr(m_dev), _ptr(g),
+                                     _stream(dev))
+    _lib.check(st, "rpc_vfe_mean_bwd")
+    return g
