@@ -1,0 +1,401 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the per-step adversarial input path (BASELINE.json metric):
+perturb (scale, clamp, add) -> hard voxelize -> HardSimpleVFE mean forward -> backward to the raw
+per-point perturbation, in M input points/s, on synthetic sweeps of the named shapes.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload kitti|nuscenes] [--impl b200|reference]
+
+A *step* is one pass of the path over one batch (KITTI: B=6 sweeps x 120k points x 4 features =
+BASELINE.json configs[1]; nuScenes: B=4 x 300k x 5 = configs[2]).  N > 1 is launched by torchrun, one
+rank per GPU, every rank its own batch (weak scaling, no data-path collective), and the step ends with
+the NCCL all-reduce of the perturber's flat parameter-gradient buffer (34 641 fp32 for KITTI).
+
+Timing: every step is bracketed by its own pair of CUDA events on the launching stream; between steps,
+outside the event pairs, a 512 MiB buffer is overwritten so that every step starts with a cold L2; the K
+step times are summed, MAX over ranks.  `value` = inputs resident in HBM; `e2e` = host (pinned) buffers
+in and out through the C-ABI, copies inside the timed region.  `--impl reference` times the CPU oracle
+(mmcv CPU semantics, dense per-call table -- see oracle/rpc_oracle.c) on the host cores instead.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+PERTURBER_PARAMS = {4: 34641, 5: 34772}        # hidden [64,128,64]
+L2_FLUSH_BYTES = 512 << 20
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def b_alg_hard(N, C, P, M, K, F):
+    """SURVEY 8(d) algorithmic bytes of the whole hard step (sum over the batch)"""
+    return 4 * (N * C + M * P * C + 5 * M + 3 * K * C + 2 * M * F)
+
+
+class ClockSampler(threading.Thread):
+    """polls SM clock and throttle reasons through NVML while the timed region runs"""
+
+    def __init__(self, index: int, period_s: float = 0.005):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period_s
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            self.nv = pynvml
+            pynvml.nvmlInit()
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            pass
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {getattr(nv, k): k for k in dir(nv) if k.startswith("nvmlClocksThrottleReason")
+                 or k.startswith("nvmlClocksEventReason")}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if isinstance(bit, int) and bit and (r & bit) and bin(bit).count("1") == 1:
+                        self.reasons.add(nm.replace("nvmlClocksThrottleReason", "").replace("nvmlClocksEventReason", ""))
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        s = sorted(self.samples)
+        benign = {"None", "GpuIdle", "ApplicationsClocksSetting", "All"}
+        bad_map = {"HwSlowdown": "hw_slowdown", "HwThermalSlowdown": "hw_thermal_slowdown",
+                   "SwThermalSlowdown": "sw_thermal_slowdown", "SwPowerCap": "sw_power_cap",
+                   "HwPowerBrakeSlowdown": "hw_power_brake", "SyncBoost": "sync_boost",
+                   "DisplayClockSetting": "display_clock"}
+        reasons = sorted({bad_map.get(r, r) for r in self.reasons if r not in benign})
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": reasons,
+                "samples": len(s)}
+
+
+def workload(name: str):
+    from robustpointclouds_b200 import synth
+    p = synth.PRESETS[name]
+    B = 6 if name == "kitti" else 4
+    return p, B
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference(args):
+    """The reference's CPU implementation of the path (oracle restatement of mmcv's CPU kernels, dense
+    per-call cell table like mmcv) on the host cores, one sweep per thread."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import ref_path as orc
+    from robustpointclouds_b200 import synth
+
+    p, B = workload(args.workload)
+    C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
+    vs, pcr = p["voxel_size"], p["point_cloud_range"]
+    cores = len(os.sched_getaffinity(0))
+    threads = max(1, min(cores, 32))            # every thread allocates its own dense table (360 MB for KITTI)
+    clouds = synth.make_batch(args.workload, B)
+    raws = [synth.make_raw(c, 99 + i) for i, c in enumerate(clouds)]
+    eb, fb = orc.perturber_bounds(C, True)
+    gf = np.random.default_rng(0).normal(size=(V, C)).astype(np.float32)
+    orc.lib()
+    # a step = S sweeps drawn round-robin from the batch, one per host thread, S bounded so that the
+    # whole run ends within ~2 minutes
+    bufs = [orc.StepBuffers(len(clouds[0]), C, P, V, C)]
+    t0 = time.perf_counter()
+    orc.step_fused(clouds[0], raws[0], eb, fb, vs, pcr, P, V, C, gf, table_mode=0, buf=bufs[0])
+    t1 = time.perf_counter() - t0
+    S = threads
+    if (args.steps + args.warmup) * t1 * 1.5 > 120.0:      # even one sweep per thread per step is too long
+        args.steps = max(3, int(120.0 / (t1 * 1.5)) - args.warmup)
+    bufs = [orc.StepBuffers(len(clouds[i % B]), C, P, V, C) for i in range(S)]
+
+    def one(i):
+        j = i % B
+        return orc.step_fused(clouds[j], raws[j], eb, fb, vs, pcr, P, V, C, gf, table_mode=0, buf=bufs[i])[0]
+
+    idx = list(range(S))
+    with ThreadPoolExecutor(threads) as ex:
+        for _ in range(args.warmup):
+            list(ex.map(one, idx))
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            list(ex.map(one, idx))
+        dt = time.perf_counter() - t0
+    pts = sum(len(clouds[i % B]) for i in idx) * args.steps
+    val = pts / dt / 1e6
+    sample = (f"{S} sweeps per step drawn round-robin from the batch's {B}, {threads} threads (one sweep per thread), "
+              f"dense int32[{'x'.join(map(str, orc.grid_size(vs, pcr)[::-1]))}] table allocated+filled per call like mmcv")
+    line = {
+        "impl": "reference", "metric": "M points/s perturb+voxelize+VFE fwd/bwd", "value": round(val, 4),
+        "unit": "M points/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(args.workload, p, B, note="CPU oracle port of the reference's mmcv CPU path"),
+        "cpu_baseline": {"value": round(val, 4), "unit": "M points/s", "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": round(val, 4), "unit": "M points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def config_dict(name, p, B, note=None, **kw):
+    d = {"workload": (f"SECOND KITTI adversarial step: perturb(0.2 m)+hard voxelize+HardSimpleVFE fwd/bwd, "
+                      f"batch {B} x {p['N']} pts x {p['C']}" if name == "kitti" else
+                      f"CenterPoint nuScenes 10-sweep hard step: perturb+hard voxelize+HardSimpleVFE fwd/bwd, "
+                      f"batch {B} x {p['N']} pts x {p['C']}"),
+         "voxel_size": p["voxel_size"], "point_cloud_range": p["point_cloud_range"],
+         "max_num_points": p["max_num_points"], "max_voxels": p["max_voxels"][0], "batch_per_gpu": B,
+         "points_per_sweep": p["N"], "distribution": "lidar (synth.py)"}
+    if note:
+        d["note"] = note
+    d.update(kw)
+    return d
+
+
+def cpu_baseline(name, clouds, raws, p, budget_s=12.0):
+    """oracle (port) on ONE host core, bounded sample of the same batch"""
+    from oracle import ref_path as orc
+    C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
+    eb, fb = orc.perturber_bounds(C, True)
+    gf = np.random.default_rng(0).normal(size=(V, C)).astype(np.float32)
+    buf = orc.StepBuffers(max(len(c) for c in clouds), C, P, V, C)
+    orc.lib()
+    done, pts = 0, 0
+    t0 = time.perf_counter()
+    while True:
+        i = done % len(clouds)
+        b = orc.StepBuffers(len(clouds[i]), C, P, V, C) if len(clouds[i]) != buf.perturbed.shape[0] else buf
+        orc.step_fused(clouds[i], raws[i], eb, fb, p["voxel_size"], p["point_cloud_range"], P, V, C, gf,
+                       table_mode=0, buf=b)
+        done += 1
+        pts += len(clouds[i])
+        dt = time.perf_counter() - t0
+        if dt > budget_s or done >= 4 * len(clouds):
+            break
+    return {"value": round(pts / dt / 1e6, 4), "unit": "M points/s", "cores": 1, "kind": "port",
+            "sample": f"{done} sweeps of the batch, sequential on 1 core, {dt:.1f} s, dense per-call cell table like mmcv"}
+
+
+# ------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from oracle import ref_path as orc           # bounds table + cpu_baseline leg only
+    from robustpointclouds_b200 import PerturbCfg, VoxelCfg, _lib, ops, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    p, B = workload(args.workload)
+    C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
+    F = C
+    cfg = VoxelCfg.make(p["voxel_size"], p["point_cloud_range"], P, V, C, F)
+    clouds = synth.make_batch(args.workload, B, seed=1234 + rank * B)
+    raws = [synth.make_raw(c, 99 + rank * B + i) for i, c in enumerate(clouds)]
+    n = [len(c) for c in clouds]
+    N = sum(n)
+    eb, fb = orc.perturber_bounds(C, True)
+    bounds = PerturbCfg.make(eb, fb)
+    h_pts = torch.from_numpy(np.concatenate(clouds)).pin_memory()
+    h_raw = torch.from_numpy(np.concatenate(raws)).pin_memory()
+    pts, raw = h_pts.to(dev), h_raw.to(dev)
+    out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True)
+    cap = out.capacity
+    gfe = torch.randn((cap, F), device=dev, generator=torch.Generator(dev).manual_seed(5 + rank))
+    graw = torch.empty((N, C), dtype=torch.float32, device=dev)
+    pgrad = torch.zeros(PERTURBER_PARAMS.get(C, 34641), dtype=torch.float32, device=dev)  # flat perturber grads
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+
+    def path():
+        ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+        ops.step_bwd(gfe, out.num_points, out.point2voxel, cfg, raw=raw, bounds=bounds, out=graw)
+
+    graph = None
+    if not args.no_graph:
+        s = torch.cuda.Stream(dev)
+        with torch.cuda.stream(s):
+            path()
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            path()
+
+    def step():
+        graph.replay() if graph is not None else path()
+        if world > 1:
+            dist.all_reduce(pgrad)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            flush.zero_(); fn()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b in ev:
+            flush.zero_()
+            a.record(); fn(); b.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        tot = sum(a.elapsed_time(b) for a, b in ev)
+        if world > 1:
+            t = torch.tensor([tot], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            tot = float(t.item())
+        return tot                                   # ms for `steps` steps
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    tot_ms = timed(step, args.steps, args.warmup)
+    clocks = sampler.stop()
+
+    vn = out.voxel_num.cpu().numpy()
+    M = int(vn[-1])
+    K = int((out.point2voxel >= 0).sum().item())
+    launches_per_step = 7 + (0 if P > 1 else -1)       # our kernels (the table memset is the driver's)
+
+    # ---- e2e: pinned host buffers in, every API-visible output back to pinned host buffers
+    h_out = {k: torch.empty_like(v, device="cpu").pin_memory() for k, v in
+             dict(voxels=out.voxels, coors=out.coors, num_points=out.num_points, voxel_num=out.voxel_num,
+                  feats=out.feats, grad_raw=graw).items()}
+    d_out = dict(voxels=out.voxels, coors=out.coors, num_points=out.num_points, voxel_num=out.voxel_num,
+                 feats=out.feats, grad_raw=graw)
+
+    def e2e_step():
+        pts.copy_(h_pts, non_blocking=True)
+        raw.copy_(h_raw, non_blocking=True)
+        step()
+        for k2, v in d_out.items():
+            h_out[k2].copy_(v, non_blocking=True)
+
+    e2e_steps = max(3, min(args.steps, 50))
+    e2e_ms = timed(e2e_step, e2e_steps, min(args.warmup, 3))
+    h2d = h_pts.numel() * 4 + h_raw.numel() * 4
+    d2h = sum(v.numel() * v.element_size() for v in h_out.values())
+
+    # ---- per-kernel durations (CUDA events inside the library, same steps, cold L2, no graph)
+    stages = {}
+    _lib.profile_enable(True)
+    prof_steps = max(3, min(args.steps, 30))
+    for it in range(prof_steps + 2):
+        flush.zero_()
+        ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+        fwd = _lib.profile_read()
+        ops.step_bwd(gfe, out.num_points, out.point2voxel, cfg, raw=raw, bounds=bounds, out=graw)
+        bwd = _lib.profile_read()
+        if it >= 2:
+            for nm, ms in fwd + bwd:
+                stages.setdefault(nm, []).append(ms)
+    _lib.profile_enable(False)
+    stage_us = {k2: round(1e3 * float(np.mean(v)), 3) for k2, v in stages.items()}
+    peak, peak_src = measured_peak_gbs()
+    balg = b_alg_hard(N, C, P, M, K, F)
+    # per-kernel algorithmic bytes (DESIGN.md "kernels"): what that kernel alone must read and write
+    kern_bytes = {
+        "k_cell_hash": 4 * (2 * N * C + N),                       # points + raw in, table entry per point out
+        "k_gather_mean": 4 * (2 * K * C + M * P * C + M + M * F + 2 * K),  # kept rows + raw in; voxels, counts, feats, maps out
+        "k_step_bwd": 4 * (N + N * C + M * F + M + N * C),        # p2v + raw + grad feats + counts in, grad out
+    }
+    dom = max(stage_us, key=stage_us.get) if stage_us else None
+    ms_per_step = tot_ms / args.steps
+    roof = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src, "traffic": None,
+            "stage_us": stage_us,
+            "step": {"b_alg_bytes": balg, "achieved": round(balg / (ms_per_step * 1e-3) / 1e9, 2),
+                     "frac": round(balg / (ms_per_step * 1e-3) / 1e9 / peak, 4)}}
+    if dom is not None:
+        kb = kern_bytes.get(dom, balg)
+        a = kb / (stage_us[dom] * 1e-6) / 1e9
+        roof.update({"achieved": round(a, 2), "frac": round(a / peak, 4), "b_alg_bytes": kb})
+    else:
+        roof.update({"achieved": None, "frac": None})
+
+    if rank == 0:
+        total_pts = N * world
+        line = {
+            "metric": "M points/s perturb+voxelize+VFE fwd/bwd", "value": round(total_pts / (ms_per_step * 1e-3) / 1e6, 2),
+            "unit": "M points/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args.workload, p, B, l2="flushed between steps (512 MiB overwrite outside the "
+                                  "per-step CUDA-event pairs)", cuda_graph=graph is not None, voxels=M, kept_points=K,
+                                  collective=("nccl all_reduce of %d fp32 perturber grads per step" % pgrad.numel())
+                                  if world > 1 else "none"),
+            "clocks": clocks,
+            "e2e": {"value": round(total_pts / (e2e_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                    "ms_per_step": round(e2e_ms / e2e_steps, 5)},
+            "gpu_launches": launches_per_step * args.steps,
+            "roofline": roof,
+        }
+        if world == 1 and not args.no_cpu:
+            line["cpu_baseline"] = cpu_baseline(args.workload, clouds, raws, p)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="kitti", choices=["kitti", "nuscenes"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -72,6 +72,13 @@ typedef struct rpc_perturb_cfg {
 int rpc_abi_version(void);
 const char *rpc_strerror(int status);
 
+/* Per-stage device timing of the MOST RECENT rpc_voxelize_hard / rpc_step_bwd call (bench.py's roofline
+ * leg; no reference counterpart).  While enabled every kernel launch of a call is bracketed by
+ * cudaEvents on the call's stream; do not enable while capturing a CUDA graph.  rpc_profile_read waits
+ * for the call to finish and returns the number of stages, their durations (ms) and kernel names. */
+void rpc_profile_enable(int on);
+int rpc_profile_read(float *ms, const char **names, int max_stages);
+
 /* grid[d] = round((hi-lo)/vs) in fp32, d = x,y,z (mmcv voxelization.cpp) */
 int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3]);
 

@@ -20,6 +20,7 @@ RPC_MAX_CHANNELS = 8
 SYMBOLS = (
     "rpc_abi_version", "rpc_strerror", "rpc_grid_size", "rpc_workspace_bytes", "rpc_voxel_capacity",
     "rpc_voxelize_hard", "rpc_step_bwd", "rpc_voxelize_dynamic", "rpc_vfe_mean_fwd", "rpc_vfe_mean_bwd",
+    "rpc_profile_enable", "rpc_profile_read",
 )
 
 
@@ -87,6 +88,9 @@ def lib() -> ctypes.CDLL:
     L.rpc_voxelize_dynamic.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, i32, vp]
     L.rpc_vfe_mean_fwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
     L.rpc_vfe_mean_bwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
+    L.rpc_profile_enable.restype = None
+    L.rpc_profile_enable.argtypes = [i32]
+    L.rpc_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]
     for name in SYMBOLS:
         getattr(L, name)                      # AttributeError if the .so is stale
     _lib = L
@@ -105,3 +109,17 @@ def check(status: int, where: str) -> None:
 def counts(n_per_sample: Sequence[int]):
     arr = (ctypes.c_int32 * len(n_per_sample))(*[int(n) for n in n_per_sample])
     return arr
+
+
+def profile_enable(on: bool) -> None:
+    lib().rpc_profile_enable(1 if on else 0)
+
+
+def profile_read(max_stages: int = 16):
+    """[(kernel name, ms)] of the most recent profiled call (waits for it to finish)"""
+    ms = (ctypes.c_float * max_stages)()
+    names = (ctypes.c_char_p * max_stages)()
+    n = lib().rpc_profile_read(ms, names, max_stages)
+    if n < 0:
+        raise RpcError(n, "rpc_profile_read")
+    return [(names[k].decode(), float(ms[k])) for k in range(n)]

@@ -114,6 +114,27 @@ void fill_perturb(const rpc_voxel_cfg *cfg, const rpc_perturb_cfg *pc, PerturbDe
         for (int c = 0; c < cfg->C; ++c) { pd->eb[c] = pc->eb[c]; pd->fb[c] = pc->fb[c]; }
 }
 
+// ---- optional per-stage timing (bench.py's roofline leg): cudaEvents recorded around every launch of
+// the most recent call while enabled.  Off by default; never enabled under graph capture.
+constexpr int kMaxStages = 12;
+struct Profiler {
+    bool on = false;
+    int n = 0;                                    // stages recorded by the last call
+    cudaEvent_t ev[kMaxStages + 1] = {};
+    const char *name[kMaxStages] = {};
+    void begin(cudaStream_t st) { if (on) { n = 0; mark(st); } }
+    void mark(cudaStream_t st) {
+        const int k = n;                          // ev[k] closes stage k-1
+        if (!ev[k]) cudaEventCreate(&ev[k]);
+        cudaEventRecord(ev[k], st);
+    }
+    void stage(const char *nm, cudaStream_t st) {
+        if (!on || n >= kMaxStages) return;
+        name[n++] = nm;
+        mark(st);
+    }
+} g_prof;
+
 inline bool misaligned(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
 
 // rows of voxels per CTA in the gather / mean kernels: the [VB,P,C] tile must fit shared memory
@@ -142,16 +163,25 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     const int VB = pick_vb(gd.P, C, &smem);
     if (!VB) return RPC_ERR_CONFIG;
     // keys = kEmpty, first = 0xFFFFFFFF (contiguous)
+    g_prof.begin(st);
     if (cudaMemsetAsync(ws.keys, 0xFF, (pl.o_vid - pl.o_keys), st) != cudaSuccess) return RPC_ERR_CUDA;
+    g_prof.stage("memset_table", st);
     if (nt > 0) {
         if (raw) k_cell_hash<C, true><<<nt, kThreads, 0, st>>>(points, raw, gd, pl.bd, pd, ws, p2v, p2s);
         else     k_cell_hash<C, false><<<nt, kThreads, 0, st>>>(points, raw, gd, pl.bd, pd, ws, p2v, p2s);
+        g_prof.stage("k_cell_hash", st);
         k_count_firsts<<<nt, kThreads, 0, st>>>(pl.bd, ws);
+        g_prof.stage("k_count_firsts", st);
     }
     k_scan_tiles<<<1, kScanThreads, 0, st>>>(pl.bd, ws, gd.V, voxel_num);
+    g_prof.stage("k_scan_tiles", st);
     if (nt > 0 && pl.cap > 0) {
         k_assign_voxels<<<nt, kThreads, 0, st>>>(gd, pl.bd, ws, coors);
-        if (gd.P > 1) k_rank_in_voxel<<<nt, kThreads, 0, st>>>(pl.bd, ws, gd.P);
+        g_prof.stage("k_assign_voxels", st);
+        if (gd.P > 1) {
+            k_rank_in_voxel<<<nt, kThreads, 0, st>>>(pl.bd, ws, gd.P);
+            g_prof.stage("k_rank_in_voxel", st);
+        }
         int64_t blocks = (pl.cap + VB - 1) / VB;
         if (blocks > kNumSM * 8) blocks = kNumSM * 8;
         auto kern = raw ? k_gather_mean<C, true> : k_gather_mean<C, false>;
@@ -160,6 +190,7 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
             return RPC_ERR_CUDA;
         kern<<<(int)blocks, kThreads, smem, st>>>(points, raw, pd, ws, pl.bd.B, gd.P, gd.F, VB, voxels,
                                                   num_points, feats, p2v, p2s);
+        g_prof.stage("k_gather_mean", st);
     }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
@@ -186,6 +217,20 @@ RPC_API const char *rpc_strerror(int status)
         case RPC_ERR_ALIGN: return "pointer not 16-byte aligned";
         default: return "unknown status";
     }
+}
+
+RPC_API void rpc_profile_enable(int on) { g_prof.on = on != 0; g_prof.n = 0; }
+
+RPC_API int rpc_profile_read(float *ms, const char **names, int max_stages)
+{
+    const int n = g_prof.n < max_stages ? g_prof.n : max_stages;
+    if (n <= 0) return 0;
+    if (cudaEventSynchronize(g_prof.ev[g_prof.n]) != cudaSuccess) return RPC_ERR_CUDA;
+    for (int k = 0; k < n; ++k) {
+        if (ms && cudaEventElapsedTime(&ms[k], g_prof.ev[k], g_prof.ev[k + 1]) != cudaSuccess) return RPC_ERR_CUDA;
+        if (names) names[k] = g_prof.name[k];
+    }
+    return n;
 }
 
 RPC_API int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3])
@@ -265,6 +310,7 @@ RPC_API int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats,
     int64_t blocks = (ntotal + kThreads - 1) / kThreads;
     if (blocks > kNumSM * 16) blocks = kNumSM * 16;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    g_prof.begin(s);
     switch (cfg->C) {
 #define RPC_CASE(CC)                                                                               \
     case CC:                                                                                       \
@@ -275,6 +321,7 @@ RPC_API int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats,
 #undef RPC_CASE
         default: return RPC_ERR_CONFIG;
     }
+    g_prof.stage("k_step_bwd", s);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
