@@ -297,7 +297,7 @@ def run_b200(args):
     vn = out.voxel_num.cpu().numpy()
     M = int(vn[-1])
     K = int((out.point2voxel >= 0).sum().item())
-    launches_per_step = 7 + (0 if P > 1 else -1)       # our kernels (the table memset is the driver's)
+    launches_per_step = 2                               # k_hard_fwd (persistent, cooperative) + k_step_bwd
 
     # ---- e2e: pinned host buffers in, every API-visible output back to pinned host buffers
     h_out = {k: torch.empty_like(v, device="cpu").pin_memory() for k, v in
@@ -319,32 +319,36 @@ def run_b200(args):
     d2h = sum(v.numel() * v.element_size() for v in h_out.values())
 
     # ---- per-kernel durations (CUDA events inside the library, same steps, cold L2, no graph)
-    stages = {}
+    stages, phases = {}, {}
     _lib.profile_enable(True)
     prof_steps = max(3, min(args.steps, 30))
     for it in range(prof_steps + 2):
         flush.zero_()
         ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
         fwd = _lib.profile_read()
+        ph = ops.phase_times_us(cfg, n, dev=dev)
         ops.step_bwd(gfe, out.num_points, out.point2voxel, cfg, raw=raw, bounds=bounds, out=graw)
         bwd = _lib.profile_read()
         if it >= 2:
             for nm, ms in fwd + bwd:
                 stages.setdefault(nm, []).append(ms)
+            for nm, us in ph.items():
+                phases.setdefault(nm, []).append(us)
     _lib.profile_enable(False)
     stage_us = {k2: round(1e3 * float(np.mean(v)), 3) for k2, v in stages.items()}
     peak, peak_src = measured_peak_gbs()
     balg = b_alg_hard(N, C, P, M, K, F)
     # per-kernel algorithmic bytes (DESIGN.md "kernels"): what that kernel alone must read and write
     kern_bytes = {
-        "k_cell_hash": 4 * (2 * N * C + N),                       # points + raw in, table entry per point out
-        "k_gather_mean": 4 * (2 * K * C + M * P * C + M + M * F + 2 * K),  # kept rows + raw in; voxels, counts, feats, maps out
-        "k_step_bwd": 4 * (N + N * C + M * F + M + N * C),        # p2v + raw + grad feats + counts in, grad out
+        # forward: points + raw in; voxels, coors(4)+num_points, feats, point2voxel out
+        "k_hard_fwd": 4 * (2 * N * C + M * P * C + 5 * M + M * F + N),
+        # backward: point2voxel + raw + grad feats + counts in, grad_raw out
+        "k_step_bwd": 4 * (N + N * C + M * F + M + N * C),
     }
     dom = max(stage_us, key=stage_us.get) if stage_us else None
     ms_per_step = tot_ms / args.steps
     roof = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src, "traffic": None,
-            "stage_us": stage_us,
+            "stage_us": stage_us, "fwd_phase_us": {k2: round(float(np.mean(v)), 2) for k2, v in phases.items()},
             "step": {"b_alg_bytes": balg, "achieved": round(balg / (ms_per_step * 1e-3) / 1e9, 2),
                      "frac": round(balg / (ms_per_step * 1e-3) / 1e9 / peak, 4)}}
     if dom is not None:

@@ -85,6 +85,10 @@ int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3]);
 /* bytes of scratch rpc_voxelize_hard / rpc_step_fwd / rpc_dynamic_scatter_mean_fwd need for a batch of B sweeps
  * with n_per_sample[b] points each; 0 on invalid arguments */
 size_t rpc_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
+/* byte offset, inside the workspace, of 8 uint64 %globaltimer stamps (ns) that rpc_voxelize_hard writes at
+ * its phase boundaries while profiling is enabled (rpc_profile_enable): start, after clear, insert, flag,
+ * assign, rank, end of CTA 0's gather.  -1 on invalid arguments. */
+int64_t rpc_workspace_stamps_offset(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
 /* rows of the voxel outputs the caller must provide: sum_b min(n_b, V) */
 int64_t rpc_voxel_capacity(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
 

@@ -20,7 +20,7 @@ RPC_MAX_CHANNELS = 8
 SYMBOLS = (
     "rpc_abi_version", "rpc_strerror", "rpc_grid_size", "rpc_workspace_bytes", "rpc_voxel_capacity",
     "rpc_voxelize_hard", "rpc_step_bwd", "rpc_voxelize_dynamic", "rpc_vfe_mean_fwd", "rpc_vfe_mean_bwd",
-    "rpc_profile_enable", "rpc_profile_read",
+    "rpc_profile_enable", "rpc_profile_read", "rpc_workspace_stamps_offset",
 )
 
 
@@ -83,6 +83,8 @@ def lib() -> ctypes.CDLL:
     L.rpc_workspace_bytes.argtypes = [cfgp, i32, i32p]
     L.rpc_voxel_capacity.restype = i64
     L.rpc_voxel_capacity.argtypes = [cfgp, i32, i32p]
+    L.rpc_workspace_stamps_offset.restype = i64
+    L.rpc_workspace_stamps_offset.argtypes = [cfgp, i32, i32p]
     L.rpc_voxelize_hard.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     L.rpc_step_bwd.argtypes = [cfgp, vp, vp, vp, vp, pcp, i64, vp, vp]
     L.rpc_voxelize_dynamic.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, i32, vp]

@@ -6,7 +6,7 @@
 #include "common.cuh"
 #include "dynamic.cuh"
 #include "vfe.cuh"
-#include "voxelize_hard.cuh"
+#include "hard_fwd.cuh"
 
 using namespace rpc;
 
@@ -52,18 +52,32 @@ int make_grid(const rpc_voxel_cfg *cfg, GridDesc *gd)
 struct Plan {                                     // host-side layout of one batched call
     BatchDesc bd;
     int64_t ntotal, ntiles, tab_total, cap;
-    size_t o_keys, o_first, o_vid, o_hslot, o_tiles, o_slots, o_voff, bytes;
+    int T, U;                                     // points per tile = U * kPT
+    size_t o_tab, o_hslot, o_tiles, o_slots, o_stamps, bytes;
 };
 
-int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
+int64_t count_tiles(int B, const int32_t *n, int64_t T)
+{
+    int64_t t = 0;
+    for (int b = 0; b < B; ++b) t += (n[b] + T - 1) / T;
+    return t;
+}
+
+// n_cta: CTAs of the persistent kernel (one per SM).  The tile size is the smallest multiple of kPT
+// that lets every CTA own at most one tile; beyond kUMax*kPT points per CTA the CTAs loop.
+int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, int n_cta, Plan *pl)
 {
     if (!n) return RPC_ERR_NULL;
     if (B < 1 || B > RPC_MAX_BATCH) return RPC_ERR_BATCH;
     memset(pl, 0, sizeof(*pl));
+    for (int b = 0; b < B; ++b)
+        if (n[b] < 0) return RPC_ERR_BATCH;
+    int U = 1;
+    while (U < kUMax && count_tiles(B, n, (int64_t)U * kPT) > n_cta) ++U;
+    pl->U = U; pl->T = U * kPT;
     pl->bd.B = B;
     int64_t pts = 0, tiles = 0, tab = 0, cap = 0;
     for (int b = 0; b < B; ++b) {
-        if (n[b] < 0) return RPC_ERR_BATCH;
         pl->bd.pt_begin[b] = (int)pts;
         pl->bd.tile_begin[b] = (int)tiles;
         int lg = 5;
@@ -73,38 +87,40 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
         pl->bd.tab_shift[b] = 32 - lg;
         tab += int64_t(1) << lg;
         pts += n[b];
-        tiles += (n[b] + kTile - 1) / kTile;
+        tiles += (n[b] + pl->T - 1) / pl->T;
         cap += n[b] < cfg->max_voxels ? n[b] : cfg->max_voxels;
-        if (pts > 0x7FFFFFF0LL || tab > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
+        if (pts > 0x7FFFFFF0LL || tab > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // bit 31 of hslot is a flag
     }
     pl->bd.pt_begin[B] = (int)pts;
     pl->bd.tile_begin[B] = (int)tiles;
     pl->ntotal = pts; pl->ntiles = tiles; pl->tab_total = tab; pl->cap = cap;
     if (cap * (int64_t)cfg->max_points > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
     size_t o = 0;
-    pl->o_keys = o;  o += align_up(4 * (size_t)tab);      // keys and first are contiguous:
-    pl->o_first = o; o += align_up(4 * (size_t)tab);      // one 0xFF fill initialises both
-    pl->o_vid = o;   o += align_up(4 * (size_t)tab);
+    pl->o_tab = o;   o += align_up(8 * (size_t)tab);
     pl->o_hslot = o; o += align_up(4 * (size_t)pts);
-    pl->o_tiles = o; o += align_up(4 * (size_t)(tiles + 1));
+    pl->o_tiles = o; o += align_up(4 * (size_t)(count_tiles(B, n, kPT) + 1));   // bound for any U
     pl->o_slots = o; o += align_up(4 * (size_t)cap * cfg->max_points);
-    pl->o_voff = o;  o += align_up(4 * (size_t)(B + 1));
+    pl->o_stamps = o; o += align_up(8 * 16 * 256);
     pl->bytes = o;
     return RPC_OK;
 }
 
-HardWs carve(const Plan &pl, void *workspace)
+// SM count of the current device (148 on B200); cached per device.  Falls back to 148 when there is
+// no device (the sizing entry points must work on a CPU-only box).
+int device_sms()
 {
-    char *w = static_cast<char *>(workspace);
-    HardWs ws;
-    ws.keys = reinterpret_cast<uint32_t *>(w + pl.o_keys);
-    ws.first = reinterpret_cast<uint32_t *>(w + pl.o_first);
-    ws.vid = reinterpret_cast<int *>(w + pl.o_vid);
-    ws.hslot = reinterpret_cast<int *>(w + pl.o_hslot);
-    ws.tile_count = reinterpret_cast<int *>(w + pl.o_tiles);
-    ws.slots = reinterpret_cast<int *>(w + pl.o_slots);
-    ws.voff = reinterpret_cast<int *>(w + pl.o_voff);
-    return ws;
+    static int cache[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { cudaGetLastError(); return kNumSM; }
+    if (!cache[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) {
+            cudaGetLastError();
+            n = kNumSM;
+        }
+        cache[dev] = n;
+    }
+    return cache[dev];
 }
 
 void fill_perturb(const rpc_voxel_cfg *cfg, const rpc_perturb_cfg *pc, PerturbDesc *pd)
@@ -137,62 +153,59 @@ struct Profiler {
 
 inline bool misaligned(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
 
-// rows of voxels per CTA in the gather / mean kernels: the [VB,P,C] tile must fit shared memory
+// rows of voxels per iteration of the gather phase: one thread per (voxel, slot), multiple of 4 so that
+// every [VB,P,C] tile starts 16-byte aligned in the output
 int pick_vb(int P, int C, size_t *smem)
 {
-    const size_t row = (size_t)P * C * sizeof(float) + sizeof(int);
-    size_t vb = (64 * 1024) / row;
-    if (vb > 64) vb = 64;
-    vb &= ~size_t(3);
-    if (vb < 4) {
-        vb = 4;
-        if (vb * row > 200 * 1024) return 0;
+    int vb = (kPT / P) & ~3;
+    if (vb < 4) vb = 4;
+    const size_t bytes = (size_t)vb * P * C * sizeof(float) + (size_t)vb * sizeof(int);
+    if (bytes > 160 * 1024) return 0;
+    *smem = bytes;
+    return vb;
+}
+
+template <int C, bool PERTURB>
+int launch_hard_t(FwdParams &fp, size_t smem, cudaStream_t st)
+{
+    auto kern = k_hard_fwd<C, PERTURB>;
+    static bool attr_done = false;
+    if (smem > 48 * 1024 && !attr_done) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024) != cudaSuccess)
+            return RPC_ERR_CUDA;
+        attr_done = true;
     }
-    *smem = vb * row;
-    return (int)vb;
+    void *args[] = {&fp};
+    g_prof.begin(st);
+    if (cudaLaunchCooperativeKernel((void *)kern, dim3(device_sms()), dim3(kPT), args, smem, st) != cudaSuccess)
+        return RPC_ERR_CUDA;
+    g_prof.stage("k_hard_fwd", st);
+    return RPC_OK;
 }
 
 template <int C>
 int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const float *points,
                 const float *raw, float *voxels, int32_t *coors, int32_t *num_points,
-                int32_t *voxel_num, int32_t *p2v, int32_t *p2s, float *feats, HardWs ws,
+                int32_t *voxel_num, int32_t *p2v, int32_t *p2s, float *feats, void *workspace,
                 cudaStream_t st)
 {
-    const int nt = (int)pl.ntiles;
+    FwdParams fp;
     size_t smem = 0;
-    const int VB = pick_vb(gd.P, C, &smem);
-    if (!VB) return RPC_ERR_CONFIG;
-    // keys = kEmpty, first = 0xFFFFFFFF (contiguous)
-    g_prof.begin(st);
-    if (cudaMemsetAsync(ws.keys, 0xFF, (pl.o_vid - pl.o_keys), st) != cudaSuccess) return RPC_ERR_CUDA;
-    g_prof.stage("memset_table", st);
-    if (nt > 0) {
-        if (raw) k_cell_hash<C, true><<<nt, kThreads, 0, st>>>(points, raw, gd, pl.bd, pd, ws, p2v, p2s);
-        else     k_cell_hash<C, false><<<nt, kThreads, 0, st>>>(points, raw, gd, pl.bd, pd, ws, p2v, p2s);
-        g_prof.stage("k_cell_hash", st);
-        k_count_firsts<<<nt, kThreads, 0, st>>>(pl.bd, ws);
-        g_prof.stage("k_count_firsts", st);
-    }
-    k_scan_tiles<<<1, kScanThreads, 0, st>>>(pl.bd, ws, gd.V, voxel_num);
-    g_prof.stage("k_scan_tiles", st);
-    if (nt > 0 && pl.cap > 0) {
-        k_assign_voxels<<<nt, kThreads, 0, st>>>(gd, pl.bd, ws, coors);
-        g_prof.stage("k_assign_voxels", st);
-        if (gd.P > 1) {
-            k_rank_in_voxel<<<nt, kThreads, 0, st>>>(pl.bd, ws, gd.P);
-            g_prof.stage("k_rank_in_voxel", st);
-        }
-        int64_t blocks = (pl.cap + VB - 1) / VB;
-        if (blocks > kNumSM * 8) blocks = kNumSM * 8;
-        auto kern = raw ? k_gather_mean<C, true> : k_gather_mean<C, false>;
-        if (smem > 48 * 1024 &&
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
-            return RPC_ERR_CUDA;
-        kern<<<(int)blocks, kThreads, smem, st>>>(points, raw, pd, ws, pl.bd.B, gd.P, gd.F, VB, voxels,
-                                                  num_points, feats, p2v, p2s);
-        g_prof.stage("k_gather_mean", st);
-    }
-    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    fp.VB = pick_vb(gd.P, C, &smem);
+    if (!fp.VB) return RPC_ERR_CONFIG;
+    char *w = static_cast<char *>(workspace);
+    fp.pts = points; fp.raw = raw;
+    fp.tab = reinterpret_cast<unsigned long long *>(w + pl.o_tab);
+    fp.hslot = reinterpret_cast<uint32_t *>(w + pl.o_hslot);
+    fp.tile_cnt = reinterpret_cast<int *>(w + pl.o_tiles);
+    fp.slots = reinterpret_cast<int *>(w + pl.o_slots);
+    fp.stamps = g_prof.on ? reinterpret_cast<unsigned long long *>(w + pl.o_stamps) : nullptr;
+    fp.voxels = voxels; fp.coors = coors; fp.num_points = num_points; fp.voxel_num = voxel_num;
+    fp.p2v = p2v; fp.p2s = p2s; fp.feats = feats;
+    fp.tab_total = pl.tab_total;
+    fp.ntiles = (int)pl.ntiles; fp.T = pl.T; fp.U = pl.U;
+    fp.gd = gd; fp.bd = pl.bd; fp.pd = pd;
+    return raw ? launch_hard_t<C, true>(fp, smem, st) : launch_hard_t<C, false>(fp, smem, st);
 }
 
 }  // namespace
@@ -248,14 +261,21 @@ RPC_API int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3])
 RPC_API size_t rpc_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
 {
     Plan pl;
-    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return 0;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, kNumSM, &pl)) return 0;
     return pl.bytes;
+}
+
+RPC_API int64_t rpc_workspace_stamps_offset(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
+{
+    Plan pl;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, kNumSM, &pl)) return -1;
+    return (int64_t)pl.o_stamps;
 }
 
 RPC_API int64_t rpc_voxel_capacity(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
 {
     Plan pl;
-    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return -1;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, kNumSM, &pl)) return -1;
     return pl.cap;
 }
 
@@ -271,7 +291,7 @@ RPC_API int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points,
     GridDesc gd;
     if ((st = make_grid(cfg, &gd))) return st;
     Plan pl;
-    if ((st = make_plan(cfg, B, n_per_sample, &pl))) return st;
+    if ((st = make_plan(cfg, B, n_per_sample, device_sms(), &pl))) return st;
     if (!voxel_num || !workspace) return RPC_ERR_NULL;
     if (pl.ntotal > 0 && !points) return RPC_ERR_NULL;
     if (pl.cap > 0 && (!voxels || !coors || !num_points)) return RPC_ERR_NULL;
@@ -282,12 +302,11 @@ RPC_API int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points,
         return RPC_ERR_ALIGN;
     PerturbDesc pd;
     fill_perturb(cfg, pc, &pd);
-    HardWs ws = carve(pl, workspace);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     switch (cfg->C) {
 #define RPC_CASE(CC)                                                                              \
     case CC: return launch_hard<CC>(gd, pl, pd, points, raw, voxels, coors, num_points, voxel_num, \
-                                    point2voxel, point2slot, feats, ws, s);
+                                    point2voxel, point2slot, feats, workspace, s);
         RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
 #undef RPC_CASE
     }
@@ -370,7 +389,7 @@ RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
     rpc_voxel_cfg c2 = *cfg;
     c2.max_points = 1; c2.max_voxels = 1;
     Plan pl;
-    if ((st = make_plan(&c2, B, n_per_sample, &pl))) return st;
+    if ((st = make_plan(&c2, B, n_per_sample, kNumSM, &pl))) return st;
     if (pl.ntotal == 0) return RPC_OK;
     if (!points || !coors) return RPC_ERR_NULL;
     if (raw && !pc) return RPC_ERR_NULL;
@@ -378,7 +397,9 @@ RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
     PerturbDesc pd;
     fill_perturb(cfg, pc, &pd);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const int nt = (int)pl.ntiles;
+    int64_t nblk = (pl.ntotal + kThreads - 1) / kThreads;
+    if (nblk > kNumSM * 16) nblk = kNumSM * 16;
+    const int nt = (int)nblk;
 #define RPC_LAUNCH(CC, PP, NC) \
     k_dynamic_voxelize<CC, PP, NC><<<nt, kThreads, 0, s>>>(points, raw, gd, pl.bd, pd, coors)
 #define RPC_CASE(CC)                                                              \

@@ -12,8 +12,7 @@
 
 namespace rpc {
 
-constexpr int kTile = 1024;          // points per tile (one CTA)
-constexpr int kThreads = 256;        // threads per CTA of the per-point kernels
+constexpr int kThreads = 256;        // threads per CTA of the streaming kernels
 constexpr uint32_t kEmpty = 0xFFFFFFFFu;
 constexpr int kInf = 0x7FFFFFFF;     // "no point" in the per-voxel slot lists
 

@@ -186,3 +186,19 @@ def vfe_mean_bwd(grad_out: torch.Tensor, num_points: torch.Tensor, P: int, C: in
                                      _stream(dev))
     _lib.check(st, "rpc_vfe_mean_bwd")
     return g
+
+
+PHASES = ("clear", "insert", "flag", "assign", "rank", "gather")
+
+
+def phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Optional[torch.Tensor] = None,
+                   dev: Optional[torch.device] = None):
+    """{phase: us} of the most recent profiled ``hard_voxelize`` call (``_lib.profile_enable(True)``),
+    from the %globaltimer stamps CTA 0 of the persistent kernel leaves in the workspace (host sync)."""
+    n_arr = _lib.counts(n_per_sample)
+    off = _lib.lib().rpc_workspace_stamps_offset(ctypes.byref(cfg), len(n_per_sample), n_arr)
+    if off < 0:
+        raise _lib.RpcError(-2, "rpc_workspace_stamps_offset")
+    ws = workspace if workspace is not None else _default_ws._buf[dev]
+    st = ws[off:off + 56].view(torch.int64).cpu().tolist()
+    return {PHASES[k]: (st[k + 1] - st[k]) / 1e3 for k in range(6)}
