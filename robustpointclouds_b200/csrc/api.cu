@@ -52,45 +52,34 @@ int make_grid(const rpc_voxel_cfg *cfg, GridDesc *gd)
 struct Plan {                                     // host-side layout of one batched call
     BatchDesc bd;
     int64_t ntotal, ntiles, tab_total, cap;
-    int T, U;                                     // points per tile = U * kPT
     size_t o_tab, o_hslot, o_tiles, o_slots, o_stamps, bytes;
 };
 
-int64_t count_tiles(int B, const int32_t *n, int64_t T)
-{
-    int64_t t = 0;
-    for (int b = 0; b < B; ++b) t += (n[b] + T - 1) / T;
-    return t;
-}
-
-// n_cta: CTAs of the persistent kernel (one per SM).  The tile size is the smallest multiple of kPT
-// that lets every CTA own at most one tile; beyond kUMax*kPT points per CTA the CTAs loop.
-int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, int n_cta, Plan *pl)
+// Tiles are kPT consecutive points of one sweep; tables hold 1.5 entries per point (worst-case load
+// 0.67 when every point is its own cell; ~0.3 on LiDAR sweeps).
+int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
 {
     if (!n) return RPC_ERR_NULL;
     if (B < 1 || B > RPC_MAX_BATCH) return RPC_ERR_BATCH;
     memset(pl, 0, sizeof(*pl));
-    for (int b = 0; b < B; ++b)
-        if (n[b] < 0) return RPC_ERR_BATCH;
-    int U = 1;
-    while (U < kUMax && count_tiles(B, n, (int64_t)U * kPT) > n_cta) ++U;
-    pl->U = U; pl->T = U * kPT;
     pl->bd.B = B;
     int64_t pts = 0, tiles = 0, tab = 0, cap = 0;
     for (int b = 0; b < B; ++b) {
+        if (n[b] < 0) return RPC_ERR_BATCH;
         pl->bd.pt_begin[b] = (int)pts;
         pl->bd.tile_begin[b] = (int)tiles;
-        int lg = 5;
-        while ((int64_t(1) << lg) < 2 * (int64_t)n[b]) ++lg;
+        int64_t sz = ((int64_t)n[b] * 3 + 1) / 2;
+        if (sz < 64) sz = 64;
+        sz = (sz + 3) & ~int64_t(3);                            // buckets of 4 entries (32 bytes)
         pl->bd.tab_off[b] = (uint32_t)tab;
-        pl->bd.tab_mask[b] = (uint32_t)((int64_t(1) << lg) - 1);
-        pl->bd.tab_shift[b] = 32 - lg;
-        tab += int64_t(1) << lg;
+        pl->bd.tab_size[b] = (uint32_t)sz;
+        tab += sz;
         pts += n[b];
-        tiles += (n[b] + pl->T - 1) / pl->T;
+        tiles += (n[b] + kPT - 1) / kPT;
         cap += n[b] < cfg->max_voxels ? n[b] : cfg->max_voxels;
-        if (pts > 0x7FFFFFF0LL || tab > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // bit 31 of hslot is a flag
+        if (pts > 0x3FFFFFF0LL || tab > 0x3FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // bits 30, 31 of hslot are flags
     }
+    if (tiles > kMaxTiles) return RPC_ERR_TOO_LARGE;
     pl->bd.pt_begin[B] = (int)pts;
     pl->bd.tile_begin[B] = (int)tiles;
     pl->ntotal = pts; pl->ntiles = tiles; pl->tab_total = tab; pl->cap = cap;
@@ -98,9 +87,9 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, int n_cta, Plan
     size_t o = 0;
     pl->o_tab = o;   o += align_up(8 * (size_t)tab);
     pl->o_hslot = o; o += align_up(4 * (size_t)pts);
-    pl->o_tiles = o; o += align_up(4 * (size_t)(count_tiles(B, n, kPT) + 1));   // bound for any U
+    pl->o_tiles = o; o += align_up(4 * (size_t)(tiles + 1));
     pl->o_slots = o; o += align_up(4 * (size_t)cap * cfg->max_points);
-    pl->o_stamps = o; o += align_up(8 * 16 * 256);
+    pl->o_stamps = o; o += align_up(8 * 16 * 1024);
     pl->bytes = o;
     return RPC_OK;
 }
@@ -153,31 +142,39 @@ struct Profiler {
 
 inline bool misaligned(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
 
-// rows of voxels per iteration of the gather phase: one thread per (voxel, slot), multiple of 4 so that
-// every [VB,P,C] tile starts 16-byte aligned in the output
-int pick_vb(int P, int C, size_t *smem)
+// rows of voxels per iteration of the gather phase: at most kGatherSlots (voxel, slot) pairs, spread
+// over the CTAs when the batch is small, multiple of 4 so that every tile starts 16-byte aligned
+int pick_vb(int P, int C, int64_t cap, int n_cta, size_t *smem)
 {
-    int vb = (kPT / P) & ~3;
+    int64_t vb = (cap + n_cta - 1) / n_cta;
+    if (vb > kGatherSlots / P) vb = kGatherSlots / P;
+    vb = (vb + 3) & ~int64_t(3);
+    if (vb > kPT) vb = kPT;                                       // one thread per voxel for the counts
     if (vb < 4) vb = 4;
-    const size_t bytes = (size_t)vb * P * C * sizeof(float) + (size_t)vb * sizeof(int);
-    if (bytes > 160 * 1024) return 0;
+    if (vb * P > 65535) return 0;                                 // kept-row list is 16 bit
+    // slot indices, tile, counts, prefix, kept-row list
+    const size_t bytes = (size_t)vb * P * sizeof(int) + (size_t)vb * P * C * sizeof(float) +
+                         2 * (size_t)vb * sizeof(int) + (size_t)vb * P * sizeof(unsigned short) + 16;
+    if (bytes > 200 * 1024 / kCtasPerSM) return 0;
     *smem = bytes;
-    return vb;
+    return (int)vb;
 }
 
 template <int C, bool PERTURB>
 int launch_hard_t(FwdParams &fp, size_t smem, cudaStream_t st)
 {
     auto kern = k_hard_fwd<C, PERTURB>;
-    static bool attr_done = false;
-    if (smem > 48 * 1024 && !attr_done) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024) != cudaSuccess)
+    static bool attr_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess)
             return RPC_ERR_CUDA;
-        attr_done = true;
+        attr_done[dev] = true;
     }
     void *args[] = {&fp};
     g_prof.begin(st);
-    if (cudaLaunchCooperativeKernel((void *)kern, dim3(device_sms()), dim3(kPT), args, smem, st) != cudaSuccess)
+    if (cudaLaunchCooperativeKernel((void *)kern, dim3(device_sms() * kCtasPerSM), dim3(kPT), args, smem, st) != cudaSuccess)
         return RPC_ERR_CUDA;
     g_prof.stage("k_hard_fwd", st);
     return RPC_OK;
@@ -191,8 +188,10 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
 {
     FwdParams fp;
     size_t smem = 0;
-    fp.VB = pick_vb(gd.P, C, &smem);
+    fp.VB = pick_vb(gd.P, C, pl.cap, device_sms() * kCtasPerSM, &smem);
     if (!fp.VB) return RPC_ERR_CONFIG;
+    const size_t scan_bytes = 4 * (size_t)(pl.ntiles + 1);          // P3's prefix array shares the buffer
+    if (smem < scan_bytes) smem = scan_bytes;
     char *w = static_cast<char *>(workspace);
     fp.pts = points; fp.raw = raw;
     fp.tab = reinterpret_cast<unsigned long long *>(w + pl.o_tab);
@@ -203,7 +202,7 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     fp.voxels = voxels; fp.coors = coors; fp.num_points = num_points; fp.voxel_num = voxel_num;
     fp.p2v = p2v; fp.p2s = p2s; fp.feats = feats;
     fp.tab_total = pl.tab_total;
-    fp.ntiles = (int)pl.ntiles; fp.T = pl.T; fp.U = pl.U;
+    fp.ntiles = (int)pl.ntiles;
     fp.gd = gd; fp.bd = pl.bd; fp.pd = pd;
     return raw ? launch_hard_t<C, true>(fp, smem, st) : launch_hard_t<C, false>(fp, smem, st);
 }
@@ -261,21 +260,21 @@ RPC_API int rpc_grid_size(const rpc_voxel_cfg *cfg, int32_t grid[3])
 RPC_API size_t rpc_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
 {
     Plan pl;
-    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, kNumSM, &pl)) return 0;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return 0;
     return pl.bytes;
 }
 
 RPC_API int64_t rpc_workspace_stamps_offset(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
 {
     Plan pl;
-    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, kNumSM, &pl)) return -1;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return -1;
     return (int64_t)pl.o_stamps;
 }
 
 RPC_API int64_t rpc_voxel_capacity(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
 {
     Plan pl;
-    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, kNumSM, &pl)) return -1;
+    if (check_cfg(cfg, true) || make_plan(cfg, B, n_per_sample, &pl)) return -1;
     return pl.cap;
 }
 
@@ -291,7 +290,7 @@ RPC_API int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points,
     GridDesc gd;
     if ((st = make_grid(cfg, &gd))) return st;
     Plan pl;
-    if ((st = make_plan(cfg, B, n_per_sample, device_sms(), &pl))) return st;
+    if ((st = make_plan(cfg, B, n_per_sample, &pl))) return st;
     if (!voxel_num || !workspace) return RPC_ERR_NULL;
     if (pl.ntotal > 0 && !points) return RPC_ERR_NULL;
     if (pl.cap > 0 && (!voxels || !coors || !num_points)) return RPC_ERR_NULL;
@@ -351,9 +350,12 @@ RPC_API int rpc_vfe_mean_fwd(const float *voxels, const int32_t *num_points, int
     if (M == 0) return RPC_OK;
     if (!voxels || !num_points || !out) return RPC_ERR_NULL;
     if (misaligned(voxels)) return RPC_ERR_ALIGN;
-    size_t smem = 0;
-    const int VB = pick_vb(P, C, &smem);
-    if (!VB) return RPC_ERR_CONFIG;
+    // voxel rows per CTA iteration: the [VB,P,C] tile is staged in shared memory (<= 32 KB)
+    int VB = (int)((32 * 1024) / ((size_t)P * C * sizeof(float))) & ~3;
+    if (VB > 64) VB = 64;
+    if (VB < 4) VB = 4;
+    const size_t smem = (size_t)VB * P * C * sizeof(float);
+    if (smem > 200 * 1024) return RPC_ERR_CONFIG;
     if (smem > 48 * 1024 &&
         cudaFuncSetAttribute(k_vfe_mean_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
         return RPC_ERR_CUDA;
@@ -389,7 +391,7 @@ RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
     rpc_voxel_cfg c2 = *cfg;
     c2.max_points = 1; c2.max_voxels = 1;
     Plan pl;
-    if ((st = make_plan(&c2, B, n_per_sample, kNumSM, &pl))) return st;
+    if ((st = make_plan(&c2, B, n_per_sample, &pl))) return st;
     if (pl.ntotal == 0) return RPC_OK;
     if (!points || !coors) return RPC_ERR_NULL;
     if (raw && !pc) return RPC_ERR_NULL;

@@ -32,8 +32,7 @@ struct BatchDesc {
     int pt_begin[RPC_MAX_BATCH + 1];
     int tile_begin[RPC_MAX_BATCH + 1];
     uint32_t tab_off[RPC_MAX_BATCH];   // first entry of the sweep's hash sub-table
-    uint32_t tab_mask[RPC_MAX_BATCH];  // entries - 1 (power of two)
-    int tab_shift[RPC_MAX_BATCH];      // 32 - log2(entries)
+    uint32_t tab_size[RPC_MAX_BATCH];  // its entries (even, >= 1.5 x points of the sweep)
 };
 
 struct PerturbDesc {
@@ -84,11 +83,6 @@ __device__ __forceinline__ int point_cell(float x, float y, float z, const GridD
     int cz = axis_cell(z, gd.lo[2], gd.vs[2], gd.gf[2]);
     if ((cx | cy | cz) < 0) return -1;
     return (cz * gd.g[1] + cy) * gd.g[0] + cx;
-}
-
-__device__ __forceinline__ uint32_t hash_cell(uint32_t cell, int shift)
-{
-    return (cell * 0x9E3779B1u) >> shift;
 }
 
 // warp / block exclusive scan of small integers (kThreads threads)
