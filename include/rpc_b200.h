@@ -20,12 +20,12 @@
  *   rpc_vfe_mean_fwd/bwd   mmdet3d `HardSimpleVFE.forward` and its autograd, called at
  *                          adversarial_voxelnet.py:135-137, adversarial_centerpoint.py:100-102
  *   rpc_valid_rows         the padding mask + boolean gather of adversarial_voxelnet.py:86-90
- *   rpc_perturb_rows_fwd/bwd   VoxelPerturber's scale/clamp/add tail
+ *   rpc_scatter_rows / rpc_gather_rows   the masked scatter-back (adversarial_voxelnet.py:113-117) and its
+ *                          autograd
+ *   rpc_perturb_apply_fwd/bwd   VoxelPerturber's scale/clamp/add tail
  *                          (/root/reference/models/adversarial/voxel_perturber.py:256,357-365,285)
- *                          fused with the masked scatter-back (adversarial_voxelnet.py:113-117) and
- *                          the VFE mean: the reference-order composition
- *   rpc_step_fwd/bwd       the north-star order: perturb -> hard voxelize -> VFE mean, and the
- *                          gradient back to the raw per-point perturbation
+ *   rpc_voxelize_hard (raw != NULL) + rpc_step_bwd   the north-star order: perturb -> hard voxelize ->
+ *                          VFE mean, and the gradient back to the raw per-point perturbation
  *   rpc_dynamic_scatter_mean_fwd/bwd   mmcv DynamicScatter(mean) for the dynamic configuration
  */
 #ifndef RPC_B200_H_
@@ -143,6 +143,42 @@ int rpc_vfe_mean_fwd(const float *voxels, const int32_t *num_points, int64_t M, 
 /* its autograd: grad_voxels[m, k, c] = grad_out[m, c] / num_points[m] (every slot), 0 for c >= F */
 int rpc_vfe_mean_bwd(const float *grad_out, const int32_t *num_points, int64_t M, int P, int C, int F,
                      const int32_t *m_dev, float *grad_voxels, void *stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Reference-order composition: voxelize first (no perturbation), then perturb the kept points inside the
+ * padded voxel tensor, as AdversarialVoxelNet.extract_feat / AdversarialCenterPoint.extract_pts_feat do.
+ * ------------------------------------------------------------------------------------------------- */
+
+/* scratch of rpc_valid_rows for an [M,P,*] tensor */
+size_t rpc_valid_rows_workspace_bytes(int64_t M, int P);
+
+/* extract_feat's padding mask + boolean gather (adversarial_voxelnet.py:86-90, adversarial_centerpoint.py:
+ * 73-77) on the [M*P, C] view of `voxels`:  mode 0 'rowsum': valid = fp32 row sum != 0 (the reference's
+ * rule, which also drops real points whose features sum to 0); mode 1 'count': valid = slot < num_points.
+ *   row_idx [M*P] i32   k-th valid row, ascending (first count[0] entries defined)
+ *   row2k   [M*P] i32   k of each row or -1                     (may be NULL)
+ *   rows_out[M*P, C]    the valid rows themselves = voxels_2d[valid_mask]   (may be NULL)
+ *   count   [1]   i32   K', on the device (no host sync)
+ * m_dev as in rpc_vfe_mean_fwd. */
+int rpc_valid_rows(const float *voxels, const int32_t *num_points, int64_t M, int P, int C, int mode,
+                   const int32_t *m_dev, int32_t *row_idx, int32_t *row2k, float *rows_out, int32_t *count,
+                   void *workspace, size_t workspace_bytes, void *stream);
+
+/* the gradient-connected copy + masked scatter-back (adversarial_voxelnet.py:113-117):
+ * out = voxels; out_2d[row_idx[k]] = rows[k]  (through row2k) */
+int rpc_scatter_rows(const float *voxels, const int32_t *row2k, const float *rows, int64_t M, int P, int C,
+                     float *out, void *stream);
+/* out[k, :] = src_2d[row_idx[k], :], k < min(K, *k_dev): the boolean gather, and the autograd of the scatter */
+int rpc_gather_rows(const float *src, const int32_t *row_idx, int64_t K, const int32_t *k_dev, int C,
+                    float *out, void *stream);
+
+/* VoxelPerturber's elementwise tail (voxel_perturber.py:256, 357-365, 285):
+ *   p = nan_to_num(clamp(raw * eb[c], -fb[c], +fb[c]));  y = x + p      (p_out may be NULL) */
+int rpc_perturb_apply_fwd(const float *x, const float *raw, const rpc_perturb_cfg *pc /*[host]*/, int64_t K,
+                          const int32_t *k_dev, int C, float *y, float *p_out, void *stream);
+/* its autograd: grad_raw = (-fb <= raw*eb <= fb) ? grad_p * eb : 0 */
+int rpc_perturb_apply_bwd(const float *grad_p, const float *raw, const rpc_perturb_cfg *pc /*[host]*/,
+                          int64_t K, const int32_t *k_dev, int C, float *grad_raw, void *stream);
 
 #ifdef __cplusplus
 }

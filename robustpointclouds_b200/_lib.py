@@ -21,6 +21,8 @@ SYMBOLS = (
     "rpc_abi_version", "rpc_strerror", "rpc_grid_size", "rpc_workspace_bytes", "rpc_voxel_capacity",
     "rpc_voxelize_hard", "rpc_step_bwd", "rpc_voxelize_dynamic", "rpc_vfe_mean_fwd", "rpc_vfe_mean_bwd",
     "rpc_profile_enable", "rpc_profile_read", "rpc_workspace_stamps_offset",
+    "rpc_valid_rows_workspace_bytes", "rpc_valid_rows", "rpc_scatter_rows", "rpc_gather_rows",
+    "rpc_perturb_apply_fwd", "rpc_perturb_apply_bwd",
 )
 
 
@@ -90,6 +92,13 @@ def lib() -> ctypes.CDLL:
     L.rpc_voxelize_dynamic.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, i32, vp]
     L.rpc_vfe_mean_fwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
     L.rpc_vfe_mean_bwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
+    L.rpc_valid_rows_workspace_bytes.restype = sz
+    L.rpc_valid_rows_workspace_bytes.argtypes = [i64, i32]
+    L.rpc_valid_rows.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp, vp, vp, vp, sz, vp]
+    L.rpc_scatter_rows.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp]
+    L.rpc_gather_rows.argtypes = [vp, vp, i64, vp, i32, vp, vp]
+    L.rpc_perturb_apply_fwd.argtypes = [vp, vp, pcp, i64, vp, i32, vp, vp, vp]
+    L.rpc_perturb_apply_bwd.argtypes = [vp, vp, pcp, i64, vp, i32, vp, vp]
     L.rpc_profile_enable.restype = None
     L.rpc_profile_enable.argtypes = [i32]
     L.rpc_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]

@@ -7,6 +7,7 @@
 #include "dynamic.cuh"
 #include "vfe.cuh"
 #include "hard_fwd.cuh"
+#include "rows.cuh"
 
 using namespace rpc;
 
@@ -415,6 +416,99 @@ RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
     }
 #undef RPC_CASE
 #undef RPC_LAUNCH
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+// ------------------------------------------------------------------ reference-order composition
+RPC_API size_t rpc_valid_rows_workspace_bytes(int64_t M, int P)
+{
+    if (M < 0 || P < 1) return 0;
+    return align_up(4 * (size_t)((M * P + kRowTile - 1) / kRowTile + 1));
+}
+
+RPC_API int rpc_valid_rows(const float *voxels, const int32_t *num_points, int64_t M, int P, int C, int mode,
+                           const int32_t *m_dev, int32_t *row_idx, int32_t *row2k, float *rows_out,
+                           int32_t *count, void *workspace, size_t workspace_bytes, void *stream)
+{
+    if (P < 1 || C < 1 || M < 0 || (mode != 0 && mode != 1)) return RPC_ERR_CONFIG;
+    if (!count) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (M == 0) return cudaMemsetAsync(count, 0, 4, st) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    if (!voxels || !num_points || !row_idx || !workspace) return RPC_ERR_NULL;
+    const int64_t R = M * P;
+    if (R > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
+    int ntiles = (int)((R + kRowTile - 1) / kRowTile);
+    if (ntiles > kMaxTiles) return RPC_ERR_TOO_LARGE;
+    if (workspace_bytes < rpc_valid_rows_workspace_bytes(M, P)) return RPC_ERR_WORKSPACE;
+    int *tile_cnt = static_cast<int *>(workspace);
+    size_t smem = 4 * (size_t)(ntiles + 1);
+    static bool attr_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        if (cudaFuncSetAttribute(k_valid_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * (kMaxTiles + 1)) != cudaSuccess)
+            return RPC_ERR_CUDA;
+        attr_done[dev] = true;
+    }
+    int grid = device_sms();
+    if (grid > ntiles) grid = ntiles;
+    void *args[] = {&voxels, &num_points, &M, &m_dev, &P, &C, &mode, &ntiles, &tile_cnt, &row_idx, &row2k, &rows_out, &count};
+    if (cudaLaunchCooperativeKernel((void *)k_valid_rows, dim3(grid), dim3(kRowTile), args, smem, st) != cudaSuccess)
+        return RPC_ERR_CUDA;
+    return RPC_OK;
+}
+
+static inline int stream_blocks(int64_t total)
+{
+    int64_t b = (total + kThreads - 1) / kThreads;
+    if (b > kNumSM * 16) b = kNumSM * 16;
+    return (int)(b < 1 ? 1 : b);
+}
+
+RPC_API int rpc_scatter_rows(const float *voxels, const int32_t *row2k, const float *rows, int64_t M, int P,
+                             int C, float *out, void *stream)
+{
+    if (P < 1 || C < 1 || M < 0) return RPC_ERR_CONFIG;
+    if (M == 0) return RPC_OK;
+    if (!voxels || !row2k || !rows || !out) return RPC_ERR_NULL;
+    k_scatter_rows<<<stream_blocks(M * P * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+        voxels, row2k, rows, M * P, C, out);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_gather_rows(const float *src, const int32_t *row_idx, int64_t K, const int32_t *k_dev, int C,
+                            float *out, void *stream)
+{
+    if (C < 1 || K < 0) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!src || !row_idx || !out) return RPC_ERR_NULL;
+    k_gather_rows<<<stream_blocks(K * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(src, row_idx, K, k_dev, C, out);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_perturb_apply_fwd(const float *x, const float *raw, const rpc_perturb_cfg *pc, int64_t K,
+                                  const int32_t *k_dev, int C, float *y, float *p_out, void *stream)
+{
+    if (C < 1 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!x || !raw || !pc || !y) return RPC_ERR_NULL;
+    PerturbDesc pd;
+    memset(&pd, 0, sizeof(pd));
+    for (int c = 0; c < C; ++c) { pd.eb[c] = pc->eb[c]; pd.fb[c] = pc->fb[c]; }
+    k_perturb_apply_fwd<<<stream_blocks(K * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(x, raw, pd, K, k_dev, C, y, p_out);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_perturb_apply_bwd(const float *grad_p, const float *raw, const rpc_perturb_cfg *pc, int64_t K,
+                                  const int32_t *k_dev, int C, float *grad_raw, void *stream)
+{
+    if (C < 1 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!grad_p || !raw || !pc || !grad_raw) return RPC_ERR_NULL;
+    PerturbDesc pd;
+    memset(&pd, 0, sizeof(pd));
+    for (int c = 0; c < C; ++c) { pd.eb[c] = pc->eb[c]; pd.fb[c] = pc->fb[c]; }
+    k_perturb_apply_bwd<<<stream_blocks(K * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(grad_p, raw, pd, K, k_dev, C, grad_raw);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 

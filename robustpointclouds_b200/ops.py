@@ -202,3 +202,84 @@ def phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Option
     ws = workspace if workspace is not None else _default_ws._buf[dev]
     st = ws[off:off + 56].view(torch.int64).cpu().tolist()
     return {PHASES[k]: (st[k + 1] - st[k]) / 1e3 for k in range(6)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference-order composition (perturb the kept points inside the padded voxel tensor)
+# ------------------------------------------------------------------------------------------------
+MASK_MODES = {"rowsum": 0, "count": 1}
+
+
+@dataclass
+class ValidRows:
+    """``rpc_valid_rows`` outputs, sized for all M*P rows; the first ``count`` entries are defined."""
+    row_idx: torch.Tensor          # [M*P] i32
+    row2k: torch.Tensor            # [M*P] i32
+    rows: torch.Tensor             # [M*P, C] f32
+    count: torch.Tensor            # [1] i32 on the device
+
+    def k(self) -> int:
+        return int(self.count.item())   # host sync (the reference's boolean index syncs here too)
+
+
+def valid_rows(voxels: torch.Tensor, num_points: torch.Tensor, mask_mode: str = "rowsum",
+               m_dev: Optional[torch.Tensor] = None) -> ValidRows:
+    dev = _need_cuda(voxels, num_points)
+    voxels = _f32c(voxels)
+    num_points = num_points.to(torch.int32).contiguous()
+    M, P, C = voxels.shape
+    L = _lib.lib()
+    R = M * P
+    i32 = dict(dtype=torch.int32, device=dev)
+    out = ValidRows(torch.empty((R,), **i32), torch.empty((R,), **i32),
+                    torch.empty((R, C), dtype=torch.float32, device=dev), torch.zeros((1,), **i32))
+    nbytes = L.rpc_valid_rows_workspace_bytes(M, P)
+    ws = _default_ws.get(nbytes, dev)
+    st = L.rpc_valid_rows(_ptr(voxels), _ptr(num_points), M, P, C, MASK_MODES[mask_mode], _ptr(m_dev),
+                          _ptr(out.row_idx), _ptr(out.row2k), _ptr(out.rows), _ptr(out.count),
+                          ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(st, "rpc_valid_rows")
+    return out
+
+
+def scatter_rows(voxels: torch.Tensor, row2k: torch.Tensor, rows: torch.Tensor) -> torch.Tensor:
+    dev = _need_cuda(voxels, row2k, rows)
+    voxels, rows = _f32c(voxels), _f32c(rows)
+    M, P, C = voxels.shape
+    out = torch.empty_like(voxels)
+    st = _lib.lib().rpc_scatter_rows(_ptr(voxels), _ptr(row2k), _ptr(rows), M, P, C, _ptr(out), _stream(dev))
+    _lib.check(st, "rpc_scatter_rows")
+    return out
+
+
+def gather_rows(src: torch.Tensor, row_idx: torch.Tensor, K: int, C: int,
+                k_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    dev = _need_cuda(src, row_idx)
+    src = _f32c(src)
+    out = torch.empty((K, C), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_gather_rows(_ptr(src), _ptr(row_idx), K, _ptr(k_dev), C, _ptr(out), _stream(dev))
+    _lib.check(st, "rpc_gather_rows")
+    return out
+
+
+def perturb_apply_fwd(x: torch.Tensor, raw: torch.Tensor, bounds: PerturbCfg, want_p: bool = True):
+    dev = _need_cuda(x, raw)
+    x, raw = _f32c(x), _f32c(raw)
+    K, C = x.shape
+    y = torch.empty_like(x)
+    p = torch.empty_like(x) if want_p else None
+    st = _lib.lib().rpc_perturb_apply_fwd(_ptr(x), _ptr(raw), ctypes.byref(bounds), K, None, C, _ptr(y), _ptr(p),
+                                          _stream(dev))
+    _lib.check(st, "rpc_perturb_apply_fwd")
+    return y, p
+
+
+def perturb_apply_bwd(grad_p: torch.Tensor, raw: torch.Tensor, bounds: PerturbCfg) -> torch.Tensor:
+    dev = _need_cuda(grad_p, raw)
+    grad_p, raw = _f32c(grad_p), _f32c(raw)
+    K, C = raw.shape
+    g = torch.empty_like(raw)
+    st = _lib.lib().rpc_perturb_apply_bwd(_ptr(grad_p), _ptr(raw), ctypes.byref(bounds), K, None, C, _ptr(g),
+                                          _stream(dev))
+    _lib.check(st, "rpc_perturb_apply_bwd")
+    return g

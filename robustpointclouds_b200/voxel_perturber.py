@@ -1,0 +1,276 @@
+"""``VoxelPerturber`` with the reference's API (/root/reference/models/adversarial/voxel_perturber.py:20-541)
+on top of the sm_100a kernels.
+
+What stays in PyTorch: the small MLP / attention (cuBLAS GEMMs) and the four loss
+scalars.  What runs in the hand-written kernels: the elementwise tail ``p = nan_to_num(clamp(raw * eb,
+-fb, +fb)); y = x + p`` and its autograd (``rpc_perturb_apply_fwd/bwd``), and -- in the fused north-star
+order -- the whole perturb + voxelize + VFE step (``adversarial_step.py``).
+
+Kept from the reference, on purpose: constructor signature and defaults (:36-40); lazy build of ``model`` /
+``attention`` on the first forward (:74-118, :142-147); per-channel scale ``eb`` and clamp ``fb`` tables
+that depend on C and on ``self.training`` (:209-256, :333-359); the return value ``(perturbed, dict(l2_norm,
+intensity_loss, bias_loss, imbalance_loss))`` (:312-321) and the fall-back ``(x, tensor(0.))`` on NaN
+(:150-153, :189-200, :259-262); metric lists and ``save_l2_norms`` (:388-432); weight init and the
+parameter-gradient hook ``nan_to_num`` + ``clamp(+-0.1)`` (:434-475); ``_reset_problematic_weights``
+(:477-497).  Dropped: debug prints.
+"""
+from __future__ import annotations
+
+import csv
+from typing import Dict, List, Sequence, Tuple
+
+import torch
+from torch import nn
+
+from . import ops
+from ._lib import PerturbCfg
+from .builder import ADVERSARIES
+
+
+def perturber_bounds(C: int, training: bool, sensor_error_bound: float = 0.2) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(error_bounds ``eb[C]``, final_bounds ``fb[C]``) as float32 CPU tensors, evaluated with the same
+    fp32 operation order as voxel_perturber.py:209-256 (eb) and :333-359 (fb)."""
+    seb = sensor_error_bound
+    eb = torch.ones(C) * seb
+    fb = torch.ones(C) * seb
+    if C == 4:
+        if not training:
+            eb *= 2.5 * ((2.0 + 1.5 + 1.2) / 3.0)
+            eb[:3] *= 2.0
+            eb[3] = 1.5
+            fb = fb * 5.0
+            fb[:3] *= 5.0
+            fb[3] = 2.0
+        else:
+            eb *= 0.8
+            eb[:3] *= 1.3
+            eb[3] = 0.2
+            fb = fb * 0.9
+            fb[:3] *= 1.2
+            fb[3] = 0.1
+    elif C > 4:
+        eb[4:] = 0.0
+        fb[4:] = 0.0
+    else:
+        # the reference leaves final_bounds unbound for C < 4 and crashes (:357)
+        raise UnboundLocalError("VoxelPerturber needs at least 4 features per point (reference: final_bounds unbound)")
+    return eb, fb
+
+
+class _PerturbApply(torch.autograd.Function):
+    """y = x + p, p = nan_to_num(clamp(raw * eb, -fb, +fb)); both y and p are outputs (the losses use p)."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, raw: torch.Tensor, bounds: PerturbCfg):
+        y, p = ops.perturb_apply_fwd(x, raw, bounds, want_p=True)
+        ctx.save_for_backward(raw)
+        ctx.bounds = bounds
+        return y, p
+
+    @staticmethod
+    def backward(ctx, grad_y, grad_p):
+        (raw,) = ctx.saved_tensors
+        g = grad_y if grad_p is None else (grad_p if grad_y is None else grad_y + grad_p)
+        grad_raw = ops.perturb_apply_bwd(g.contiguous(), raw, ctx.bounds) if ctx.needs_input_grad[1] else None
+        grad_x = grad_y if ctx.needs_input_grad[0] else None
+        return grad_x, grad_raw, None
+
+
+def _gradient_hook(grad):
+    if grad is None:
+        return grad
+    return torch.clamp(torch.nan_to_num(grad, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
+
+
+@ADVERSARIES.register_module()
+class VoxelPerturber(nn.Module):
+    def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
+                 use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
+                 nan_guards: bool = True):
+        super().__init__()
+        voxel_size = list(voxel_size)
+        self.sensor_error_bound = sensor_error_bound
+        self.voxel_size = torch.tensor(voxel_size)
+        self.use_spatial_attention = use_spatial_attention
+        self.voxel_error_bound = sensor_error_bound / torch.tensor(voxel_size + [1.0])
+        self.auto_detect_dims = True
+        self.in_features = 5 if (voxel_size[0] >= 0.1 or voxel_size[2] >= 0.15) else 4
+        self.model = None
+        self.attention = None
+        self.hidden_channels = list(hidden_channels)
+        self.l2_norms: List[float] = []
+        self.l2_percentages: List[float] = []
+        self.constraint_violations: List[float] = []
+        self.perturbation_stats: List[Dict[str, float]] = []
+        self.nan_guards = nan_guards          # False: no isnan().any() host syncs (the fused step's choice)
+        self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
+
+    # ------------------------------------------------------------------ construction
+    def _build_model(self, num_features: int) -> None:
+        if self.model is not None:
+            return
+        h = self.hidden_channels
+        dims = [num_features, h[0], h[1], h[2], h[1], h[0]]
+        layers: List[nn.Module] = []
+        for a, b in zip(dims[:-1], dims[1:]):
+            layers += [nn.Linear(a, b), nn.BatchNorm1d(b), nn.ReLU(inplace=True)]
+        layers += [nn.Linear(h[0], num_features), nn.Tanh()]
+        self.model = nn.Sequential(*layers)
+        if self.use_spatial_attention:
+            mid = max(num_features // 2, 1)
+            self.attention = nn.Sequential(nn.Linear(num_features, mid), nn.ReLU(inplace=True),
+                                           nn.Linear(mid, 1), nn.Sigmoid())
+        self._init_weights()
+        self._hidden_channels = self.hidden_channels
+
+    def build(self, num_features: int, device=None) -> "VoxelPerturber":
+        """Eager build with an explicit C, so that the weights exist before the optimizer / a checkpoint
+        load (the reference only builds on the first forward; SURVEY 5 'checkpoint' caveat)."""
+        self._build_model(num_features)
+        if device is not None:
+            self.to(device)
+        return self
+
+    def _init_weights(self) -> None:
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                if m.out_features in (4, 5):
+                    std = 0.025 if m.out_features == 4 else 0.01
+                    nn.init.normal_(m.weight, mean=0.0, std=std)
+                    if m.bias is not None:
+                        nn.init.normal_(m.bias, mean=0.0, std=std)
+                else:
+                    nn.init.xavier_uniform_(m.weight, gain=1.0)
+                    if m.bias is not None:
+                        nn.init.constant_(m.bias, 0)
+            elif isinstance(m, nn.BatchNorm1d):
+                nn.init.constant_(m.weight, 1)
+                nn.init.constant_(m.bias, 0)
+                m.momentum = 0.1
+                m.eps = 1e-3
+        for param in self.parameters():
+            if param.requires_grad:
+                param.register_hook(_gradient_hook)
+
+    def _reset_problematic_weights(self) -> None:
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                if torch.isnan(m.weight).any():
+                    nn.init.xavier_uniform_(m.weight, gain=0.001)
+                if m.bias is not None and torch.isnan(m.bias).any():
+                    nn.init.constant_(m.bias, 0)
+            elif isinstance(m, nn.BatchNorm1d):
+                if torch.isnan(m.weight).any():
+                    nn.init.constant_(m.weight, 1)
+                if torch.isnan(m.bias).any():
+                    nn.init.constant_(m.bias, 0)
+                if m.running_mean is not None and torch.isnan(m.running_mean).any():
+                    nn.init.constant_(m.running_mean, 0)
+                if m.running_var is not None and torch.isnan(m.running_var).any():
+                    nn.init.constant_(m.running_var, 1)
+
+    # ------------------------------------------------------------------ bounds
+    def bounds(self, num_features: int) -> Tuple[torch.Tensor, torch.Tensor, PerturbCfg]:
+        """(eb, fb, PerturbCfg) for the current train/eval mode; cached."""
+        key = (num_features, bool(self.training))
+        if key not in self._bounds_cache:
+            eb, fb = perturber_bounds(num_features, self.training, self.sensor_error_bound)
+            self._bounds_cache[key] = (eb, fb, PerturbCfg.make(eb.tolist(), fb.tolist()))
+        return self._bounds_cache[key]
+
+    # ------------------------------------------------------------------ forward
+    def _prepare(self, x: torch.Tensor) -> None:
+        if not self.training:
+            for module in self.modules():
+                if isinstance(module, nn.BatchNorm1d):
+                    module.eval()
+        assert x.dim() == 2, f"Expected 2D input, got {x.dim()}D"
+        if self.model is None:
+            self._build_model(x.shape[1])
+            self.model = self.model.to(x.device)
+            if self.attention is not None:
+                self.attention = self.attention.to(x.device)
+        self.voxel_size = self.voxel_size.to(x.device)
+        self.voxel_error_bound = self.voxel_error_bound.to(x.device)
+
+    def raw_perturbation(self, x: torch.Tensor):
+        """The network part of ``forward`` (:157-205): std-normalise, clamp +-10, MLP -> tanh, attention gate.
+        Returns ``raw`` [K, C] in [-1, 1] or ``None`` when a NaN guard trips (caller returns x unchanged)."""
+        if self.nan_guards and torch.isnan(x).any():
+            return None
+        scale = torch.std(x, dim=0, keepdim=True) + 1e-6
+        if self.nan_guards and (torch.isnan(scale).any() or torch.isinf(scale).any()):
+            scale = torch.ones_like(scale)
+        xn = torch.clamp(x / scale, -10.0, 10.0)
+        try:
+            raw = self.model(xn)
+        except RuntimeError:
+            return None
+        if self.nan_guards and torch.isnan(raw).any():
+            self._reset_problematic_weights()
+            return None
+        if self.use_spatial_attention:
+            raw = raw * self.attention(xn)
+        return raw
+
+    @staticmethod
+    def losses(p: torch.Tensor) -> Dict[str, torch.Tensor]:
+        """The four regularisers of voxel_perturber.py:268-299 on the applied perturbation p [K, C]."""
+        C = p.shape[1]
+        l2_norm = torch.norm(p, p=2, dim=1).mean()
+        if C >= 4:
+            intensity = p[:, 3].abs().mean()
+        else:
+            intensity = torch.tensor(0.0, device=p.device, requires_grad=True)
+        bias = p.mean(dim=0).abs().mean()
+        imbalance = p.std(dim=0).std()
+        return dict(l2_norm=l2_norm, intensity_loss=intensity, bias_loss=bias, imbalance_loss=imbalance)
+
+    def forward(self, voxel_features: torch.Tensor):
+        x = voxel_features
+        self._prepare(x)
+        raw = self.raw_perturbation(x)
+        if raw is None:
+            return x, torch.tensor(0.0, device=x.device)
+        _, _, cfg = self.bounds(x.shape[1])
+        if self.nan_guards and torch.isnan(raw).any():          # "NaN after scaling" guard (:259-262)
+            return x, torch.tensor(0.0, device=x.device)
+        y, p = _PerturbApply.apply(x, raw, cfg)
+        loss_dict = self.losses(p)
+        if self.training:
+            self._track_metrics(p, x, loss_dict["l2_norm"])
+        return y, loss_dict
+
+    # ------------------------------------------------------------------ metrics
+    def _track_metrics(self, p: torch.Tensor, x: torch.Tensor, l2_norm: torch.Tensor) -> None:
+        """Same lists as the reference (:388-409), one host sync instead of seven ``.item()`` calls."""
+        with torch.no_grad():
+            ref = torch.norm(x, p=2, dim=1).mean()
+            pa = p.abs()
+            vals = torch.stack([l2_norm.detach(), l2_norm.detach() / (ref + 1e-8) * 100, pa.max(), pa.mean(),
+                                torch.std(p)]).tolist()
+        l2, pct, mx, mean, std = vals
+        violation = max(0.0, mx - float(self.voxel_error_bound.max()))
+        self.l2_norms.append(l2)
+        self.l2_percentages.append(pct)
+        self.constraint_violations.append(violation)
+        self.perturbation_stats.append(dict(l2_norm=l2, l2_percentage=pct, max_perturbation=mx,
+                                            mean_perturbation=mean, std_perturbation=std,
+                                            constraint_violation=violation))
+
+    def save_l2_norms(self, filename: str = "l2_norms.csv") -> None:
+        with open(filename, "w", newline="") as f:
+            w = csv.writer(f)
+            w.writerow(["L2 Norm", "L2 Percentage", "Constraint Violations"])
+            for row in zip(self.l2_norms, self.l2_percentages,
+                           self.constraint_violations or [0] * len(self.l2_norms)):
+                w.writerow(list(row))
+        if self.perturbation_stats:
+            with open(filename.replace(".csv", "_detailed.csv"), "w", newline="") as f:
+                w = csv.DictWriter(f, fieldnames=list(self.perturbation_stats[0].keys()))
+                w.writeheader()
+                w.writerows(self.perturbation_stats)
+        self.l2_norms.clear()
+        self.l2_percentages.clear()
+        self.constraint_violations.clear()
+        self.perturbation_stats.clear()

@@ -1,0 +1,162 @@
+"""CPU tests of the host side: the C-ABI library loads and exports every symbol the header declares, the
+sizing / error entry points behave (no compute calls without a GPU), the registry / perturber host logic
+matches the reference's rules, and the multi-rank plumbing works over gloo with world_size 2."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+import robustpointclouds_b200 as rpc
+from oracle import ref_path as orc
+from robustpointclouds_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_exported():
+    hdr = open(os.path.join(ROOT, "include", "rpc_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(rpc_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert _lib.lib().rpc_abi_version() == 1
+    assert _lib.strerror(0) == "ok" and "NULL" in _lib.strerror(-1)
+
+
+def test_sizing_and_errors_without_gpu():
+    L = _lib.lib()
+    cfg = rpc.VoxelCfg.make([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 16000, 4)
+    g = (ctypes.c_int32 * 3)()
+    assert L.rpc_grid_size(ctypes.byref(cfg), g) == 0 and list(g) == [1408, 1600, 40]
+    n = _lib.counts([120000] * 6)
+    assert L.rpc_voxel_capacity(ctypes.byref(cfg), 6, n) == 96000
+    assert L.rpc_workspace_bytes(ctypes.byref(cfg), 6, n) > 6 * 120000 * 12
+    assert L.rpc_voxel_capacity(ctypes.byref(cfg), 3, _lib.counts([10, 0, 20000])) == 10 + 0 + 16000
+    # invalid configurations are refused before anything is launched
+    bad = rpc.VoxelCfg.make([0.05, 0.0, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 16000, 4)
+    assert L.rpc_grid_size(ctypes.byref(bad), g) == -2
+    assert L.rpc_workspace_bytes(ctypes.byref(bad), 6, n) == 0
+    assert L.rpc_voxel_capacity(ctypes.byref(cfg), 33, n) == -1            # B > RPC_MAX_BATCH
+    assert L.rpc_workspace_bytes(ctypes.byref(cfg), 1, _lib.counts([-5])) == 0
+    bad_c = rpc.VoxelCfg.make([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 16000, 9)
+    assert L.rpc_voxelize_hard(ctypes.byref(bad_c), None, n, 6, None, None, None, None, None, None, None, None,
+                               None, None, 0, None) == -2
+    assert L.rpc_voxelize_hard(ctypes.byref(cfg), None, n, 6, None, None, None, None, None, None, None, None,
+                               None, None, 0, None) == -1                   # NULL pointers
+    assert L.rpc_valid_rows_workspace_bytes(96000, 5) >= 4 * (96000 * 5 // 1024 + 1)
+
+
+def test_ops_refuse_cpu_tensors():
+    cfg = rpc.VoxelCfg.make([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 100, 4)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        rpc.ops.hard_voxelize(torch.zeros(10, 4), [10], cfg)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        rpc.ops.vfe_mean_fwd(torch.zeros(3, 5, 4), torch.ones(3, dtype=torch.int32), 4)
+
+
+@pytest.mark.parametrize("C,training", [(4, True), (4, False), (5, True), (5, False), (6, True)])
+def test_perturber_bounds_match_reference_rules(C, training):
+    eb, fb = rpc.perturber_bounds(C, training, 0.2)
+    oeb, ofb = orc.perturber_bounds(C, training, 0.2)
+    assert np.array_equal(eb.numpy(), oeb) and np.array_equal(fb.numpy(), ofb)
+    if C == 5:
+        assert eb.tolist() == pytest.approx([0.2, 0.2, 0.2, 0.2, 0.0]) and fb[4] == 0
+
+
+def test_perturber_bounds_below_four_features_crashes_like_reference():
+    with pytest.raises(UnboundLocalError):
+        rpc.perturber_bounds(3, True)
+
+
+def test_registry_and_lazy_build():
+    adv = rpc.build_adversary(dict(type="VoxelPerturber", sensor_error_bound=0.2, voxel_size=[0.05, 0.05, 0.1],
+                                   use_spatial_attention=True, hidden_channels=[64, 128, 64]))
+    assert isinstance(adv, rpc.VoxelPerturber) and rpc.ADVERSARIES.get("VoxelPerturber") is rpc.VoxelPerturber
+    assert adv.model is None and adv.attention is None and len(list(adv.parameters())) == 0   # lazy, like the reference
+    adv.build(4)
+    assert sum(p.numel() for p in adv.parameters()) == 34641
+    adv5 = rpc.VoxelPerturber(voxel_size=[0.075, 0.075, 0.2], hidden_channels=[64, 128, 64]).build(5)
+    assert sum(p.numel() for p in adv5.parameters()) == 34772 and adv5.in_features == 5
+    with pytest.raises(KeyError):
+        rpc.build_adversary(dict(type="NoSuchAdversary"))
+    bn = [m for m in adv.modules() if isinstance(m, torch.nn.BatchNorm1d)]
+    assert len(bn) == 5 and all(m.eps == 1e-3 and m.momentum == 0.1 for m in bn)
+
+
+def test_state_dict_keys_match_reference_fixture(golden_dir):
+    g = dict(np.load(os.path.join(golden_dir, "perturber_kitti_train.npz")))
+    state = {k[len("state_"):]: torch.from_numpy(v) for k, v in g.items() if k.startswith("state_")}
+    adv = rpc.VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]]).build(int(g["C"]))
+    missing, unexpected = adv.load_state_dict(state, strict=True)
+    assert not missing and not unexpected
+
+
+def test_param_grad_hook_clamps_like_reference():
+    torch.manual_seed(0)
+    adv = rpc.VoxelPerturber(hidden_channels=[16, 32, 64]).build(4)
+    adv.train()
+    out = adv.model(torch.randn(64, 4) * 5)          # the MLP alone runs anywhere; the fused tail is CUDA-only
+    (out.sum() * 1e4).backward()
+    gmax = max(float(p.grad.abs().max()) for p in adv.parameters() if p.grad is not None)
+    assert gmax == pytest.approx(0.1)
+
+
+def test_metrics_csv_roundtrip(tmp_path):
+    adv = rpc.VoxelPerturber()
+    adv.l2_norms, adv.l2_percentages, adv.constraint_violations = [0.1, 0.2], [1.0, 2.0], [0.0, 0.5]
+    adv.perturbation_stats = [dict(l2_norm=0.1), dict(l2_norm=0.2)]
+    f = tmp_path / "l2.csv"
+    adv.save_l2_norms(str(f))
+    rows = f.read_text().strip().splitlines()
+    assert rows[0] == "L2 Norm,L2 Percentage,Constraint Violations" and len(rows) == 3
+    assert (tmp_path / "l2_detailed.csv").exists() and adv.l2_norms == []
+
+
+def test_shard_batch():
+    assert rpc.shard_batch(6, 0, 1) == [0, 1, 2, 3, 4, 5]
+    assert [rpc.shard_batch(8, r, 8) for r in range(8)] == [[r] for r in range(8)]
+    assert rpc.shard_batch(6, 1, 4) == [1, 5] and rpc.shard_batch(2, 3, 4) == []
+    got = sorted(s for r in range(4) for s in rpc.shard_batch(6, r, 4))
+    assert got == list(range(6))
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)                                   # same weights on every rank
+    adv = rpc.VoxelPerturber(hidden_channels=[8, 16, 32]).build(4)
+    torch.manual_seed(100 + rank)                          # rank-local shard of the batch
+    x = torch.randn(32, 4)
+    out = adv.model(x) * adv.attention(x)
+    (out.square().sum() * 50).backward()                   # the +-0.1 hook fires here, before the reduce
+    local = torch.cat([p.grad.reshape(-1) for p in adv.parameters()]).clone()
+    sync = rpc.FlatGradSync(adv.parameters())
+    sync.all_reduce()
+    after = torch.cat([p.grad.reshape(-1) for p in adv.parameters()])
+    gathered = [torch.zeros_like(local) for _ in range(world)]
+    dist.all_gather(gathered, local)
+    q.put((rank, sync.numel(), float((after - torch.stack(gathered).mean(0)).abs().max()), float(local.abs().max())))
+    dist.destroy_process_group()
+
+
+def test_flat_grad_allreduce_gloo_world2():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=60) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    n_params = sum(p.numel() for p in rpc.VoxelPerturber(hidden_channels=[8, 16, 32]).build(4).parameters())
+    for rank, numel, err, gmax in res:
+        assert numel == n_params and err < 1e-7 and gmax <= 0.1 + 1e-7
