@@ -246,6 +246,8 @@ def scatter_rows(voxels: torch.Tensor, row2k: torch.Tensor, rows: torch.Tensor) 
     dev = _need_cuda(voxels, row2k, rows)
     voxels, rows = _f32c(voxels), _f32c(rows)
     M, P, C = voxels.shape
+    if rows.numel() == 0:                       # no valid row: the copy alone
+        return voxels.clone()
     out = torch.empty_like(voxels)
     st = _lib.lib().rpc_scatter_rows(_ptr(voxels), _ptr(row2k), _ptr(rows), M, P, C, _ptr(out), _stream(dev))
     _lib.check(st, "rpc_scatter_rows")
