@@ -100,11 +100,34 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
-def workload(name: str):
+def workload(name: str, batch: int = 0):
+    """(preset, sweeps per GPU, dynamic?)  kitti = configs[1], nuscenes = configs[2], nuscenes-dynamic = configs[3]"""
     from robustpointclouds_b200 import synth
-    p = synth.PRESETS[name]
-    B = 6 if name == "kitti" else 4
-    return p, B
+    dynamic = name.endswith("-dynamic")
+    base = name.split("-")[0]
+    p = synth.PRESETS[base]
+    B = batch or (6 if base == "kitti" else 4)
+    return p, B, dynamic
+
+
+def b_alg_dyn(N, C, M, F):
+    """SURVEY 8(d) algorithmic bytes of the whole dynamic step"""
+    return 4 * (3 * N * C + 4 * N + 2 * M * F + 4 * M)
+
+
+def cpu_step(dynamic, cloud, raw, eb, fb, p, gf, buf):
+    """one sweep of the path on the CPU oracle (the timed unit of the CPU legs)"""
+    from oracle import ref_path as orc
+    C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
+    if not dynamic:
+        return orc.step_fused(cloud, raw, eb, fb, p["voxel_size"], p["point_cloud_range"], P, V, C, gf,
+                              table_mode=0, buf=buf)[0]
+    y, _ = orc.perturb_apply(cloud, raw, eb, fb)
+    co = orc.dynamic_voxelize(y, p["voxel_size"], p["point_cloud_range"])
+    f, oc, mp, cnt = orc.dynamic_scatter_mean(y, co)
+    g = orc.dynamic_scatter_mean_bwd(gf[: len(cnt)], mp, cnt)
+    orc.perturb_bwd(g, raw, eb, fb)
+    return len(cnt)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -119,21 +142,22 @@ def run_reference(args):
     from oracle import ref_path as orc
     from robustpointclouds_b200 import synth
 
-    p, B = workload(args.workload)
+    p, B, dynamic = workload(args.workload, args.batch)
+    base = args.workload.split("-")[0]
     C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
     vs, pcr = p["voxel_size"], p["point_cloud_range"]
     cores = len(os.sched_getaffinity(0))
     threads = max(1, min(cores, 32))            # every thread allocates its own dense table (360 MB for KITTI)
-    clouds = synth.make_batch(args.workload, B)
+    clouds = synth.make_batch(base, B)
     raws = [synth.make_raw(c, 99 + i) for i, c in enumerate(clouds)]
     eb, fb = orc.perturber_bounds(C, True)
-    gf = np.random.default_rng(0).normal(size=(V, C)).astype(np.float32)
+    gf = np.random.default_rng(0).normal(size=(max(V, p["N"]) if dynamic else V, C)).astype(np.float32)
     orc.lib()
     # a step = S sweeps drawn round-robin from the batch, one per host thread, S bounded so that the
     # whole run ends within ~2 minutes
     bufs = [orc.StepBuffers(len(clouds[0]), C, P, V, C)]
     t0 = time.perf_counter()
-    orc.step_fused(clouds[0], raws[0], eb, fb, vs, pcr, P, V, C, gf, table_mode=0, buf=bufs[0])
+    cpu_step(dynamic, clouds[0], raws[0], eb, fb, p, gf, bufs[0])
     t1 = time.perf_counter() - t0
     S = threads
     if (args.steps + args.warmup) * t1 * 1.5 > 120.0:      # even one sweep per thread per step is too long
@@ -142,7 +166,7 @@ def run_reference(args):
 
     def one(i):
         j = i % B
-        return orc.step_fused(clouds[j], raws[j], eb, fb, vs, pcr, P, V, C, gf, table_mode=0, buf=bufs[i])[0]
+        return cpu_step(dynamic, clouds[j], raws[j], eb, fb, p, gf, bufs[i])
 
     idx = list(range(S))
     with ThreadPoolExecutor(threads) as ex:
@@ -154,8 +178,9 @@ def run_reference(args):
         dt = time.perf_counter() - t0
     pts = sum(len(clouds[i % B]) for i in idx) * args.steps
     val = pts / dt / 1e6
-    sample = (f"{S} sweeps per step drawn round-robin from the batch's {B}, {threads} threads (one sweep per thread), "
-              f"dense int32[{'x'.join(map(str, orc.grid_size(vs, pcr)[::-1]))}] table allocated+filled per call like mmcv")
+    sample = (f"{S} sweeps per step drawn round-robin from the batch's {B}, {threads} threads (one sweep per thread), " +
+              ("dynamic voxelize + sort-unique scatter-mean + backward (oracle port)" if dynamic else
+               f"dense int32[{'x'.join(map(str, orc.grid_size(vs, pcr)[::-1]))}] table allocated+filled per call like mmcv"))
     line = {
         "impl": "reference", "metric": "M points/s perturb+voxelize+VFE fwd/bwd", "value": round(val, 4),
         "unit": "M points/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -172,12 +197,16 @@ def run_reference(args):
 
 
 def config_dict(name, p, B, note=None, **kw):
-    d = {"workload": (f"SECOND KITTI adversarial step: perturb(0.2 m)+hard voxelize+HardSimpleVFE fwd/bwd, "
-                      f"batch {B} x {p['N']} pts x {p['C']}" if name == "kitti" else
-                      f"CenterPoint nuScenes 10-sweep hard step: perturb+hard voxelize+HardSimpleVFE fwd/bwd, "
-                      f"batch {B} x {p['N']} pts x {p['C']}"),
+    dynamic = name.endswith("-dynamic")
+    wl = {"kitti": "SECOND KITTI adversarial step: perturb(0.2 m)+hard voxelize+HardSimpleVFE fwd/bwd",
+          "nuscenes": "CenterPoint nuScenes 10-sweep hard step: perturb+hard voxelize+HardSimpleVFE fwd/bwd",
+          "nuscenes-dynamic": "CenterPoint nuScenes 10-sweep dynamic step (no caps): perturb+dynamic voxelize+"
+                              "scatter-mean VFE fwd/bwd",
+          "kitti-dynamic": "KITTI dynamic step (no caps): perturb+dynamic voxelize+scatter-mean VFE fwd/bwd"}[name]
+    d = {"workload": f"{wl}, batch {B} x {p['N']} pts x {p['C']}",
          "voxel_size": p["voxel_size"], "point_cloud_range": p["point_cloud_range"],
-         "max_num_points": p["max_num_points"], "max_voxels": p["max_voxels"][0], "batch_per_gpu": B,
+         "max_num_points": -1 if dynamic else p["max_num_points"],
+         "max_voxels": -1 if dynamic else p["max_voxels"][0], "batch_per_gpu": B,
          "points_per_sweep": p["N"], "distribution": "lidar (synth.py)"}
     if note:
         d["note"] = note
@@ -188,9 +217,10 @@ def config_dict(name, p, B, note=None, **kw):
 def cpu_baseline(name, clouds, raws, p, budget_s=12.0):
     """oracle (port) on ONE host core, bounded sample of the same batch"""
     from oracle import ref_path as orc
+    dynamic = name.endswith("-dynamic")
     C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
     eb, fb = orc.perturber_bounds(C, True)
-    gf = np.random.default_rng(0).normal(size=(V, C)).astype(np.float32)
+    gf = np.random.default_rng(0).normal(size=(max(V, max(len(c) for c in clouds)) if dynamic else V, C)).astype(np.float32)
     buf = orc.StepBuffers(max(len(c) for c in clouds), C, P, V, C)
     orc.lib()
     done, pts = 0, 0
@@ -198,15 +228,15 @@ def cpu_baseline(name, clouds, raws, p, budget_s=12.0):
     while True:
         i = done % len(clouds)
         b = orc.StepBuffers(len(clouds[i]), C, P, V, C) if len(clouds[i]) != buf.perturbed.shape[0] else buf
-        orc.step_fused(clouds[i], raws[i], eb, fb, p["voxel_size"], p["point_cloud_range"], P, V, C, gf,
-                       table_mode=0, buf=b)
+        cpu_step(dynamic, clouds[i], raws[i], eb, fb, p, gf, b)
         done += 1
         pts += len(clouds[i])
         dt = time.perf_counter() - t0
         if dt > budget_s or done >= 4 * len(clouds):
             break
     return {"value": round(pts / dt / 1e6, 4), "unit": "M points/s", "cores": 1, "kind": "port",
-            "sample": f"{done} sweeps of the batch, sequential on 1 core, {dt:.1f} s, dense per-call cell table like mmcv"}
+            "sample": f"{done} sweeps of the batch, sequential on 1 core, {dt:.1f} s, " +
+                      ("sort-unique scatter-mean" if dynamic else "dense per-call cell table like mmcv")}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -228,11 +258,11 @@ def run_b200(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
 
-    p, B = workload(args.workload)
+    p, B, dynamic = workload(args.workload, args.batch)
     C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
     F = C
     cfg = VoxelCfg.make(p["voxel_size"], p["point_cloud_range"], P, V, C, F)
-    clouds = synth.make_batch(args.workload, B, seed=1234 + rank * B)
+    clouds = synth.make_batch(args.workload.split("-")[0], B, seed=1234 + rank * B)
     raws = [synth.make_raw(c, 99 + rank * B + i) for i, c in enumerate(clouds)]
     n = [len(c) for c in clouds]
     N = sum(n)
@@ -241,16 +271,29 @@ def run_b200(args):
     h_pts = torch.from_numpy(np.concatenate(clouds)).pin_memory()
     h_raw = torch.from_numpy(np.concatenate(raws)).pin_memory()
     pts, raw = h_pts.to(dev), h_raw.to(dev)
-    out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True)
-    cap = out.capacity
+    if dynamic:
+        out = ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds)
+        cap = N
+    else:
+        out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True)
+        cap = out.capacity
     gfe = torch.randn((cap, F), device=dev, generator=torch.Generator(dev).manual_seed(5 + rank))
     graw = torch.empty((N, C), dtype=torch.float32, device=dev)
     pgrad = torch.zeros(PERTURBER_PARAMS.get(C, 34641), dtype=torch.float32, device=dev)  # flat perturber grads
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
 
-    def path():
-        ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+    def fwd():
+        if dynamic:
+            ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+        else:
+            ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+
+    def bwd():
         ops.step_bwd(gfe, out.num_points, out.point2voxel, cfg, raw=raw, bounds=bounds, out=graw)
+
+    def path():
+        fwd()
+        bwd()
 
     graph = None
     if not args.no_graph:
@@ -297,14 +340,16 @@ def run_b200(args):
     vn = out.voxel_num.cpu().numpy()
     M = int(vn[-1])
     K = int((out.point2voxel >= 0).sum().item())
-    launches_per_step = 2                               # k_hard_fwd (persistent, cooperative) + k_step_bwd
+    launches_per_step = 2                               # k_hard_fwd | k_dyn_scatter (persistent, cooperative) + k_step_bwd
 
     # ---- e2e: pinned host buffers in, every API-visible output back to pinned host buffers
-    h_out = {k: torch.empty_like(v, device="cpu").pin_memory() for k, v in
-             dict(voxels=out.voxels, coors=out.coors, num_points=out.num_points, voxel_num=out.voxel_num,
-                  feats=out.feats, grad_raw=graw).items()}
-    d_out = dict(voxels=out.voxels, coors=out.coors, num_points=out.num_points, voxel_num=out.voxel_num,
-                 feats=out.feats, grad_raw=graw)
+    if dynamic:
+        d_out = dict(coors=out.coors, voxel_coors=out.voxel_coors, num_points=out.num_points,
+                     voxel_num=out.voxel_num, feats=out.feats, grad_raw=graw)
+    else:
+        d_out = dict(voxels=out.voxels, coors=out.coors, num_points=out.num_points, voxel_num=out.voxel_num,
+                     feats=out.feats, grad_raw=graw)
+    h_out = {k: torch.empty_like(v, device="cpu").pin_memory() for k, v in d_out.items()}
 
     def e2e_step():
         pts.copy_(h_pts, non_blocking=True)
@@ -324,24 +369,26 @@ def run_b200(args):
     prof_steps = max(3, min(args.steps, 30))
     for it in range(prof_steps + 2):
         flush.zero_()
-        ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
-        fwd = _lib.profile_read()
-        ph = ops.phase_times_us(cfg, n, dev=dev)
-        ops.step_bwd(gfe, out.num_points, out.point2voxel, cfg, raw=raw, bounds=bounds, out=graw)
-        bwd = _lib.profile_read()
+        fwd()
+        t_fwd = _lib.profile_read()
+        ph = {} if dynamic else ops.phase_times_us(cfg, n, dev=dev)
+        bwd()
+        t_bwd = _lib.profile_read()
         if it >= 2:
-            for nm, ms in fwd + bwd:
+            for nm, ms in t_fwd + t_bwd:
                 stages.setdefault(nm, []).append(ms)
             for nm, us in ph.items():
                 phases.setdefault(nm, []).append(us)
     _lib.profile_enable(False)
     stage_us = {k2: round(1e3 * float(np.mean(v)), 3) for k2, v in stages.items()}
     peak, peak_src = measured_peak_gbs()
-    balg = b_alg_hard(N, C, P, M, K, F)
+    balg = b_alg_dyn(N, C, M, F) if dynamic else b_alg_hard(N, C, P, M, K, F)
     # per-kernel algorithmic bytes (DESIGN.md "kernels"): what that kernel alone must read and write
     kern_bytes = {
         # forward: points + raw in; voxels, coors(4)+num_points, feats, point2voxel out
         "k_hard_fwd": 4 * (2 * N * C + M * P * C + 5 * M + M * F + N),
+        # dynamic forward: points + raw in; per-point coors (4) + map, voxel coors (4), counts, feats out
+        "k_dyn_scatter": 4 * (2 * N * C + 5 * N + 5 * M + M * F),
         # backward: point2voxel + raw + grad feats + counts in, grad_raw out
         "k_step_bwd": 4 * (N + N * C + M * F + M + N * C),
     }
@@ -391,7 +438,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="kitti", choices=["kitti", "nuscenes"])
+    ap.add_argument("--workload", default="kitti", choices=["kitti", "nuscenes", "nuscenes-dynamic", "kitti-dynamic"])
+    ap.add_argument("--batch", type=int, default=0, help="sweeps per GPU (default: 6 KITTI, 4 nuScenes)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()

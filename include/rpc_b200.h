@@ -26,7 +26,8 @@
  *                          (/root/reference/models/adversarial/voxel_perturber.py:256,357-365,285)
  *   rpc_voxelize_hard (raw != NULL) + rpc_step_bwd   the north-star order: perturb -> hard voxelize ->
  *                          VFE mean, and the gradient back to the raw per-point perturbation
- *   rpc_dynamic_scatter_mean_fwd/bwd   mmcv DynamicScatter(mean) for the dynamic configuration
+ *   rpc_dynamic_scatter_mean_fwd   dynamic voxelization + mmcv DynamicScatter(mean) in one launch for the
+ *                          dynamic configuration; its backward is rpc_step_bwd
  */
 #ifndef RPC_B200_H_
 #define RPC_B200_H_
@@ -135,6 +136,29 @@ int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats /*[cap,F]*/,
 int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
                          const int32_t *n_per_sample /*[host]*/, int B, const float *raw,
                          const rpc_perturb_cfg *pc, int32_t *coors, int ncol, void *stream);
+
+/*
+ * Dynamic voxelization + mmcv DynamicScatter(mean) of a batch (BASELINE.json config 4; mmdet3d
+ * DynamicSimpleVFE / `voxel_type='dynamic'` consumers of the call sites above), one launch.
+ *   coors_in    [ntotal, 4] i32 (b, z, y, x) or NULL.  NULL: cells are computed from the (perturbed, when
+ *               raw/pc are given) points and sweep b owns rows n_per_sample-wise; non-NULL: points are
+ *               scattered by these rows (DynamicScatter.forward(points, coors)); rows with a negative or
+ *               out-of-grid entry are dropped.
+ *   coors_out   [ntotal, 4] i32 per-point (b, z, y, x), cells -1 when dropped (may be NULL; ignored with coors_in)
+ *   point2voxel [ntotal]    i32 voxel row of each point, -1 when dropped
+ *   feats       [cap, F]    f32 mean of the (perturbed) points of the voxel, all points, no cap
+ *   voxel_coors [cap, 4]    i32 (b, z, y, x); per sample ascending in (z, y, x) (torch.unique order), samples in order
+ *   num_points  [cap]       i32 points per voxel
+ *   voxel_num   [B + 1]     i32 per-sample voxel counts, then the total            (device memory)
+ * cap = ntotal rows (every point its own voxel).  Sums are fp32 red.add (order-free; mmcv's CUDA reduce is
+ * atomic too).  The backward is rpc_step_bwd(grad_feats, num_points, point2voxel, raw, ...).
+ */
+size_t rpc_dynamic_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
+int rpc_dynamic_scatter_mean_fwd(const rpc_voxel_cfg *cfg, const float *points,
+                                 const int32_t *n_per_sample /*[host]*/, int B, const float *raw,
+                                 const rpc_perturb_cfg *pc, const int32_t *coors_in, int32_t *coors_out,
+                                 int32_t *point2voxel, float *feats, int32_t *voxel_coors, int32_t *num_points,
+                                 int32_t *voxel_num, void *workspace, size_t workspace_bytes, void *stream);
 
 /* HardSimpleVFE: out[m, c] = sum_k voxels[m, k, c] / num_points[m], c < F, slots summed in order.
  * m_dev (device int32, may be NULL) bounds the rows at run time: only min(M, *m_dev) rows are done. */

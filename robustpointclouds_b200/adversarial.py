@@ -108,3 +108,29 @@ def adversarial_step(points: torch.Tensor, raw: torch.Tensor, n_per_sample: Sequ
     nothing here synchronises the host.  ``feats.backward(g)`` fills ``raw.grad`` with
     ``(-fb <= raw*eb <= fb) ? g[v]/n[v] * eb : 0`` for the stored points and 0 elsewhere."""
     return _AdversarialStep.apply(points, raw, list(n_per_sample), cfg, bounds, out)
+
+
+class _DynamicStep(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, points, raw, n_per_sample, cfg: VoxelCfg, bounds: PerturbCfg, out: Optional[ops.DynVoxels]):
+        dv = ops.dynamic_scatter_mean(points, n_per_sample, cfg, raw=raw, bounds=bounds, out=out)
+        ctx.save_for_backward(raw, dv.num_points, dv.point2voxel)
+        ctx.cfg, ctx.bounds = cfg, bounds
+        ctx.mark_non_differentiable(dv.voxel_coors, dv.num_points, dv.voxel_num, dv.point2voxel)
+        return dv.feats, dv.voxel_coors, dv.num_points, dv.voxel_num, dv.point2voxel
+
+    @staticmethod
+    def backward(ctx, grad_feats, *unused):
+        raw, num_points, p2v = ctx.saved_tensors
+        grad_raw = ops.step_bwd(grad_feats.contiguous(), num_points, p2v, ctx.cfg, raw=raw, bounds=ctx.bounds)
+        return None, grad_raw, None, None, None, None
+
+
+def dynamic_step(points: torch.Tensor, raw: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelCfg,
+                 bounds: PerturbCfg, out: Optional[ops.DynVoxels] = None):
+    """Fused dynamic configuration (BASELINE.json config 4): perturb every point, dynamic-voxelize, mean of ALL
+    points of a voxel (mmcv DynamicScatter(mean): voxels per sample in sorted (z, y, x) order, no caps).
+    Returns ``(feats, voxel_coors, num_points, voxel_num, point2voxel)`` sized for one voxel per point;
+    ``feats.backward(g)`` fills ``raw.grad`` with ``(-fb <= raw*eb <= fb) ? g[v]/n[v] * eb : 0``
+    (DynamicScatter's autograd rule through the clamp and scale of voxel_perturber.py:256,357-359)."""
+    return _DynamicStep.apply(points, raw, list(n_per_sample), cfg, bounds, out)

@@ -8,6 +8,7 @@
 #include "vfe.cuh"
 #include "hard_fwd.cuh"
 #include "rows.cuh"
+#include "dyn_scatter.cuh"
 
 using namespace rpc;
 
@@ -419,6 +420,118 @@ RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
+}  // extern "C" (closed for the dynamic-scatter helpers)
+
+// ------------------------------------------------------------------ dynamic scatter (config 4)
+namespace {
+struct DynPlan {
+    Plan pl;
+    long long Gp, acap;
+    int W1;
+    size_t o_coarse, o_fine, o_gpre, o_sgrp, o_cell, o_pslot, o_part, o_ssb, bytes;
+};
+constexpr int kDynMaxCtas = 4096;
+
+int make_dyn_plan(const rpc_voxel_cfg *cfg, const GridDesc &gd, int B, const int32_t *n, DynPlan *dp)
+{
+    rpc_voxel_cfg c2 = *cfg;
+    c2.max_points = 1; c2.max_voxels = 1;
+    int st = make_plan(&c2, B, n, &dp->pl);
+    if (st) return st;
+    const long long G = (long long)gd.g[0] * gd.g[1] * gd.g[2];
+    dp->Gp = (G + kCoarseCells - 1) / kCoarseCells * kCoarseCells;
+    const long long w1 = dp->Gp / kCoarseCells * B;
+    if (w1 > 0x3FFFFFFFLL) return RPC_ERR_TOO_LARGE;
+    dp->W1 = (int)w1;
+    const long long groups = dp->Gp / kGroupCells * B;
+    dp->acap = dp->pl.ntotal < groups ? dp->pl.ntotal : groups;
+    if (dp->acap < 1) dp->acap = 1;
+    size_t o = 0;
+    dp->o_coarse = o; o += align_up(8 * (size_t)dp->W1);
+    dp->o_fine = o;   o += align_up(32 * (size_t)dp->acap);
+    dp->o_gpre = o;   o += align_up(4 * (size_t)dp->acap);
+    dp->o_sgrp = o;   o += align_up(4 * (size_t)dp->acap);
+    dp->o_cell = o;   o += align_up(4 * (size_t)dp->pl.ntotal);
+    dp->o_pslot = o;  o += align_up(4 * (size_t)dp->pl.ntotal);
+    dp->o_part = o;   o += align_up(4 * 2 * (size_t)kDynMaxCtas);
+    dp->o_ssb = o;    o += align_up(4 * (RPC_MAX_BATCH + 1));
+    dp->bytes = o;
+    return RPC_OK;
+}
+
+template <int C, bool PERTURB>
+int launch_dyn_t(DynParams &p, cudaStream_t st)
+{
+    auto kern = k_dyn_scatter<C, PERTURB>;
+    int grid = device_sms() * kDynCtasPerSM;
+    if (grid > kDynMaxCtas) grid = kDynMaxCtas;
+    void *args[] = {&p};
+    g_prof.begin(st);
+    if (cudaLaunchCooperativeKernel((void *)kern, dim3(grid), dim3(kDynThreads), args, 0, st) != cudaSuccess)
+        return RPC_ERR_CUDA;
+    g_prof.stage("k_dyn_scatter", st);
+    return RPC_OK;
+}
+}  // namespace
+
+extern "C" {
+
+RPC_API size_t rpc_dynamic_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
+{
+    GridDesc gd;
+    DynPlan dp;
+    if (check_cfg(cfg, false) || make_grid(cfg, &gd) || make_dyn_plan(cfg, gd, B, n_per_sample, &dp)) return 0;
+    return dp.bytes;
+}
+
+RPC_API int rpc_dynamic_scatter_mean_fwd(const rpc_voxel_cfg *cfg, const float *points,
+                                         const int32_t *n_per_sample, int B, const float *raw,
+                                         const rpc_perturb_cfg *pc, const int32_t *coors_in, int32_t *coors_out,
+                                         int32_t *point2voxel, float *feats, int32_t *voxel_coors,
+                                         int32_t *num_points, int32_t *voxel_num, void *workspace,
+                                         size_t workspace_bytes, void *stream)
+{
+    int st = check_cfg(cfg, false);
+    if (st) return st;
+    GridDesc gd;
+    if ((st = make_grid(cfg, &gd))) return st;
+    DynPlan dp;
+    if ((st = make_dyn_plan(cfg, gd, B, n_per_sample, &dp))) return st;
+    if (!voxel_num || !workspace) return RPC_ERR_NULL;
+    if (dp.pl.ntotal > 0 && (!points || !point2voxel || !feats || !voxel_coors || !num_points)) return RPC_ERR_NULL;
+    if (raw && !pc) return RPC_ERR_NULL;
+    if (workspace_bytes < dp.bytes) return RPC_ERR_WORKSPACE;
+    if (misaligned(points) || misaligned(raw) || misaligned(coors_in) || misaligned(coors_out) ||
+        misaligned(feats) || misaligned(voxel_coors) || misaligned(workspace))
+        return RPC_ERR_ALIGN;
+    DynParams p;
+    char *w = static_cast<char *>(workspace);
+    p.pts = points; p.raw = raw; p.coors_in = coors_in; p.coors_out = coors_in ? nullptr : coors_out;
+    p.p2v = point2voxel; p.feats = feats; p.vcoors = voxel_coors; p.count = num_points; p.voxel_num = voxel_num;
+    p.coarse = reinterpret_cast<uint2 *>(w + dp.o_coarse);
+    p.fine = reinterpret_cast<uint32_t *>(w + dp.o_fine);
+    p.gpre = reinterpret_cast<uint32_t *>(w + dp.o_gpre);
+    p.slot_grp = reinterpret_cast<int *>(w + dp.o_sgrp);
+    p.cell = reinterpret_cast<int *>(w + dp.o_cell);
+    p.pslot = reinterpret_cast<int *>(w + dp.o_pslot);
+    p.part = reinterpret_cast<uint32_t *>(w + dp.o_part);
+    p.ssb = reinterpret_cast<int *>(w + dp.o_ssb);
+    p.Gp = dp.Gp; p.W1 = dp.W1; p.ntotal = (int)dp.pl.ntotal;
+    p.gd = gd; p.bd = dp.pl.bd;
+    fill_perturb(cfg, pc, &p.pd);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (cfg->C) {
+#define RPC_CASE(CC) \
+    case CC: return raw ? launch_dyn_t<CC, true>(p, s) : launch_dyn_t<CC, false>(p, s);
+        RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+#undef RPC_CASE
+    }
+    return RPC_ERR_CONFIG;
+}
+
+}  // extern "C"
+
+extern "C" {
 // ------------------------------------------------------------------ reference-order composition
 RPC_API size_t rpc_valid_rows_workspace_bytes(int64_t M, int P)
 {

@@ -162,6 +162,64 @@ def dynamic_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: Vox
     return coors
 
 
+@dataclass
+class DynVoxels:
+    """Outputs of one batched dynamic voxelization + scatter-mean, sized for one voxel per point; only the
+    first ``voxel_num[-1]`` rows of ``feats`` / ``voxel_coors`` / ``num_points`` are defined."""
+    feats: torch.Tensor            # [N, F] f32
+    voxel_coors: torch.Tensor      # [N, 4] i32 (b, z, y, x)
+    num_points: torch.Tensor       # [N] i32
+    voxel_num: torch.Tensor        # [B + 1] i32 on the device
+    point2voxel: torch.Tensor      # [N] i32
+    coors: Optional[torch.Tensor]  # [N, 4] i32 per point, or None
+
+    def total(self) -> int:
+        return int(self.voxel_num[-1].item())
+
+
+def dynamic_scatter_mean(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelCfg,
+                         raw: Optional[torch.Tensor] = None, bounds: Optional[PerturbCfg] = None,
+                         coors_in: Optional[torch.Tensor] = None, want_coors: bool = True,
+                         out: Optional[DynVoxels] = None, workspace: Optional[torch.Tensor] = None) -> DynVoxels:
+    """``rpc_dynamic_scatter_mean_fwd``: dynamic voxelization of the (perturbed) points and mmcv
+    DynamicScatter(mean) in one launch; with ``coors_in`` [N,4] the points are scattered by those rows."""
+    dev = _need_cuda(points, raw, coors_in)
+    points = _f32c(points)
+    if points.dim() != 2 or points.shape[1] != cfg.C:
+        raise ValueError(f"points must be [N, {cfg.C}], got {tuple(points.shape)}")
+    if sum(n_per_sample) != points.shape[0]:
+        raise ValueError("n_per_sample does not add up to the number of rows")
+    if raw is not None:
+        raw = _f32c(raw)
+        if raw.shape != points.shape or bounds is None:
+            raise ValueError("raw must match points and come with bounds")
+    if coors_in is not None:
+        coors_in = coors_in.to(torch.int32).contiguous()
+        if coors_in.shape != (points.shape[0], 4):
+            raise ValueError("coors_in must be [N, 4] (batch, z, y, x)")
+    L = _lib.lib()
+    B = len(n_per_sample)
+    n_arr = _lib.counts(n_per_sample)
+    nbytes = L.rpc_dynamic_workspace_bytes(ctypes.byref(cfg), B, n_arr)
+    if nbytes == 0:
+        raise _lib.RpcError(-2, "rpc_dynamic_workspace_bytes")
+    ws = workspace if workspace is not None else _default_ws.get(nbytes, dev)
+    N, F = points.shape[0], cfg.F
+    if out is None:
+        i32 = dict(dtype=torch.int32, device=dev)
+        out = DynVoxels(feats=torch.empty((N, F), dtype=torch.float32, device=dev),
+                        voxel_coors=torch.empty((N, 4), **i32), num_points=torch.empty((N,), **i32),
+                        voxel_num=torch.empty((B + 1,), **i32), point2voxel=torch.empty((N,), **i32),
+                        coors=torch.empty((N, 4), **i32) if (want_coors and coors_in is None) else None)
+    st = L.rpc_dynamic_scatter_mean_fwd(ctypes.byref(cfg), _ptr(points), n_arr, B, _ptr(raw),
+                                        ctypes.byref(bounds) if bounds is not None else None,
+                                        _ptr(coors_in), _ptr(out.coors), _ptr(out.point2voxel), _ptr(out.feats),
+                                        _ptr(out.voxel_coors), _ptr(out.num_points), _ptr(out.voxel_num),
+                                        ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(st, "rpc_dynamic_scatter_mean_fwd")
+    return out
+
+
 def vfe_mean_fwd(voxels: torch.Tensor, num_points: torch.Tensor, num_features: int,
                  m_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
     dev = _need_cuda(voxels, num_points)

@@ -118,3 +118,44 @@ class HardSimpleVFE(nn.Module):
 
     def forward(self, features: torch.Tensor, num_points: torch.Tensor, coors: torch.Tensor = None, *args, **kwargs):
         return _VfeMean.apply(features, num_points, self.num_features)
+
+
+class _ScatterMean(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, points, coors, cfg: VoxelCfg, B: int):
+        dv = ops.dynamic_scatter_mean(points, [points.shape[0]] + [0] * (B - 1), cfg, coors_in=coors)
+        m = dv.total()                                          # host sync, as mmcv's unique() has
+        ctx.save_for_backward(dv.num_points, dv.point2voxel)
+        ctx.cfg = cfg
+        ctx.mark_non_differentiable(dv.voxel_coors)
+        return dv.feats[:m], dv.voxel_coors[:m]
+
+    @staticmethod
+    def backward(ctx, grad_feats, _):
+        num_points, p2v = ctx.saved_tensors
+        return ops.step_bwd(grad_feats.contiguous(), num_points, p2v, ctx.cfg), None, None, None
+
+
+class DynamicScatter(nn.Module):
+    """mmcv ``ops.DynamicScatter(voxel_size, point_cloud_range, average_points)``: ``forward(points[N,C],
+    coors[N,4] (batch, z, y, x)) -> (voxel_feats[M,C], voxel_coors[M,4])``, voxels per sample in sorted
+    (z, y, x) order, rows with a negative coordinate dropped.  Only the mean reduction
+    (``average_points=True``) is on the path (DynamicSimpleVFE); max raises."""
+
+    def __init__(self, voxel_size: Sequence[float], point_cloud_range: Sequence[float], average_points: bool):
+        super().__init__()
+        if not average_points:
+            raise NotImplementedError("DynamicScatter(max) is not on the adversarial input path")
+        self.voxel_size = list(voxel_size)
+        self.point_cloud_range = list(point_cloud_range)
+        self.average_points = average_points
+
+    def forward(self, points: torch.Tensor, coors: torch.Tensor):
+        C = points.shape[1]
+        cfg = VoxelCfg.make(self.voxel_size, self.point_cloud_range, 1, 1, C, C)
+        if coors.shape[-1] == 3:                                # single sample, (z, y, x)
+            coors4 = torch.nn.functional.pad(coors, (1, 0), value=0)
+            f, c = _ScatterMean.apply(points, coors4, cfg, 1)
+            return f, c[:, 1:]
+        B = int(coors[-1, 0].item()) + 1 if coors.shape[0] else 1   # mmcv reads the batch size the same way
+        return _ScatterMean.apply(points, coors, cfg, max(B, 1))
