@@ -281,6 +281,15 @@ def run_b200(args):
     graw = torch.empty((N, C), dtype=torch.float32, device=dev)
     pgrad = torch.zeros(PERTURBER_PARAMS.get(C, 34641), dtype=torch.float32, device=dev)  # flat perturber grads
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    flush_rd = torch.zeros(L2_FLUSH_BYTES // 8, dtype=torch.int32, device=dev)        # 256 MiB, only ever read
+    flush_sink = torch.zeros(1, dtype=torch.int64, device=dev)
+
+    def l2_flush():
+        """overwrite 512 MiB (evicts everything), then -- unless --flush write -- stream 256 MiB of clean data
+        through L2 so that the step does not also pay for writing back the flush's own dirty lines"""
+        flush.zero_()
+        if args.flush == "write+read":
+            flush_sink.copy_(flush_rd.sum())
 
     def fwd():
         if dynamic:
@@ -312,14 +321,14 @@ def run_b200(args):
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
-            flush.zero_(); fn()
+            l2_flush(); fn()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         for a, b in ev:
-            flush.zero_()
+            l2_flush()
             a.record(); fn(); b.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -368,10 +377,10 @@ def run_b200(args):
     _lib.profile_enable(True)
     prof_steps = max(3, min(args.steps, 30))
     for it in range(prof_steps + 2):
-        flush.zero_()
+        l2_flush()
         fwd()
         t_fwd = _lib.profile_read()
-        ph = {} if dynamic else ops.phase_times_us(cfg, n, dev=dev)
+        ph = ops.dyn_phase_times_us(cfg, n, dev=dev) if dynamic else ops.phase_times_us(cfg, n, dev=dev)
         bwd()
         t_bwd = _lib.profile_read()
         if it >= 2:
@@ -412,8 +421,9 @@ def run_b200(args):
             "unit": "M points/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": config_dict(args.workload, p, B, l2="flushed between steps (512 MiB overwrite outside the "
-                                  "per-step CUDA-event pairs)", cuda_graph=graph is not None, voxels=M, kept_points=K,
+            "config": config_dict(args.workload, p, B, l2="flushed between steps, outside the per-step CUDA-event pairs: 512 MiB overwrite" +
+                                  (" then a 256 MiB read-only sweep (L2 left full of clean lines)"
+                                   if args.flush == "write+read" else ""), cuda_graph=graph is not None, voxels=M, kept_points=K,
                                   collective=("nccl all_reduce of %d fp32 perturber grads per step" % pgrad.numel())
                                   if world > 1 else "none"),
             "clocks": clocks,
@@ -441,6 +451,8 @@ def main():
     ap.add_argument("--workload", default="kitti", choices=["kitti", "nuscenes", "nuscenes-dynamic", "kitti-dynamic"])
     ap.add_argument("--batch", type=int, default=0, help="sweeps per GPU (default: 6 KITTI, 4 nuScenes)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--flush", default="write", choices=["write", "write+read"],
+                    help="L2 flush between steps: 512 MiB overwrite, optionally followed by a 256 MiB read sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

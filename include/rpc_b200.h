@@ -154,6 +154,10 @@ int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
  * atomic too).  The backward is rpc_step_bwd(grad_feats, num_points, point2voxel, raw, ...).
  */
 size_t rpc_dynamic_workspace_bytes(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
+/* byte offset, inside the workspace, of 10 uint64 %globaltimer stamps (ns) that CTA 0 of the dynamic kernel
+ * writes at its phase boundaries while profiling is enabled: start, after clear, mark, coarse sums, coarse
+ * scan, fine bits, fine sums, rank, sum, mean.  -1 on invalid arguments. */
+int64_t rpc_dynamic_stamps_offset(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample /*[host]*/);
 int rpc_dynamic_scatter_mean_fwd(const rpc_voxel_cfg *cfg, const float *points,
                                  const int32_t *n_per_sample /*[host]*/, int B, const float *raw,
                                  const rpc_perturb_cfg *pc, const int32_t *coors_in, int32_t *coors_out,

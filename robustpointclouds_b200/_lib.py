@@ -23,7 +23,7 @@ SYMBOLS = (
     "rpc_profile_enable", "rpc_profile_read", "rpc_workspace_stamps_offset",
     "rpc_valid_rows_workspace_bytes", "rpc_valid_rows", "rpc_scatter_rows", "rpc_gather_rows",
     "rpc_perturb_apply_fwd", "rpc_perturb_apply_bwd",
-    "rpc_dynamic_workspace_bytes", "rpc_dynamic_scatter_mean_fwd",
+    "rpc_dynamic_workspace_bytes", "rpc_dynamic_scatter_mean_fwd", "rpc_dynamic_stamps_offset",
 )
 
 
@@ -93,6 +93,8 @@ def lib() -> ctypes.CDLL:
     L.rpc_voxelize_dynamic.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, i32, vp]
     L.rpc_dynamic_workspace_bytes.restype = sz
     L.rpc_dynamic_workspace_bytes.argtypes = [cfgp, i32, i32p]
+    L.rpc_dynamic_stamps_offset.restype = i64
+    L.rpc_dynamic_stamps_offset.argtypes = [cfgp, i32, i32p]
     L.rpc_dynamic_scatter_mean_fwd.argtypes = [cfgp, vp, i32p, i32, vp, pcp, vp, vp, vp, vp, vp, vp, vp, vp, sz, vp]
     L.rpc_vfe_mean_fwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]
     L.rpc_vfe_mean_bwd.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp, vp]

@@ -2,6 +2,7 @@
 // No allocation, no host synchronisation, fixed launch topology per call (CUDA-graph capturable).
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "dynamic.cuh"
@@ -42,6 +43,7 @@ int make_grid(const rpc_voxel_cfg *cfg, GridDesc *gd)
         if (!(g >= 1.0f) || g > 2147483647.0f) return RPC_ERR_CONFIG;
         gd->lo[d] = cfg->pcr[d];
         gd->vs[d] = cfg->voxel_size[d];
+        { volatile float r = 1.0f / cfg->voxel_size[d]; gd->rvs[d] = r; }
         gd->g[d] = (int)g;
         gd->gf[d] = (float)gd->g[d];
         cells *= gd->g[d];
@@ -428,7 +430,9 @@ struct DynPlan {
     Plan pl;
     long long Gp, acap;
     int W1;
-    size_t o_coarse, o_fine, o_gpre, o_sgrp, o_cell, o_pslot, o_part, o_ssb, bytes;
+    size_t o_coarse, o_fine, o_gpre, o_cell, o_pslot, o_part, o_ssb, o_stamps, o_acc, bytes;
+    uint32_t w1p;
+    int acc_vec;
 };
 constexpr int kDynMaxCtas = 4096;
 
@@ -447,16 +451,29 @@ int make_dyn_plan(const rpc_voxel_cfg *cfg, const GridDesc &gd, int B, const int
     dp->acap = dp->pl.ntotal < groups ? dp->pl.ntotal : groups;
     if (dp->acap < 1) dp->acap = 1;
     size_t o = 0;
-    dp->o_coarse = o; o += align_up(8 * (size_t)dp->W1);
+    dp->w1p = 1;
+    while (dp->w1p < (uint32_t)dp->W1) dp->w1p <<= 1;
+    dp->o_coarse = o; o += align_up(8 * (size_t)dp->w1p);
     dp->o_fine = o;   o += align_up(32 * (size_t)dp->acap);
     dp->o_gpre = o;   o += align_up(4 * (size_t)dp->acap);
-    dp->o_sgrp = o;   o += align_up(4 * (size_t)dp->acap);
     dp->o_cell = o;   o += align_up(4 * (size_t)dp->pl.ntotal);
     dp->o_pslot = o;  o += align_up(4 * (size_t)dp->pl.ntotal);
     dp->o_part = o;   o += align_up(4 * 2 * (size_t)kDynMaxCtas);
     dp->o_ssb = o;    o += align_up(4 * (RPC_MAX_BATCH + 1));
+    dp->o_stamps = o; o += align_up(8 * 32 * (size_t)kDynMaxCtas);
+    dp->acc_vec = (cfg->F + 1 + 3) / 4;
+    dp->o_acc = o;    o += align_up(16 * (size_t)dp->acc_vec * (size_t)(dp->pl.ntotal > 0 ? dp->pl.ntotal : 1));
     dp->bytes = o;
     return RPC_OK;
+}
+
+// n / d for n < 2^31 as (umulhi(n, mg) + n) >> sh
+void fast_div_magic(uint32_t d, uint32_t *mg, uint32_t *sh)
+{
+    uint32_t s = 0;
+    while ((1ull << s) < d) ++s;
+    *sh = s;
+    *mg = (uint32_t)((((1ull << s) - d) << 32) / d + 1);
 }
 
 template <int C, bool PERTURB>
@@ -465,9 +482,18 @@ int launch_dyn_t(DynParams &p, cudaStream_t st)
     auto kern = k_dyn_scatter<C, PERTURB>;
     int grid = device_sms() * kDynCtasPerSM;
     if (grid > kDynMaxCtas) grid = kDynMaxCtas;
+    const size_t smem = C == 4 ? 0 : (size_t)(kDynThreads / 32) * (PERTURB ? 2 : 1) * 32 * C * sizeof(float);
+    static bool attr_done[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && dev >= 0 && dev < 64 && !attr_done[dev]) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return RPC_ERR_CUDA;
+        attr_done[dev] = true;
+    }
     void *args[] = {&p};
     g_prof.begin(st);
-    if (cudaLaunchCooperativeKernel((void *)kern, dim3(grid), dim3(kDynThreads), args, 0, st) != cudaSuccess)
+    if (cudaLaunchCooperativeKernel((void *)kern, dim3(grid), dim3(kDynThreads), args, smem, st) != cudaSuccess)
         return RPC_ERR_CUDA;
     g_prof.stage("k_dyn_scatter", st);
     return RPC_OK;
@@ -484,6 +510,14 @@ RPC_API size_t rpc_dynamic_workspace_bytes(const rpc_voxel_cfg *cfg, int B, cons
     return dp.bytes;
 }
 
+RPC_API int64_t rpc_dynamic_stamps_offset(const rpc_voxel_cfg *cfg, int B, const int32_t *n_per_sample)
+{
+    GridDesc gd;
+    DynPlan dp;
+    if (check_cfg(cfg, false) || make_grid(cfg, &gd) || make_dyn_plan(cfg, gd, B, n_per_sample, &dp)) return -1;
+    return (int64_t)dp.o_stamps;
+}
+
 RPC_API int rpc_dynamic_scatter_mean_fwd(const rpc_voxel_cfg *cfg, const float *points,
                                          const int32_t *n_per_sample, int B, const float *raw,
                                          const rpc_perturb_cfg *pc, const int32_t *coors_in, int32_t *coors_out,
@@ -497,6 +531,7 @@ RPC_API int rpc_dynamic_scatter_mean_fwd(const rpc_voxel_cfg *cfg, const float *
     if ((st = make_grid(cfg, &gd))) return st;
     DynPlan dp;
     if ((st = make_dyn_plan(cfg, gd, B, n_per_sample, &dp))) return st;
+    if (dp.pl.ntotal > (1 << 24)) return RPC_ERR_TOO_LARGE;         // per-voxel counts ride in fp32 accumulators
     if (!voxel_num || !workspace) return RPC_ERR_NULL;
     if (dp.pl.ntotal > 0 && (!points || !point2voxel || !feats || !voxel_coors || !num_points)) return RPC_ERR_NULL;
     if (raw && !pc) return RPC_ERR_NULL;
@@ -511,11 +546,16 @@ RPC_API int rpc_dynamic_scatter_mean_fwd(const rpc_voxel_cfg *cfg, const float *
     p.coarse = reinterpret_cast<uint2 *>(w + dp.o_coarse);
     p.fine = reinterpret_cast<uint32_t *>(w + dp.o_fine);
     p.gpre = reinterpret_cast<uint32_t *>(w + dp.o_gpre);
-    p.slot_grp = reinterpret_cast<int *>(w + dp.o_sgrp);
     p.cell = reinterpret_cast<int *>(w + dp.o_cell);
     p.pslot = reinterpret_cast<int *>(w + dp.o_pslot);
     p.part = reinterpret_cast<uint32_t *>(w + dp.o_part);
     p.ssb = reinterpret_cast<int *>(w + dp.o_ssb);
+    p.acc = reinterpret_cast<float4 *>(w + dp.o_acc);
+    p.acc_vec = dp.acc_vec;
+    p.w1_mask = dp.w1p - 1;
+    fast_div_magic((uint32_t)gd.g[0] * (uint32_t)gd.g[1], &p.mg_gxy, &p.sh_gxy);
+    fast_div_magic((uint32_t)gd.g[0], &p.mg_gx, &p.sh_gx);
+    p.stamps = g_prof.on ? reinterpret_cast<unsigned long long *>(w + dp.o_stamps) : nullptr;
     p.Gp = dp.Gp; p.W1 = dp.W1; p.ntotal = (int)dp.pl.ntotal;
     p.gd = gd; p.bd = dp.pl.bd;
     fill_perturb(cfg, pc, &p.pd);

@@ -20,6 +20,7 @@ constexpr int kInf = 0x7FFFFFFF;     // "no point" in the per-voxel slot lists
 struct GridDesc {
     float lo[3];      // x, y, z lower bounds
     float vs[3];      // voxel sizes
+    float rvs[3];     // RN(1 / vs): quotient estimate of axis_cell
     float gf[3];      // grid extents as float (comparison is done in fp32 like mmcv's int compare)
     int g[3];         // grid extents gx, gy, gz
     int P, V, C, F;
@@ -68,19 +69,31 @@ __device__ __forceinline__ bool perturb_pass(float raw, float eb, float fb)
 
 // one coordinate -> cell index along axis d, or -1 (mmcv dynamic_voxelize_forward_cpu_kernel:
 // c = floor((p - lo) / vs); fail if c < 0 or c >= grid; NaN fails).
-__device__ __forceinline__ int axis_cell(float p, float lo, float vs, float gf)
+//
+// The IEEE division is a ~40-instruction routine and three of them per point are a visible share of the
+// point-parallel phases, so the quotient is first estimated as q = (p - lo) * RN(1 / vs).  q differs from
+// RN((p - lo) / vs) by at most 3 * 2^-24 |q|; whenever q is farther than 4 * 2^-23 |q| from an integer the
+// two floors are equal and the estimate is used, otherwise (and for NaN / inf / |q| >= 2^22) the true
+// division decides.  Results are bit-identical to the division-only form.
+__device__ __forceinline__ int axis_cell(float p, const GridDesc &gd, int d)
 {
-    float f = floorf(__fdiv_rn(__fsub_rn(p, lo), vs));
-    if (!(f >= 0.0f) || !(f < gf)) return -1;
+    const float a = __fsub_rn(p, gd.lo[d]);
+    const float q = __fmul_rn(a, gd.rvs[d]);
+    float f = floorf(q);
+    const float frac = __fsub_rn(q, f);                         // exact, in [0, 1)
+    const float tol = __fmul_rn(fabsf(q), 4.8e-7f);
+    if (!(frac > tol && __fsub_rn(1.0f, frac) > tol) || !(fabsf(q) < 4194304.0f))
+        f = floorf(__fdiv_rn(a, gd.vs[d]));
+    if (!(f >= 0.0f) || !(f < gd.gf[d])) return -1;
     return (int)f;
 }
 
 // (x,y,z) -> linear cell id (z*gy + y)*gx + x, or -1 when the point is dropped
 __device__ __forceinline__ int point_cell(float x, float y, float z, const GridDesc &gd)
 {
-    int cx = axis_cell(x, gd.lo[0], gd.vs[0], gd.gf[0]);
-    int cy = axis_cell(y, gd.lo[1], gd.vs[1], gd.gf[1]);
-    int cz = axis_cell(z, gd.lo[2], gd.vs[2], gd.gf[2]);
+    int cx = axis_cell(x, gd, 0);
+    int cy = axis_cell(y, gd, 1);
+    int cz = axis_cell(z, gd, 2);
     if ((cx | cy | cz) < 0) return -1;
     return (cz * gd.g[1] + cy) * gd.g[0] + cx;
 }

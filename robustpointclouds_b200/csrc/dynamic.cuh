@@ -19,9 +19,9 @@ k_dynamic_voxelize(const float *__restrict__ pts, const float *__restrict__ raw,
     for (int i = blockIdx.x * kThreads + threadIdx.x; i < ntotal; i += gridDim.x * kThreads) {
         float x, y, z;
         load_xyz<C, PERTURB>(pts, raw, pd, i, x, y, z);
-        int cx = axis_cell(x, gd.lo[0], gd.vs[0], gd.gf[0]);
-        int cy = axis_cell(y, gd.lo[1], gd.vs[1], gd.gf[1]);
-        int cz = axis_cell(z, gd.lo[2], gd.vs[2], gd.gf[2]);
+        int cx = axis_cell(x, gd, 0);
+        int cy = axis_cell(y, gd, 1);
+        int cz = axis_cell(z, gd, 2);
         if ((cx | cy | cz) < 0) cx = cy = cz = -1;
         if constexpr (NCOL == 4) {
             int b = 0;

@@ -547,9 +547,9 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             }
             if (tid < nv) {
                 const float *f0 = tile + (int64_t)tid * P * C;            // the voxel's first point
-                const int cx = axis_cell(f0[0], p.gd.lo[0], p.gd.vs[0], p.gd.gf[0]);
-                const int cy = axis_cell(f0[1], p.gd.lo[1], p.gd.vs[1], p.gd.gf[1]);
-                const int cz = axis_cell(f0[2], p.gd.lo[2], p.gd.vs[2], p.gd.gf[2]);
+                const int cx = axis_cell(f0[0], p.gd, 0);
+                const int cy = axis_cell(f0[1], p.gd, 1);
+                const int cz = axis_cell(f0[2], p.gd, 2);
                 int b = 0;
                 while (b + 1 < p.bd.B && v0 + tid >= s_voff[b + 1]) ++b;
                 reinterpret_cast<int4 *>(p.coors)[v0 + tid] = make_int4(b, cz, cy, cx);

@@ -262,6 +262,21 @@ def phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Option
     return {PHASES[k]: (st[k + 1] - st[k]) / 1e3 for k in range(6)}
 
 
+DYN_PHASES = ("clear", "mark", "coarse_sums", "coarse_scan", "fine_bits", "fine_sums", "rank", "sum", "mean")
+
+
+def dyn_phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Optional[torch.Tensor] = None,
+                       dev: Optional[torch.device] = None):
+    """{phase: us} of the most recent profiled ``dynamic_scatter_mean`` call (host sync)"""
+    n_arr = _lib.counts(n_per_sample)
+    off = _lib.lib().rpc_dynamic_stamps_offset(ctypes.byref(cfg), len(n_per_sample), n_arr)
+    if off < 0:
+        raise _lib.RpcError(-2, "rpc_dynamic_stamps_offset")
+    ws = workspace if workspace is not None else _default_ws._buf[dev]
+    st = ws[off:off + 80].view(torch.int64).cpu().tolist()
+    return {DYN_PHASES[k]: (st[k + 1] - st[k]) / 1e3 for k in range(9)}
+
+
 # ------------------------------------------------------------------------------------------------
 # reference-order composition (perturb the kept points inside the padded voxel tensor)
 # ------------------------------------------------------------------------------------------------

@@ -11,6 +11,8 @@ from __future__ import annotations
 
 from typing import Dict, Sequence
 
+import os
+
 import numpy as np
 
 KITTI = dict(name="kitti", voxel_size=[0.05, 0.05, 0.1], point_cloud_range=[0, -40, -3, 70.4, 40, 1],
@@ -52,7 +54,7 @@ def _lidar(rng: np.random.Generator, N: int, C: int, beams: int, elev, sensor_h:
         pts = pts.reshape(beams, cols, C).transpose(1, 0, 2).reshape(-1, C)[:per]
         out.append(pts)
     pts = np.concatenate(out)[:N]
-    null = rng.uniform(size=pts.shape[0]) < 0.005
+    null = rng.uniform(size=pts.shape[0]) < float(os.environ.get("RPC_SYNTH_NULL", "0.005"))
     pts[null] = 0.0
     return np.ascontiguousarray(pts, np.float32)
 
