@@ -11,7 +11,7 @@ import os
 from typing import Optional, Sequence
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librpc_b200.so")
+LIB_PATH = os.environ.get("RPC_B200_LIB") or os.path.join(_HERE, "librpc_b200.so")   # override: kernel experiments
 
 RPC_MAX_BATCH = 32
 RPC_MAX_CHANNELS = 8

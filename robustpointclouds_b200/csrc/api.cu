@@ -59,7 +59,7 @@ struct Plan {                                     // host-side layout of one bat
     size_t o_tab, o_hslot, o_tiles, o_slots, o_stamps, bytes;
 };
 
-// Tiles are kPT consecutive points of one sweep; tables hold 1.5 entries per point (worst-case load
+// Tiles are kTile consecutive points of one sweep; tables hold 1.5 entries per point (worst-case load
 // 0.67 when every point is its own cell; ~0.3 on LiDAR sweeps).
 int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
 {
@@ -79,7 +79,7 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
         pl->bd.tab_size[b] = (uint32_t)sz;
         tab += sz;
         pts += n[b];
-        tiles += (n[b] + kPT - 1) / kPT;
+        tiles += (n[b] + kTile - 1) / kTile;
         cap += n[b] < cfg->max_voxels ? n[b] : cfg->max_voxels;
         if (pts > 0x3FFFFFF0LL || tab > 0x3FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // bits 30, 31 of hslot are flags
     }
@@ -91,7 +91,7 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
     size_t o = 0;
     pl->o_tab = o;   o += align_up(8 * (size_t)tab);
     pl->o_hslot = o; o += align_up(4 * (size_t)pts);
-    pl->o_tiles = o; o += align_up(4 * (size_t)(tiles + 1));
+    pl->o_tiles = o; o += align_up(4 * (size_t)(tiles + 2));       // + the gather task counter
     pl->o_slots = o; o += align_up(4 * (size_t)cap * cfg->max_points);
     pl->o_stamps = o; o += align_up(8 * 16 * 1024);
     pl->bytes = o;
@@ -146,24 +146,6 @@ struct Profiler {
 
 inline bool misaligned(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) != 0; }
 
-// rows of voxels per iteration of the gather phase: at most kGatherSlots (voxel, slot) pairs, spread
-// over the CTAs when the batch is small, multiple of 4 so that every tile starts 16-byte aligned
-int pick_vb(int P, int C, int64_t cap, int n_cta, size_t *smem)
-{
-    int64_t vb = (cap + n_cta - 1) / n_cta;
-    if (vb > kGatherSlots / P) vb = kGatherSlots / P;
-    vb = (vb + 3) & ~int64_t(3);
-    if (vb > kPT) vb = kPT;                                       // one thread per voxel for the counts
-    if (vb < 4) vb = 4;
-    if (vb * P > 65535) return 0;                                 // kept-row list is 16 bit
-    // slot indices, tile, counts, prefix, kept-row list
-    const size_t bytes = (size_t)vb * P * sizeof(int) + (size_t)vb * P * C * sizeof(float) +
-                         2 * (size_t)vb * sizeof(int) + (size_t)vb * P * sizeof(unsigned short) + 16;
-    if (bytes > 200 * 1024 / kCtasPerSM) return 0;
-    *smem = bytes;
-    return (int)vb;
-}
-
 template <int C, bool PERTURB>
 int launch_hard_t(FwdParams &fp, size_t smem, cudaStream_t st)
 {
@@ -192,8 +174,12 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
 {
     FwdParams fp;
     size_t smem = 0;
-    fp.VB = pick_vb(gd.P, C, pl.cap, device_sms() * kCtasPerSM, &smem);
-    if (!fp.VB) return RPC_ERR_CONFIG;
+    // P5: slot lists of VT voxels per warp in shared memory; VT = 32 unless max_points is large
+    fp.VT = 32;
+    while (fp.VT > 4 && (size_t)(kPT / 32) * fp.VT * gd.P * sizeof(int) > 200 * 1024 / kCtasPerSM) fp.VT >>= 1;
+    fp.gather_stride = fp.VT * gd.P;
+    smem = (size_t)(kPT / 32) * fp.gather_stride * sizeof(int);
+    if (smem > 200 * 1024 / kCtasPerSM) return RPC_ERR_CONFIG;         // max_points > 195
     const size_t scan_bytes = 4 * (size_t)(pl.ntiles + 1);          // P3's prefix array shares the buffer
     if (smem < scan_bytes) smem = scan_bytes;
     char *w = static_cast<char *>(workspace);
@@ -329,8 +315,8 @@ RPC_API int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats,
     if (misaligned(grad_feats) || misaligned(raw) || misaligned(grad_raw)) return RPC_ERR_ALIGN;
     PerturbDesc pd;
     fill_perturb(cfg, pc, &pd);
-    int64_t blocks = (ntotal + kThreads - 1) / kThreads;
-    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
+    int64_t blocks = (ntotal + (int64_t)kThreads * kBwdIlp - 1) / ((int64_t)kThreads * kBwdIlp);
+    if (blocks > kNumSM * 8) blocks = kNumSM * 8;                   // 8 x 256 threads per SM, one wave
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     g_prof.begin(s);
     switch (cfg->C) {

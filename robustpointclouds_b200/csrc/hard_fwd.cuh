@@ -32,11 +32,11 @@ namespace cg = cooperative_groups;
 
 namespace rpc {
 
-constexpr int kPT = 1024;                       // threads per CTA of the persistent kernel = points per tile
-constexpr int kKB = 1;                          // tiles a CTA keeps in flight in the unordered phases
+constexpr int kPT = 1024;                       // threads per CTA of the persistent kernel
+constexpr int kTile = 256;                      // points per tile: the unit that is dealt to the CTAs
+constexpr int kSub = kPT / kTile;               // tiles a CTA works on per iteration (8 warps each)
 constexpr int kCtasPerSM = 2;                   // resident CTAs per SM (register cap 32 at 1024 threads)
-constexpr int kMaxTiles = 32768;                // tile counts are scanned in shared memory (128 KB)
-constexpr int kGatherSlots = 2048;              // (voxel, slot) pairs per gather iteration
+constexpr int kMaxTiles = 24576;                // tile counts are scanned in shared memory (96 KB per CTA)
 constexpr uint32_t kDropped = 0xFFFFFFFFu;      // hslot: point outside the range
 constexpr uint32_t kFirstBit = 0x80000000u;     // hslot: point is the first of its cell (set in P2)
 constexpr uint32_t kCandBit = 0x40000000u;      // hslot: point may be the first of its cell (set in P1)
@@ -53,7 +53,7 @@ struct FwdParams {
     float *voxels; int *coors; int *num_points; int *voxel_num; int *p2v; int *p2s; float *feats;
     unsigned long long *stamps;                 // [gridDim][16] %globaltimer per CTA and phase, or NULL
     long long tab_total;
-    int ntiles, VB;
+    int ntiles, VT, gather_stride;               // VT: voxel rows per gather task (one warp); floats of smem per warp
     GridDesc gd;
     BatchDesc bd;
     PerturbDesc pd;
@@ -99,8 +99,8 @@ __device__ __forceinline__ TileRange tile_range(const FwdParams &p, int tile)
 {
     TileRange r;
     r.b = tile_to_sweep(p.bd, tile);
-    r.begin = p.bd.pt_begin[r.b] + (tile - p.bd.tile_begin[r.b]) * kPT;
-    r.end = min(r.begin + kPT, p.bd.pt_begin[r.b + 1]);
+    r.begin = p.bd.pt_begin[r.b] + (tile - p.bd.tile_begin[r.b]) * kTile;
+    r.end = min(r.begin + kTile, p.bd.pt_begin[r.b + 1]);
     return r;
 }
 
@@ -114,36 +114,38 @@ __device__ __forceinline__ uint32_t probe_start(uint32_t cell, uint32_t size)
     return __umulhi(h, size);
 }
 
-// For kKB tiles at once: exclusive rank of every flagged thread within its tile (thread order = point
-// order) and the tile totals.  sm: kKB * 33 ints.
-__device__ __forceinline__ void block_rank_flags(const bool f[kKB], int rank[kKB], int total[kKB], int *sm)
+// Tiles are dealt round-robin: CTA c owns tiles c, c + G, c + 2G, ... (G = gridDim.x) and works on kSub of
+// them per iteration, one per group of 8 warps, thread order = point order inside the tile.  With 256-point
+// tiles every CTA gets the same number of tiles to within one (a 1024-point unit left 3-versus-2 tile
+// shares on a KITTI batch: the grid barriers then waited for the unlucky CTAs in every phase).
+__device__ __forceinline__ int cta_iterations(int ntiles)
+{
+    const int mine = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    return (mine + kSub - 1) / kSub;
+}
+__device__ __forceinline__ int my_tile(int ntiles, int it)
+{
+    const int t = (int)blockIdx.x + (it * kSub + (int)(threadIdx.x >> 8)) * (int)gridDim.x;
+    return t < ntiles ? t : -1;
+}
+
+// exclusive rank of every flagged thread within its tile (8 warps) and the tile total.  sm: 32 ints.
+__device__ __forceinline__ void tile_rank_flags(bool f, int &rank, int &total, int *sm)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t bal[kKB];
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, f);
+    if (lane == 0) sm[warp] = __popc(bal);
+    __syncthreads();
+    int pre = 0, tot = 0;
 #pragma unroll
-    for (int k = 0; k < kKB; ++k) {
-        bal[k] = __ballot_sync(0xFFFFFFFFu, f[k]);
-        if (lane == 0) sm[k * 33 + warp] = __popc(bal[k]);
+    for (int j = 0; j < 8; ++j) {
+        const int c = sm[(warp & ~7) + j];
+        pre += j < (warp & 7) ? c : 0;
+        tot += c;
     }
     __syncthreads();
-    if (warp < kKB) {                            // kKB <= 32 warps
-        const int w = sm[warp * 33 + lane];
-        int incl = w;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        sm[warp * 33 + lane] = incl - w;
-        if (lane == 31) sm[warp * 33 + 32] = incl;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kKB; ++k) {
-        rank[k] = sm[k * 33 + warp] + __popc(bal[k] & ((1u << lane) - 1u));
-        total[k] = sm[k * 33 + 32];
-    }
-    __syncthreads();
+    rank = pre + __popc(bal & ((1u << lane) - 1u));
+    total = tot;
 }
 
 template <int C, bool PERTURB>
@@ -152,7 +154,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
 {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char dyn_sm[];     // P3: int prefix[ntiles]; P5: gather tile
-    __shared__ int sm[kKB * 33];
+    __shared__ int sm[33];
     __shared__ int s_voff[RPC_MAX_BATCH + 1];                   // first voxel row of each sweep, then M
     const int tid = threadIdx.x;
     const int P = p.gd.P, V = p.gd.V;
@@ -161,10 +163,13 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // ------------------------------------------------------------------------------- P0 clear
     stamp(p, 0);
     // pull this CTA's point / perturbation tiles into L2 while the table is being cleared
-    for (int tile = blockIdx.x; tile < p.ntiles; tile += nct) {
+    const int iters = cta_iterations(p.ntiles);
+    for (int it = 0; it < iters; ++it) {
+        const int tile = my_tile(p.ntiles, it);
+        if (tile < 0) continue;
         const TileRange tr = tile_range(p, tile);
         const size_t b0 = (size_t)tr.begin * C * 4, b1 = (size_t)tr.end * C * 4;
-        for (size_t o = (b0 & ~size_t(127)) + (size_t)tid * 128; o < b1; o += (size_t)kPT * 128) {
+        for (size_t o = (b0 & ~size_t(127)) + (size_t)(tid & (kTile - 1)) * 128; o < b1; o += (size_t)kTile * 128) {
             asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(p.pts) + o));
             if constexpr (PERTURB)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(p.raw) + o));
@@ -182,121 +187,60 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 1);
 
     // ------------------------------------------------------------------------------- P1 insert
-    // thread t owns point t of kKB tiles (blockIdx.x + k*gridDim.x ...) at once.  The SM issues in
-    // order, so every step is written as "issue kKB independent memory operations, then consume them":
-    // coordinate loads -> cells; 32-byte bucket loads -> local scan; CAS only where a slot looked empty.
-    for (int t0 = blockIdx.x; t0 < p.ntiles; t0 += kKB * nct) {
-        int cell[kKB], idx[kKB];
-        uint32_t bkt[kKB], off[kKB], nb[kKB];
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            const int tile = t0 + k * nct;
-            idx[k] = -1; off[k] = 0; nb[k] = 1;
-            if (tile < p.ntiles) {
-                const TileRange tr = tile_range(p, tile);
-                if (tr.begin + tid < tr.end) {
-                    idx[k] = tr.begin + tid;
-                    off[k] = p.bd.tab_off[tr.b]; nb[k] = p.bd.tab_size[tr.b] >> 2;
-                }
+    // coordinate loads -> cell; 32-byte bucket load -> local scan; CAS only where a slot looked empty,
+    // atomicMin only where the holder has a larger index
+    for (int it = 0; it < iters; ++it) {
+        const int tile = my_tile(p.ntiles, it);
+        int idx = -1, cell = -1;
+        uint32_t off = 0, nb = 1;
+        if (tile >= 0) {
+            const TileRange tr = tile_range(p, tile);
+            if (tr.begin + (tid & (kTile - 1)) < tr.end) {
+                idx = tr.begin + (tid & (kTile - 1));
+                off = p.bd.tab_off[tr.b]; nb = p.bd.tab_size[tr.b] >> 2;
             }
         }
-        {
-            float xyz[kKB][3], d[kKB][3];
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                const int i = max(idx[k], 0);                       // tail threads re-read row 0 (unused)
-                if constexpr (C == 4) {
-                    const float4 v = __ldg(reinterpret_cast<const float4 *>(p.pts) + i);
-                    xyz[k][0] = v.x; xyz[k][1] = v.y; xyz[k][2] = v.z;
-                    if constexpr (PERTURB) {
-                        const float4 r = __ldg(reinterpret_cast<const float4 *>(p.raw) + i);
-                        d[k][0] = r.x; d[k][1] = r.y; d[k][2] = r.z;
-                    }
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        xyz[k][c] = __ldg(p.pts + (int64_t)i * C + c);
-                        if constexpr (PERTURB) d[k][c] = __ldg(p.raw + (int64_t)i * C + c);
-                    }
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                if constexpr (PERTURB) {
-#pragma unroll
-                    for (int c = 0; c < 3; ++c)
-                        xyz[k][c] = __fadd_rn(xyz[k][c], perturb_delta(d[k][c], p.pd.eb[c], p.pd.fb[c]));
-                }
-                cell[k] = idx[k] >= 0 ? point_cell(xyz[k][0], xyz[k][1], xyz[k][2], p.gd) : -1;
-            }
+        if (idx >= 0) {
+            float x, y, z;
+            load_xyz<C, PERTURB>(p.pts, p.raw, p.pd, idx, x, y, z);
+            cell = point_cell(x, y, z, p.gd);
+            if (p.p2v) p.p2v[idx] = -1;
+            if (p.p2s) p.p2s[idx] = -1;
+            if (cell < 0) p.hslot[idx] = kDropped;
         }
+        if (p.stamps && it == 0) { __syncthreads(); stamp(p, 13); }
+        uint32_t bkt = cell >= 0 ? probe_start((uint32_t)cell, nb) : 0u;
+        int j0 = 0;                                                  // first slot of the bucket still to look at
+        bool pend = cell >= 0;
+        while (pend) {
+            const ulonglong2 *bp = reinterpret_cast<const ulonglong2 *>(p.tab + off + 4 * bkt);
+            const ulonglong2 e01 = __ldcg(bp), e23 = __ldcg(bp + 1);
+            const unsigned long long e[4] = {e01.x, e01.y, e23.x, e23.y};
+            int j = 4;
 #pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            if (idx[k] < 0) continue;
-            if (p.p2v) p.p2v[idx[k]] = -1;
-            if (p.p2s) p.p2s[idx[k]] = -1;
-            if (cell[k] < 0) p.hslot[idx[k]] = kDropped;
-            else bkt[k] = probe_start((uint32_t)cell[k], nb[k]);
-        }
-        if (p.stamps && t0 == blockIdx.x) { __syncthreads(); stamp(p, 13); }
-        int j0[kKB];                                                // first slot of the bucket still to look at
-        bool pend[kKB];
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) { pend[k] = cell[k] >= 0; j0[k] = 0; }
-        for (;;) {
-            bool any = false;
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) any |= pend[k];
-            if (!any) break;
-            ulonglong2 e01[kKB], e23[kKB];
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                if (!pend[k]) continue;
-                const ulonglong2 *bp = reinterpret_cast<const ulonglong2 *>(p.tab + off[k] + 4 * bkt[k]);
-                e01[k] = __ldcg(bp); e23[k] = __ldcg(bp + 1);
-            }
-            int jc[kKB];                                            // slot to CAS, or -1
-            unsigned long long old[kKB];
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                jc[k] = -1;
-                if (!pend[k]) continue;
-                const unsigned long long e[4] = {e01[k].x, e01[k].y, e23[k].x, e23[k].y};
-                int j = 4;
-#pragma unroll
-                for (int q = 3; q >= 0; --q)
-                    if (q >= j0[k] && (e[q] == kEmpty64 || (uint32_t)(e[q] >> 32) == (uint32_t)cell[k])) j = q;
-                if (j == 4) { bkt[k] = bkt[k] + 1 == nb[k] ? 0 : bkt[k] + 1; j0[k] = 0; continue; }
-                const unsigned long long ej = j == 0 ? e[0] : j == 1 ? e[1] : j == 2 ? e[2] : e[3];
-                j0[k] = j;
-                if (ej == kEmpty64) { jc[k] = j; continue; }
-                old[k] = ej;                                         // the cell's entry, no atomic needed to find it
-                jc[k] = -2;
-            }
-#pragma unroll
-            for (int k = 0; k < kKB; ++k)
-                if (jc[k] >= 0)
-                    old[k] = atomicCAS(&p.tab[off[k] + 4 * bkt[k] + jc[k]], kEmpty64,
-                                       ((unsigned long long)(uint32_t)cell[k] << 32) | (uint32_t)idx[k]);
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                if (jc[k] == -1) continue;
-                const uint32_t i = (uint32_t)idx[k];
-                if (old[k] != kEmpty64 && (uint32_t)(old[k] >> 32) != (uint32_t)cell[k]) {
-                    j0[k] += 1;                                      // lost the slot to another cell
-                    if (j0[k] == 4) { bkt[k] = bkt[k] + 1 == nb[k] ? 0 : bkt[k] + 1; j0[k] = 0; }
+            for (int q = 3; q >= 0; --q)
+                if (q >= j0 && (e[q] == kEmpty64 || (uint32_t)(e[q] >> 32) == (uint32_t)cell)) j = q;
+            if (j == 4) { bkt = bkt + 1 == nb ? 0 : bkt + 1; j0 = 0; continue; }
+            unsigned long long old = j == 0 ? e[0] : j == 1 ? e[1] : j == 2 ? e[2] : e[3];
+            j0 = j;
+            const unsigned long long mine = ((unsigned long long)(uint32_t)cell << 32) | (uint32_t)idx;
+            if (old == kEmpty64) {
+                old = atomicCAS(&p.tab[off + 4 * bkt + j], kEmpty64, mine);
+                if (old != kEmpty64 && (uint32_t)(old >> 32) != (uint32_t)cell) {
+                    j0 += 1;                                         // lost the slot to another cell
+                    if (j0 == 4) { bkt = bkt + 1 == nb ? 0 : bkt + 1; j0 = 0; }
                     continue;
                 }
-                uint32_t h = off[k] + 4 * bkt[k] + j0[k];
-                if (old[k] == kEmpty64) {
-                    h |= kCandBit;                                   // claimed: first so far
-                } else if ((uint32_t)old[k] > i) {
-                    atomicMin(&p.tab[h], ((unsigned long long)(uint32_t)cell[k] << 32) | i);
-                    h |= kCandBit;                                   // displaced a later point
-                }
-                p.hslot[i] = h;
-                pend[k] = false;
             }
+            uint32_t h = off + 4 * bkt + j0;
+            if (old == kEmpty64) {
+                h |= kCandBit;                                       // claimed: first so far
+            } else if ((uint32_t)old > (uint32_t)idx) {
+                atomicMin(&p.tab[h], mine);
+                h |= kCandBit;                                       // displaced a later point
+            }
+            p.hslot[idx] = h;
+            pend = false;
         }
     }
     if (p.stamps) __syncthreads();
@@ -305,35 +249,21 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 2);
 
     // ------------------------------------------------------------------------------- P2 flag
-    // thread t owns point t of the tile (thread order = point order, which the scan of P3 needs)
-    for (int t0 = blockIdx.x; t0 < p.ntiles; t0 += kKB * nct) {
-        uint32_t hs[kKB];
-        int idx[kKB];
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            const int tile = t0 + k * nct;
-            hs[k] = kDropped; idx[k] = -1;
-            if (tile < p.ntiles) {
-                const TileRange tr = tile_range(p, tile);
-                if (tr.begin + tid < tr.end) { idx[k] = tr.begin + tid; hs[k] = __ldcg(p.hslot + idx[k]); }
-            }
+    // thread order = point order inside the tile, which the scan of P3 needs
+    for (int it = 0; it < iters; ++it) {
+        const int tile = my_tile(p.ntiles, it);
+        uint32_t hs = kDropped;
+        int idx = -1;
+        if (tile >= 0) {
+            const TileRange tr = tile_range(p, tile);
+            if (tr.begin + (tid & (kTile - 1)) < tr.end) { idx = tr.begin + (tid & (kTile - 1)); hs = __ldcg(p.hslot + idx); }
         }
-        uint32_t lo[kKB];
-#pragma unroll
-        for (int k = 0; k < kKB; ++k)
-            lo[k] = (hs[k] != kDropped && (hs[k] & kCandBit)) ? (uint32_t)__ldcg(p.tab + (hs[k] & kEntryMask))
-                                                              : 0xFFFFFFFEu;
-        bool f[kKB];
-        int rank[kKB], total[kKB];
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            f[k] = lo[k] == (uint32_t)idx[k];
-            if (f[k]) p.hslot[idx[k]] = hs[k] | kFirstBit;
-        }
-        block_rank_flags(f, rank, total, sm);
-#pragma unroll
-        for (int k = 0; k < kKB; ++k)
-            if (tid == k && t0 + k * nct < p.ntiles) p.tile_cnt[t0 + k * nct] = total[k];
+        const uint32_t lo = (hs != kDropped && (hs & kCandBit)) ? (uint32_t)__ldcg(p.tab + (hs & kEntryMask)) : 0xFFFFFFFEu;
+        const bool f = lo == (uint32_t)idx;
+        if (f) p.hslot[idx] = hs | kFirstBit;
+        int rank, total;
+        tile_rank_flags(f, rank, total, sm);
+        if ((tid & (kTile - 1)) == 0 && tile >= 0) p.tile_cnt[tile] = total;
     }
     if (p.stamps) __syncthreads();
     stamp(p, 10);
@@ -367,40 +297,35 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         __syncthreads();
     }
-    for (int t0 = blockIdx.x; t0 < p.ntiles; t0 += kKB * nct) {
-        uint32_t hs[kKB];
-        int idx[kKB], base[kKB], voff[kKB];
-        bool f[kKB];
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            const int tile = t0 + k * nct;
-            hs[k] = kDropped; idx[k] = -1; base[k] = 0; voff[k] = 0;
-            if (tile < p.ntiles) {
-                const TileRange tr = tile_range(p, tile);
-                base[k] = prefix[tile] - prefix[p.bd.tile_begin[tr.b]];
-                voff[k] = s_voff[tr.b];
-                if (tr.begin + tid < tr.end) { idx[k] = tr.begin + tid; hs[k] = __ldcg(p.hslot + idx[k]); }
-            }
-            f[k] = hs[k] != kDropped && (hs[k] & kFirstBit);
+    for (int it = 0; it < iters; ++it) {
+        const int tile = my_tile(p.ntiles, it);
+        uint32_t hs = kDropped;
+        int idx = -1, base = 0, voff = 0;
+        if (tile >= 0) {
+            const TileRange tr = tile_range(p, tile);
+            base = prefix[tile] - prefix[p.bd.tile_begin[tr.b]];
+            voff = s_voff[tr.b];
+            if (tr.begin + (tid & (kTile - 1)) < tr.end) { idx = tr.begin + (tid & (kTile - 1)); hs = __ldcg(p.hslot + idx); }
         }
-        int rank[kKB], total[kKB];
-        block_rank_flags(f, rank, total, sm);
+        const bool f = hs != kDropped && (hs & kFirstBit);
+        int rank, total;
+        tile_rank_flags(f, rank, total, sm);
         // slot lists of the tile's admitted voxels: rows [voff+base, voff+min(base+total, V)) := kInf
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            const int r0 = min(base[k], V), r1 = min(base[k] + total[k], V);
-            int *sl = p.slots + (int64_t)(voff[k] + r0) * P;
-            for (int t = tid; t < (r1 - r0) * P; t += kPT) sl[t] = kInf;
+        {
+            const int r0 = min(base, V), r1 = min(base + total, V);
+            int *sl = p.slots + (int64_t)(voff + r0) * P;
+            for (int t = tid & (kTile - 1); t < (r1 - r0) * P; t += kTile) sl[t] = kInf;
         }
         __syncthreads();
-#pragma unroll
-        for (int k = 0; k < kKB; ++k) {
-            if (!f[k]) continue;
-            const int r = base[k] + rank[k];
-            uint32_t *lo = reinterpret_cast<uint32_t *>(p.tab + (hs[k] & kEntryMask));   // low word
-            if (r >= V) { *lo = kRefused; continue; }
-            *lo = (uint32_t)(voff[k] + r);
-            p.slots[(int64_t)(voff[k] + r) * P] = idx[k];
+        if (f) {
+            const int r = base + rank;
+            uint32_t *lo = reinterpret_cast<uint32_t *>(p.tab + (hs & kEntryMask));   // low word
+            if (r >= V) {
+                *lo = kRefused;
+            } else {
+                *lo = (uint32_t)(voff + r);
+                p.slots[(int64_t)(voff + r) * P] = idx;
+            }
         }
     }
     if (p.stamps) __syncthreads();
@@ -415,44 +340,22 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // index regardless of interleaving.  Slot 0 is the first point (already known).  An index
     // larger than the current last level can never enter the list, which prunes crowded voxels.
     if (P > 1) {
-        for (int t0 = blockIdx.x; t0 < p.ntiles; t0 += kKB * nct) {
-            uint32_t hs[kKB];
-            int idx[kKB];
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                const int tile = t0 + k * nct;
-                hs[k] = kDropped; idx[k] = -1;
-                if (tile < p.ntiles) {
-                    const TileRange tr = tile_range(p, tile);
-                    if (tr.begin + tid < tr.end) { idx[k] = tr.begin + tid; hs[k] = __ldcg(p.hslot + idx[k]); }
-                }
-            }
-            uint32_t v[kKB];
-#pragma unroll
-            for (int k = 0; k < kKB; ++k)
-                v[k] = (hs[k] != kDropped && !(hs[k] & kFirstBit)) ? (uint32_t)__ldcg(p.tab + (hs[k] & kEntryMask))
-                                                                   : kRefused;
-            int *sl[kKB];
-            int last[kKB], carry[kKB];
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) {
-                sl[k] = p.slots + (int64_t)(v[k] == kRefused ? 0 : v[k]) * P;
-                last[k] = v[k] != kRefused ? __ldcg(sl[k] + P - 1) : 0;
-            }
-#pragma unroll
-            for (int k = 0; k < kKB; ++k) carry[k] = (v[k] != kRefused && last[k] > idx[k]) ? idx[k] : kInf;
-            for (int q = 1; q < P; ++q) {
-                bool any = false;
-#pragma unroll
-                for (int k = 0; k < kKB; ++k) any |= carry[k] != kInf;
-                if (!any) break;
-                int old[kKB];
-#pragma unroll
-                for (int k = 0; k < kKB; ++k)
-                    if (carry[k] != kInf) old[k] = atomicMin(sl[k] + q, carry[k]);
-#pragma unroll
-                for (int k = 0; k < kKB; ++k)
-                    if (carry[k] != kInf && old[k] > carry[k]) carry[k] = old[k];   // displaced (kInf: was free)
+        for (int it = 0; it < iters; ++it) {
+            const int tile = my_tile(p.ntiles, it);
+            if (tile < 0) continue;
+            const TileRange tr = tile_range(p, tile);
+            const int idx = tr.begin + (tid & (kTile - 1));
+            if (idx >= tr.end) continue;
+            const uint32_t hs = __ldcg(p.hslot + idx);
+            if (hs == kDropped || (hs & kFirstBit)) continue;
+            const uint32_t v = (uint32_t)__ldcg(p.tab + (hs & kEntryMask));
+            if (v == kRefused) continue;
+            int *sl = p.slots + (int64_t)v * P;
+            if (__ldcg(sl + P - 1) <= idx) continue;
+            int carry = idx;
+            for (int q = 1; q < P && carry != kInf; ++q) {
+                const int old = atomicMin(sl + q, carry);
+                if (old > carry) carry = old;                       // displaced (kInf: was free)
             }
         }
         if (p.stamps) __syncthreads();
@@ -462,113 +365,89 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 5);
 
     // ------------------------------------------------------------------------------- P5 gather
-    // One CTA handles VB consecutive voxel rows per iteration (VB * P <= kGatherSlots).  Most slots of
-    // the padded output are empty (84 % on a nuScenes sweep), so the padding and the points are handled
-    // separately: the [VB,P,C] tile is zeroed in shared memory with 16-byte stores, only the KEPT
-    // (voxel, slot) rows -- compacted through a block scan of the counts -- gather their point, and the
-    // finished tile, which is one contiguous block of the output, leaves with a single bulk (TMA)
-    // shared->global copy that overlaps the next iteration.  Thread per (voxel, channel) sums the kept
-    // slots in order and divides by the count (HardSimpleVFE; adding the zero padding would not change
-    // the sum); thread per voxel re-derives the cell of the first point for coors.
+    // Warp-granular, no CTA barrier, one LANE per voxel; tasks of VT = 32 consecutive voxel rows are dealt
+    // round-robin over the CTAs first, then over their warps.  The padded [VT,P,C] block of the output is one
+    // contiguous 16-byte-aligned range: the warp zero-fills it with coalesced float4 stores, then (after
+    // __syncwarp, which orders the stores of the participating lanes) every lane walks the kept slots of
+    // its voxel in order: gather (and perturb) the point row, store it over the padding, add it to the
+    // running per-channel sum -- the HardSimpleVFE order; adding the zero padding would not change it --
+    // and record point2voxel / point2slot.
     {
-        const int VB = p.VB, F = p.gd.F;
+        const int F = p.gd.F;
         const int M = s_voff[p.bd.B];
-        int *s_idx = reinterpret_cast<int *>(dyn_sm);                       // [VB*P] point index per slot
-        float *tile = reinterpret_cast<float *>(s_idx + VB * P);            // [VB*P*C]
-        int *s_cnt = reinterpret_cast<int *>(tile + VB * P * C);            // [VB]
-        int *s_pre = s_cnt + VB;                                            // [VB] kept rows before the voxel
-        unsigned short *s_list = reinterpret_cast<unsigned short *>(s_pre + VB);   // [VB*P] kept rows
-        const uint32_t tile_sa = (uint32_t)__cvta_generic_to_shared(tile);
-        for (int64_t v0 = (int64_t)blockIdx.x * VB; v0 < M; v0 += (int64_t)nct * VB) {
-            const int nv = (int)min((int64_t)VB, M - v0);
+        const int lane = tid & 31, warp = tid >> 5;
+        const int VT = p.VT;                                               // 32 (fewer when P is large), % 4 == 0
+        int *s_idx = reinterpret_cast<int *>(dyn_sm) + (size_t)warp * p.gather_stride;   // [VT * P] slot lists
+        const long long ntask = ((long long)M + VT - 1) / VT;
+        for (long long t = (long long)warp * nct + blockIdx.x; t < ntask; t += (long long)nct * (kPT / 32)) {
+            const long long v0 = t * VT;
+            const int nv = (int)min((long long)VT, M - v0);
             const int ns = nv * P;
-            const int nf = ns * C;
-            if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // tile free again
-            __syncthreads();
-            for (int t = tid; t < (nf + 3) >> 2; t += kPT)
-                reinterpret_cast<float4 *>(tile)[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int t = tid; t < ns; t += kPT) s_idx[t] = __ldcg(p.slots + v0 * P + t);
-            __syncthreads();
-            int kept_total;
+            __syncwarp();
+            for (int j = lane; j < ns; j += 32) s_idx[j] = __ldcg(p.slots + v0 * P + j);
             {
-                int c = 0;
-                if (tid < nv)
-                    for (int q = 0; q < P; ++q) c += s_idx[tid * P + q] != kInf ? 1 : 0;
-                const int pre = block_excl_scan<kPT>(c, sm, &kept_total);
-                if (tid < nv) {
-                    s_cnt[tid] = c;
-                    s_pre[tid] = pre;
-                    p.num_points[v0 + tid] = c;
-                    for (int q = 0; q < c; ++q) s_list[pre + q] = (unsigned short)(tid * P + q);
-                }
+                float *out = p.voxels + v0 * P * C;
+                const int nf = ns * C;
+                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int q = lane; q < (nf >> 2); q += 32) reinterpret_cast<float4 *>(out)[q] = z4;
+                for (int q = (nf & ~3) + lane; q < nf; q += 32) out[q] = 0.0f;
             }
-            __syncthreads();
-            if constexpr (C == 4) {
-                for (int j = tid; j < kept_total; j += kPT) {
-                    const int r = s_list[j];
-                    const int idx = s_idx[r];
-                    float4 x = __ldg(reinterpret_cast<const float4 *>(p.pts) + idx);
-                    if constexpr (PERTURB) {
-                        const float4 d = __ldg(reinterpret_cast<const float4 *>(p.raw) + idx);
-                        x.x = __fadd_rn(x.x, perturb_delta(d.x, p.pd.eb[0], p.pd.fb[0]));
-                        x.y = __fadd_rn(x.y, perturb_delta(d.y, p.pd.eb[1], p.pd.fb[1]));
-                        x.z = __fadd_rn(x.z, perturb_delta(d.z, p.pd.eb[2], p.pd.fb[2]));
-                        x.w = __fadd_rn(x.w, perturb_delta(d.w, p.pd.eb[3], p.pd.fb[3]));
+            __syncwarp();
+            if (lane < nv) {
+                const long long v = v0 + lane;
+                float *row = p.voxels + v * P * C;
+                float sum[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) sum[c] = 0.0f;
+                int n = 0;
+                int cx = 0, cy = 0, cz = 0;
+                for (; n < P; ++n) {
+                    const int idx = s_idx[lane * P + n];
+                    if (idx == kInf) break;                                    // levels fill from slot 0 up
+                    float x[C];
+                    if constexpr (C == 4) {
+                        const float4 t4 = __ldg(reinterpret_cast<const float4 *>(p.pts) + idx);
+                        x[0] = t4.x; x[1] = t4.y; x[2] = t4.z; x[3] = t4.w;
+                        if constexpr (PERTURB) {
+                            const float4 d = __ldg(reinterpret_cast<const float4 *>(p.raw) + idx);
+                            const float dv[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) x[c] = __fadd_rn(x[c], perturb_delta(dv[c], p.pd.eb[c], p.pd.fb[c]));
+                        }
+                        reinterpret_cast<float4 *>(row)[n] = make_float4(x[0], x[1], x[2], x[3]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) x[c] = __ldg(p.pts + (int64_t)idx * C + c);
+                        if constexpr (PERTURB) {
+#pragma unroll
+                            for (int c = 0; c < C; ++c)
+                                x[c] = __fadd_rn(x[c], perturb_delta(__ldg(p.raw + (int64_t)idx * C + c), p.pd.eb[c], p.pd.fb[c]));
+                        }
+#pragma unroll
+                        for (int c = 0; c < C; ++c) row[n * C + c] = x[c];
                     }
-                    reinterpret_cast<float4 *>(tile)[r] = x;
-                    if (p.p2v) p.p2v[idx] = (int)(v0 + r / P);
-                    if (p.p2s) p.p2s[idx] = r % P;
-                }
-            } else {
-                // one ELEMENT per lane: a warp instruction touches ~32/C rows (lines) instead of 32
-                for (int j = tid; j < kept_total * C; j += kPT) {
-                    const int jr = j / C, c = j - jr * C;
-                    const int r = s_list[jr];
-                    const int idx = s_idx[r];
-                    float x = __ldg(p.pts + (int64_t)idx * C + c);
-                    if constexpr (PERTURB)
-                        x = __fadd_rn(x, perturb_delta(__ldg(p.raw + (int64_t)idx * C + c), p.pd.eb[c], p.pd.fb[c]));
-                    tile[r * C + c] = x;
-                    if (c == 0) {
-                        if (p.p2v) p.p2v[idx] = (int)(v0 + r / P);
-                        if (p.p2s) p.p2s[idx] = r % P;
+#pragma unroll
+                    for (int c = 0; c < C; ++c) sum[c] = __fadd_rn(sum[c], x[c]);
+                    if (n == 0) {                                              // coors from the first point
+                        cx = axis_cell(x[0], p.gd, 0);
+                        cy = axis_cell(x[1], p.gd, 1);
+                        cz = axis_cell(x[2], p.gd, 2);
                     }
+                    if (p.p2v) p.p2v[idx] = (int)v;
+                    if (p.p2s) p.p2s[idx] = n;
                 }
-            }
-            __syncthreads();
-            if (p.feats) {
-                for (int t = tid; t < nv * F; t += kPT) {
-                    const int v = t / F, c = t - v * F;
-                    const int n = s_cnt[v];
-                    float s = 0.0f;
-                    for (int q = 0; q < n; ++q) s = __fadd_rn(s, tile[(v * P + q) * C + c]);
-                    p.feats[(v0 + v) * F + c] = __fdiv_rn(s, (float)n);
-                }
-            }
-            if (tid < nv) {
-                const float *f0 = tile + (int64_t)tid * P * C;            // the voxel's first point
-                const int cx = axis_cell(f0[0], p.gd, 0);
-                const int cy = axis_cell(f0[1], p.gd, 1);
-                const int cz = axis_cell(f0[2], p.gd, 2);
+                p.num_points[v] = n;
                 int b = 0;
-                while (b + 1 < p.bd.B && v0 + tid >= s_voff[b + 1]) ++b;
-                reinterpret_cast<int4 *>(p.coors)[v0 + tid] = make_int4(b, cz, cy, cx);
-            }
-            float *out = p.voxels + v0 * P * C;
-            if ((nf & 3) == 0) {
-                // generic-proxy writes to the tile -> visible to the async proxy, then one bulk store
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncthreads();
-                if (tid == 0) {
-                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
-                                 ::"l"(out), "r"(tile_sa), "r"(nf * 4) : "memory");
-                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                while (b + 1 < p.bd.B && v >= s_voff[b + 1]) ++b;
+                reinterpret_cast<int4 *>(p.coors)[v] = make_int4(b, cz, cy, cx);
+                if (p.feats) {
+                    const float fn = (float)n;
+#pragma unroll
+                    for (int c = 0; c < C; ++c)
+                        if (c < F) p.feats[v * F + c] = __fdiv_rn(sum[c], fn);
                 }
-            } else {                                                     // ragged tail tile
-                for (int t = tid; t < nf; t += kPT) out[t] = tile[t];
             }
         }
-        if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
     if (p.stamps) __syncthreads();
     stamp(p, 6);

@@ -34,6 +34,7 @@ names = ['clear', 'insert', 'flag', 'assign', 'rank', 'gather']
 for k, nm in enumerate(names):
     start = st[:, k]; arrive = st[:, 8 + k] if k < 5 else st[:, 6]
     work = arrive - start
-    print(f"{nm:8s} start {start.min():7.2f}..{start.max():7.2f}  work min {work.min():6.2f} med {np.median(work):6.2f} max {work.max():6.2f} (cta {work.argmax()})  all-arrived {arrive.max():7.2f}")
+    top = np.argsort(-work)[:8]
+    print(f"{nm:8s} start {start.min():7.2f}..{start.max():7.2f}  work min {work.min():6.2f} med {np.median(work):6.2f} p90 {np.percentile(work, 90):6.2f} max {work.max():6.2f}  all-arrived {arrive.max():7.2f}  slowest " + " ".join(f"{c}:{work[c]:.1f}" for c in top))
 print('insert: loads+cell of first batch done (cta-wide) med', np.median(st[:,13]), 'max', st[:,13].max())
 print('end', st[:, 6].max(), 'dist', dist, 'voxels', int(out.voxel_num[-1]), 'kept', int((out.point2voxel >= 0).sum()))
