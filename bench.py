@@ -275,7 +275,7 @@ def run_b200(args):
         out = ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds)
         cap = N
     else:
-        out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True)
+        out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True, want_slots=False)
         cap = out.capacity
     gfe = torch.randn((cap, F), device=dev, generator=torch.Generator(dev).manual_seed(5 + rank))
     graw = torch.empty((N, C), dtype=torch.float32, device=dev)

@@ -86,7 +86,7 @@ class _AdversarialStep(torch.autograd.Function):
     @staticmethod
     def forward(ctx, points, raw, n_per_sample, cfg: VoxelCfg, bounds: PerturbCfg, out: Optional[ops.HardVoxels]):
         hv = ops.hard_voxelize(points, n_per_sample, cfg, raw=raw, bounds=bounds, want_feats=True,
-                               want_maps=True, out=out)
+                               want_maps=True, want_slots=False, out=out)
         ctx.save_for_backward(raw, hv.num_points, hv.point2voxel)
         ctx.cfg, ctx.bounds = cfg, bounds
         ctx.hv = hv

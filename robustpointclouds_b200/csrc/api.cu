@@ -315,8 +315,8 @@ RPC_API int rpc_step_bwd(const rpc_voxel_cfg *cfg, const float *grad_feats,
     if (misaligned(grad_feats) || misaligned(raw) || misaligned(grad_raw)) return RPC_ERR_ALIGN;
     PerturbDesc pd;
     fill_perturb(cfg, pc, &pd);
-    int64_t blocks = (ntotal + (int64_t)kThreads * kBwdIlp - 1) / ((int64_t)kThreads * kBwdIlp);
-    if (blocks > kNumSM * 8) blocks = kNumSM * 8;                   // 8 x 256 threads per SM, one wave
+    int64_t blocks = (ntotal + kThreads - 1) / kThreads;
+    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     g_prof.begin(s);
     switch (cfg->C) {

@@ -54,65 +54,48 @@ k_vfe_mean_bwd(const float *__restrict__ grad_out, const int *__restrict__ num_p
 //   grad_raw[i,c] = (-fb <= raw*eb <= fb) ? g * eb[c] : 0
 // point2voxel comes from the forward.  With raw == NULL (no perturbation) the gradient w.r.t. the
 // point features themselves is written (g).
-// kBwdIlp points per thread: the index loads of all of them are issued before the first dependent gather
-// (the chain p2v -> {count, grad row} -> store is two memory latencies long; one point per thread left the
-// kernel latency-bound at a third of the HBM rate).
-constexpr int kBwdIlp = 4;
-
 template <int C>
 __global__ void __launch_bounds__(kThreads)
 k_step_bwd(const float *__restrict__ grad_feats, const int *__restrict__ num_points,
            const int *__restrict__ p2v, const float *__restrict__ raw,
            const __grid_constant__ PerturbDesc pd, int64_t ntotal, int F, float *__restrict__ grad_raw)
 {
-    const int64_t stride = (int64_t)gridDim.x * kThreads;
-    for (int64_t i0 = (int64_t)blockIdx.x * kThreads + threadIdx.x; i0 < ntotal; i0 += stride * kBwdIlp) {
-        int v[kBwdIlp];
-        float n[kBwdIlp];
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < ntotal;
+         i += (int64_t)gridDim.x * kThreads) {
+        const int v = __ldg(p2v + i);
+        float g[C];
 #pragma unroll
-        for (int k = 0; k < kBwdIlp; ++k) {
-            const int64_t i = i0 + k * stride;
-            v[k] = i < ntotal ? __ldg(p2v + i) : -1;
-        }
-#pragma unroll
-        for (int k = 0; k < kBwdIlp; ++k) n[k] = v[k] >= 0 ? (float)__ldg(num_points + v[k]) : 1.0f;
-#pragma unroll
-        for (int k = 0; k < kBwdIlp; ++k) {
-            const int64_t i = i0 + k * stride;
-            if (i >= ntotal) continue;
-            float g[C];
-#pragma unroll
-            for (int c = 0; c < C; ++c) g[c] = 0.0f;
-            if (v[k] >= 0) {
-                if (C == 4 && F == 4) {
-                    const float4 t = __ldg(reinterpret_cast<const float4 *>(grad_feats) + v[k]);
-                    g[0] = __fdiv_rn(t.x, n[k]); g[1] = __fdiv_rn(t.y, n[k]);
-                    g[2] = __fdiv_rn(t.z, n[k]); g[3 % C] = __fdiv_rn(t.w, n[k]);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < C; ++c)
-                        if (c < F) g[c] = __fdiv_rn(__ldg(grad_feats + (int64_t)v[k] * F + c), n[k]);
-                }
-            }
-            if (raw) {
-                if constexpr (C == 4) {
-                    const float4 r = __ldg(reinterpret_cast<const float4 *>(raw) + i);
-                    const float rr[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c)
-                        g[c] = perturb_pass(rr[c], pd.eb[c], pd.fb[c]) ? __fmul_rn(g[c], pd.eb[c]) : 0.0f;
-                } else {
-#pragma unroll
-                    for (int c = 0; c < C; ++c)
-                        g[c] = perturb_pass(__ldg(raw + i * C + c), pd.eb[c], pd.fb[c]) ? __fmul_rn(g[c], pd.eb[c]) : 0.0f;
-                }
-            }
-            if constexpr (C == 4) {
-                reinterpret_cast<float4 *>(grad_raw)[i] = make_float4(g[0], g[1], g[2], g[3]);
+        for (int c = 0; c < C; ++c) g[c] = 0.0f;
+        if (v >= 0) {
+            const float n = (float)__ldg(num_points + v);
+            if (C == 4 && F == 4) {
+                float4 t = __ldg(reinterpret_cast<const float4 *>(grad_feats) + v);
+                g[0] = __fdiv_rn(t.x, n); g[1] = __fdiv_rn(t.y, n);
+                g[2] = __fdiv_rn(t.z, n); g[3 % C] = __fdiv_rn(t.w, n);
             } else {
 #pragma unroll
-                for (int c = 0; c < C; ++c) grad_raw[i * C + c] = g[c];
+                for (int c = 0; c < C; ++c)
+                    if (c < F) g[c] = __fdiv_rn(__ldg(grad_feats + (int64_t)v * F + c), n);
             }
+        }
+        if (raw) {
+            if constexpr (C == 4) {
+                float4 r = __ldg(reinterpret_cast<const float4 *>(raw) + i);
+                const float rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    g[c] = perturb_pass(rr[c], pd.eb[c], pd.fb[c]) ? __fmul_rn(g[c], pd.eb[c]) : 0.0f;
+            } else {
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+                    g[c] = perturb_pass(__ldg(raw + i * C + c), pd.eb[c], pd.fb[c]) ? __fmul_rn(g[c], pd.eb[c]) : 0.0f;
+            }
+        }
+        if constexpr (C == 4) {
+            reinterpret_cast<float4 *>(grad_raw)[i] = make_float4(g[0], g[1], g[2], g[3]);
+        } else {
+#pragma unroll
+            for (int c = 0; c < C; ++c) grad_raw[i * C + c] = g[c];
         }
     }
 }

@@ -83,10 +83,11 @@ _default_ws = Workspace()
 
 def hard_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelCfg,
                   raw: Optional[torch.Tensor] = None, bounds: Optional[PerturbCfg] = None,
-                  want_feats: bool = False, want_maps: bool = False,
+                  want_feats: bool = False, want_maps: bool = False, want_slots: Optional[bool] = None,
                   out: Optional[HardVoxels] = None, workspace: Optional[torch.Tensor] = None) -> HardVoxels:
     """``rpc_voxelize_hard``: B sweeps concatenated in ``points`` [sum n_b, C]; ``raw`` [sum n_b, C] +
-    ``bounds`` voxelize the perturbed points x + clamp(raw*eb, +-fb) instead."""
+    ``bounds`` voxelize the perturbed points x + clamp(raw*eb, +-fb) instead.  ``want_maps`` adds point2voxel
+    (what the backward needs) and, unless ``want_slots=False``, point2slot."""
     dev = _need_cuda(points, raw)
     points = _f32c(points)
     if points.dim() != 2 or points.shape[1] != cfg.C:
@@ -113,7 +114,7 @@ def hard_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelC
             coors=torch.empty((cap, 4), **i32), num_points=torch.empty((cap,), **i32),
             voxel_num=torch.empty((B + 1,), **i32),
             point2voxel=torch.empty((N,), **i32) if want_maps else None,
-            point2slot=torch.empty((N,), **i32) if want_maps else None,
+            point2slot=torch.empty((N,), **i32) if (want_maps if want_slots is None else want_slots) else None,
             feats=torch.empty((cap, F), dtype=torch.float32, device=dev) if want_feats else None,
             capacity=int(cap))
     st = L.rpc_voxelize_hard(ctypes.byref(cfg), _ptr(points), n_arr, B, _ptr(raw),
