@@ -34,6 +34,7 @@ if ROOT not in sys.path:
 
 PERTURBER_PARAMS = {4: 34641, 5: 34772}        # hidden [64,128,64]
 L2_FLUSH_BYTES = 512 << 20
+POINTS_OVERRIDE = 0                            # --points
 
 
 def measured_peak_gbs():
@@ -105,7 +106,9 @@ def workload(name: str, batch: int = 0):
     from robustpointclouds_b200 import synth
     dynamic = name.endswith("-dynamic")
     base = name.split("-")[0]
-    p = synth.PRESETS[base]
+    p = dict(synth.PRESETS[base])
+    if POINTS_OVERRIDE:
+        p["N"] = POINTS_OVERRIDE
     B = batch or (6 if base == "kitti" else 4)
     return p, B, dynamic
 
@@ -148,7 +151,7 @@ def run_reference(args):
     vs, pcr = p["voxel_size"], p["point_cloud_range"]
     cores = len(os.sched_getaffinity(0))
     threads = max(1, min(cores, 32))            # every thread allocates its own dense table (360 MB for KITTI)
-    clouds = synth.make_batch(base, B)
+    clouds = synth.make_batch(base, B, N=p["N"])
     raws = [synth.make_raw(c, 99 + i) for i, c in enumerate(clouds)]
     eb, fb = orc.perturber_bounds(C, True)
     gf = np.random.default_rng(0).normal(size=(max(V, p["N"]) if dynamic else V, C)).astype(np.float32)
@@ -262,7 +265,7 @@ def run_b200(args):
     C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
     F = C
     cfg = VoxelCfg.make(p["voxel_size"], p["point_cloud_range"], P, V, C, F)
-    clouds = synth.make_batch(args.workload.split("-")[0], B, seed=1234 + rank * B)
+    clouds = synth.make_batch(args.workload.split("-")[0], B, N=p["N"], seed=1234 + rank * B)
     raws = [synth.make_raw(c, 99 + rank * B + i) for i, c in enumerate(clouds)]
     n = [len(c) for c in clouds]
     N = sum(n)
@@ -450,12 +453,15 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="kitti", choices=["kitti", "nuscenes", "nuscenes-dynamic", "kitti-dynamic"])
     ap.add_argument("--batch", type=int, default=0, help="sweeps per GPU (default: 6 KITTI, 4 nuScenes)")
+    ap.add_argument("--points", type=int, default=0, help="points per sweep (default: the preset's; BASELINE.json configs[4] sweep)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--flush", default="write", choices=["write", "write+read"],
                     help="L2 flush between steps: 512 MiB overwrite, optionally followed by a 256 MiB read sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    global POINTS_OVERRIDE
+    POINTS_OVERRIDE = args.points
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)
