@@ -182,6 +182,8 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     if (smem > 200 * 1024 / kCtasPerSM) return RPC_ERR_CONFIG;         // max_points > 195
     const size_t scan_bytes = 4 * (size_t)(pl.ntiles + 1);          // P3's prefix array shares the buffer
     if (smem < scan_bytes) smem = scan_bytes;
+    const size_t stage_bytes = C == 4 ? (size_t)2 * kSub * (raw ? 2 : 1) * kTile * 16 : 0;   // P1's TMA tile stages
+    smem = smem > stage_bytes ? smem : stage_bytes;
     char *w = static_cast<char *>(workspace);
     fp.pts = points; fp.raw = raw;
     fp.tab = reinterpret_cast<unsigned long long *>(w + pl.o_tab);

@@ -148,6 +148,35 @@ __device__ __forceinline__ void tile_rank_flags(bool f, int &rank, int &total, i
     total = tot;
 }
 
+// ---- TMA (bulk async copy) + mbarrier helpers for the point-tile pipeline of P1 (C == 4: a tile of rows is a
+// contiguous 16-byte-aligned range, so one cp.async.bulk per array brings it into shared memory while the
+// previous iteration is still probing the table)
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+
 template <int C, bool PERTURB>
 __global__ void __launch_bounds__(kPT, kCtasPerSM)
 k_hard_fwd(const __grid_constant__ FwdParams p)
@@ -156,6 +185,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     extern __shared__ __align__(16) unsigned char dyn_sm[];     // P3: int prefix[ntiles]; P5: gather tile
     __shared__ int sm[33];
     __shared__ int s_voff[RPC_MAX_BATCH + 1];                   // first voxel row of each sweep, then M
+    __shared__ __align__(8) unsigned long long s_bar[2 * (kPT / 32)];   // P1 (C == 4): one mbarrier per warp and stage
     const int tid = threadIdx.x;
     const int P = p.gd.P, V = p.gd.V;
     const int nct = gridDim.x;
@@ -188,7 +218,43 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
 
     // ------------------------------------------------------------------------------- P1 insert
     // coordinate loads -> cell; 32-byte bucket load -> local scan; CAS only where a slot looked empty,
-    // atomicMin only where the holder has a larger index
+    // atomicMin only where the holder has a larger index.
+    // C == 4: every WARP runs its own two-stage TMA pipeline -- lane 0 fetches the warp's 32 rows (512 bytes
+    // per array, contiguous and 16-byte aligned) of iteration it + 1 into the other shared-memory stage and
+    // arms that stage's mbarrier with the byte count while iteration it probes the table.  Per warp, not per
+    // CTA: a CTA-wide stage (one barrier per iteration) made every warp wait for the slowest probe chain.
+    constexpr bool kTma = (C == 4);
+    constexpr int kArr = PERTURB ? 2 : 1;                            // arrays staged per warp
+    const int wlane = tid & 31, wid = tid >> 5;
+    const uint32_t bar_sa = (uint32_t)__cvta_generic_to_shared(s_bar) + 8u * wid;          // + 8 * 32 * stage
+    const uint32_t stage_sa = (uint32_t)__cvta_generic_to_shared(dyn_sm) + (uint32_t)(wid * kArr * 512);   // + stage
+    constexpr uint32_t kStageBytes = (kPT / 32) * kArr * 512;
+    auto issue_rows = [&](int it) {                                  // called by lane 0
+        const int st = it & 1;
+        const int tile = my_tile(p.ntiles, it);
+        const uint32_t bar = bar_sa + 8u * (kPT / 32) * st;
+        int r0 = 0, r1 = 0;
+        if (tile >= 0) {
+            const TileRange tr = tile_range(p, tile);
+            r0 = tr.begin + (wid & 7) * 32;
+            r1 = min(r0 + 32, tr.end);
+        }
+        if (r1 <= r0) { mbar_arrive(bar); return; }
+        const uint32_t bytes = (uint32_t)(r1 - r0) * 16u;
+        const uint32_t dst = stage_sa + kStageBytes * st;
+        mbar_arrive_expect_tx(bar, bytes * kArr);
+        tma_load_1d(dst, reinterpret_cast<const float4 *>(p.pts) + r0, bytes, bar);
+        if constexpr (PERTURB) tma_load_1d(dst + 512, reinterpret_cast<const float4 *>(p.raw) + r0, bytes, bar);
+    };
+    if constexpr (kTma) {
+        if (wlane == 0) {
+            mbar_init(bar_sa, 1);
+            mbar_init(bar_sa + 8u * (kPT / 32), 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            if (iters > 0) issue_rows(0);
+        }
+        __syncwarp();
+    }
     for (int it = 0; it < iters; ++it) {
         const int tile = my_tile(p.ntiles, it);
         int idx = -1, cell = -1;
@@ -200,14 +266,33 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                 off = p.bd.tab_off[tr.b]; nb = p.bd.tab_size[tr.b] >> 2;
             }
         }
+        if constexpr (kTma) {
+            // every lane is past its reads of the other stage (__syncwarp at the end of the iteration): refill it
+            if (wlane == 0 && it + 1 < iters) issue_rows(it + 1);
+            mbar_wait(bar_sa + 8u * (kPT / 32) * (it & 1), (uint32_t)(it >> 1) & 1u);
+        }
         if (idx >= 0) {
             float x, y, z;
-            load_xyz<C, PERTURB>(p.pts, p.raw, p.pd, idx, x, y, z);
+            if constexpr (kTma) {
+                const float4 *sp = reinterpret_cast<const float4 *>(dyn_sm) +
+                                   ((it & 1) * (kPT / 32) + wid) * kArr * 32 + wlane;
+                const float4 v = sp[0];
+                x = v.x; y = v.y; z = v.z;
+                if constexpr (PERTURB) {
+                    const float4 r = sp[32];
+                    x = __fadd_rn(x, perturb_delta(r.x, p.pd.eb[0], p.pd.fb[0]));
+                    y = __fadd_rn(y, perturb_delta(r.y, p.pd.eb[1], p.pd.fb[1]));
+                    z = __fadd_rn(z, perturb_delta(r.z, p.pd.eb[2], p.pd.fb[2]));
+                }
+            } else {
+                load_xyz<C, PERTURB>(p.pts, p.raw, p.pd, idx, x, y, z);
+            }
             cell = point_cell(x, y, z, p.gd);
             if (p.p2v) p.p2v[idx] = -1;
             if (p.p2s) p.p2s[idx] = -1;
             if (cell < 0) p.hslot[idx] = kDropped;
         }
+        if constexpr (kTma) __syncwarp();                            // the stage may be refilled from here on
         if (p.stamps && it == 0) { __syncthreads(); stamp(p, 13); }
         uint32_t bkt = cell >= 0 ? probe_start((uint32_t)cell, nb) : 0u;
         int j0 = 0;                                                  // first slot of the bucket still to look at
