@@ -1,0 +1,62 @@
+"""StepPipeline (pinned host buffers in and out, three streams, double buffering) must return exactly what the
+direct C-ABI calls return, step after step, in both the hard and the dynamic configuration."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_path as orc
+from robustpointclouds_b200 import PerturbCfg, StepPipeline, VoxelCfg, ops, synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("dynamic", [False, True])
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_pipeline_matches_direct_calls(dynamic, use_graph):
+    dev = torch.device("cuda:0")
+    k = synth.KITTI
+    C, P, V = k["C"], k["max_num_points"], 3000
+    n = [7001, 5000]
+    cfg = VoxelCfg.make(k["voxel_size"], k["point_cloud_range"], P, V, C, C)
+    eb, fb = orc.perturber_bounds(C, True)
+    bounds = PerturbCfg.make(eb, fb)
+    pipe = StepPipeline(cfg, bounds, n, dev, depth=2, dynamic=dynamic, use_graph=use_graph)
+    cap = sum(n) if dynamic else sum(min(x, V) for x in n)
+    gf = torch.randn((cap, C), device=dev, generator=torch.Generator(dev).manual_seed(3))
+    batches = []
+    for s in range(5):
+        clouds = [synth.make_cloud("kitti", m, "lidar", 50 + 10 * s + i) for i, m in enumerate(n)]
+        raws = [synth.make_raw(c, 70 + 10 * s + i) for i, c in enumerate(clouds)]
+        batches.append((torch.from_numpy(np.concatenate(clouds)).pin_memory(),
+                        torch.from_numpy(np.concatenate(raws)).pin_memory()))
+    tickets, got = [], []
+    for s, (hp, hr) in enumerate(batches):
+        tickets.append(pipe.submit(hp, hr, gf))
+        if s >= 1:                                           # results are read one step behind the submissions
+            got.append({k2: v.clone() for k2, v in pipe.result(tickets[s - 1]).items()})
+    got.append({k2: v.clone() for k2, v in pipe.result(tickets[-1]).items()})
+    with pytest.raises(ValueError):
+        pipe.result(tickets[0])
+    for (hp, hr), res in zip(batches, got):
+        pts, raw = hp.to(dev), hr.to(dev)
+        if dynamic:
+            ref = ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds)
+            names = dict(coors=ref.coors, voxel_coors=ref.voxel_coors, num_points=ref.num_points, feats=ref.feats)
+        else:
+            ref = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True)
+            names = dict(voxels=ref.voxels, coors=ref.coors, num_points=ref.num_points, feats=ref.feats)
+        graw = ops.step_bwd(gf, ref.num_points, ref.point2voxel, cfg, raw=raw, bounds=bounds)
+        M = int(ref.voxel_num[-1])
+        assert res["voxel_num"].tolist() == ref.voxel_num.cpu().tolist()
+        for name, t in names.items():
+            a, b = res[name], t.cpu()
+            if name != "coors" or not dynamic:
+                a, b = a[:M], b[:M]
+            if name == "feats" and dynamic:                  # red.add order differs from run to run
+                torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-4)
+            else:
+                assert torch.equal(a, b), name
+        if dynamic:
+            torch.testing.assert_close(res["grad_raw"], graw.cpu(), rtol=1e-5, atol=1e-6)
+        else:
+            assert torch.equal(res["grad_raw"], graw.cpu())
