@@ -1,20 +1,25 @@
 #!/usr/bin/env python
 """bench.py -- throughput of the per-step adversarial input path (BASELINE.json metric):
-perturb (scale, clamp, add) -> hard voxelize -> HardSimpleVFE mean forward -> backward to the raw
-per-point perturbation, in M input points/s, on synthetic sweeps of the named shapes.
+perturb (scale, clamp, add) -> hard | dynamic voxelize -> HardSimpleVFE | scatter mean forward -> backward to
+the raw per-point perturbation, in M input points/s, on synthetic sweeps of the named shapes.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload kitti|nuscenes] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload kitti|nuscenes|nuscenes-dynamic|kitti-dynamic] [--batch B] [--points N]
 
-A *step* is one pass of the path over one batch (KITTI: B=6 sweeps x 120k points x 4 features =
-BASELINE.json configs[1]; nuScenes: B=4 x 300k x 5 = configs[2]).  N > 1 is launched by torchrun, one
-rank per GPU, every rank its own batch (weak scaling, no data-path collective), and the step ends with
-the NCCL all-reduce of the perturber's flat parameter-gradient buffer (34 641 fp32 for KITTI).
+A *step* is one pass of the path over one batch (kitti: B=6 sweeps x 120k points x 4 features =
+BASELINE.json configs[1], the default; nuscenes: B=4 x 300k x 5 = configs[2]; nuscenes-dynamic = configs[3];
+--points/--batch = the configs[4] sweep).  N > 1 is launched by torchrun, one rank per GPU, every rank its
+own batch (weak scaling, no data-path collective), and the step ends with the NCCL all-reduce of the
+perturber's flat parameter-gradient buffer (34 641 fp32 for KITTI).
 
 Timing: every step is bracketed by its own pair of CUDA events on the launching stream; between steps,
 outside the event pairs, a 512 MiB buffer is overwritten so that every step starts with a cold L2; the K
-step times are summed, MAX over ranks.  `value` = inputs resident in HBM; `e2e` = host (pinned) buffers
-in and out through the C-ABI, copies inside the timed region.  `--impl reference` times the CPU oracle
-(mmcv CPU semantics, dense per-call table -- see oracle/rpc_oracle.c) on the host cores instead.
+step times are summed, MAX over ranks.  `value` = inputs resident in HBM, CUDA-graph replay.  `e2e` = the
+public host front end (StepPipeline): pinned host buffers in and out, every step's H2D and D2H copies inside
+the timed region, three streams, double-buffered.  `roofline` = per-kernel CUDA-event durations measured
+inside the library (rpc_profile_*), algorithmic bytes per launch, measured HBM peak; `traffic` = DRAM bytes per
+launch from the committed ncu capture of the same workload (profiles/).  `--impl reference` times the CPU
+oracle (mmcv CPU semantics, dense per-call table -- see oracle/rpc_oracle.c) on the host cores instead.
 """
 from __future__ import annotations
 
