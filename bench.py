@@ -312,24 +312,67 @@ def run_b200(args):
         fwd()
         bwd()
 
+    par = None
+    if world > 1 and args.allreduce == "p2p":
+        from robustpointclouds_b200 import PeerAllReduce
+        try:
+            par = PeerAllReduce(pgrad.numel(), dev)
+        except Exception as e:                          # no peer mapping on this box: every rank falls back together
+            print(f"[bench] rank {rank}: peer all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+            par = None
+        agree = torch.tensor([1.0 if par is not None else 0.0], device=dev)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN)
+        if agree.item() < 1.0:
+            par = None
+
+    sync_buf = torch.zeros(4, dtype=torch.float32, device=dev)
+    sync_par = None
+    if par is not None:
+        from robustpointclouds_b200 import PeerAllReduce as _PAR
+        sync_par = _PAR(4, dev)                         # same mechanism as par, which every rank just built
+
+    def rank_sync():
+        """device-side rendezvous of the ranks, OUTSIDE the per-step event pairs: every rank flushes its L2 at its
+        own pace, and without this the skew is paid inside the timed step by the all-reduce waiting for the peer"""
+        if sync_par is not None:
+            sync_par.all_reduce(sync_buf)
+        elif world > 1:
+            dist.all_reduce(sync_buf)
+
+    def exchange():                                     # the step's only collective: perturber-gradient all-reduce
+        if par is not None:
+            par.all_reduce(pgrad)
+        elif world > 1:
+            dist.all_reduce(pgrad)
+
     graph = None
     if not args.no_graph:
         s = torch.cuda.Stream(dev)
         with torch.cuda.stream(s):
             path()
+            if par is not None:
+                exchange()
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             path()
+            if par is not None:                     # fixed launch parameters: the exchange sits in the step's graph
+                exchange()
 
     def step():
-        graph.replay() if graph is not None else path()
-        if world > 1:
-            dist.all_reduce(pgrad)
+        if graph is not None:
+            graph.replay()
+            if par is None:
+                exchange()
+        else:
+            path()
+            exchange()
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
-            l2_flush(); fn()
+            l2_flush(); rank_sync(); fn()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -337,6 +380,7 @@ def run_b200(args):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         for a, b in ev:
             l2_flush()
+            rank_sync()
             a.record(); fn(); b.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -357,7 +401,7 @@ def run_b200(args):
     vn = out.voxel_num.cpu().numpy()
     M = int(vn[-1])
     K = int((out.point2voxel >= 0).sum().item())
-    launches_per_step = 2                               # k_hard_fwd | k_dyn_scatter (persistent, cooperative) + k_step_bwd
+    launches_per_step = 2 + (1 if par is not None else 0)   # k_hard_fwd | k_dyn_scatter (persistent, cooperative) + k_step_bwd [+ k_allreduce_oneshot]
 
     # ---- e2e: pinned host buffers in, every API-visible output back to pinned host buffers, through the
     # package's public host front end (StepPipeline: H2D, kernels and D2H on three streams, double-buffered,
@@ -369,8 +413,11 @@ def run_b200(args):
     def e2e_run(k):
         for _ in range(k):
             pipe.submit(h_pts, h_raw, gfe)
-            if world > 1:
+            if world > 1 and par is None:
                 dist.all_reduce(pgrad)
+            elif par is not None:
+                with torch.cuda.stream(pipe.s_cmp):
+                    par.all_reduce(pgrad)
         pipe.drain()
 
     e2e_run(max(3, min(args.warmup, 5)))
@@ -446,7 +493,9 @@ def run_b200(args):
             "config": config_dict(args.workload, p, B, l2="flushed between steps, outside the per-step CUDA-event pairs: 512 MiB overwrite" +
                                   (" then a 256 MiB read-only sweep (L2 left full of clean lines)"
                                    if args.flush == "write+read" else ""), cuda_graph=graph is not None, voxels=M, kept_points=K,
-                                  collective=("nccl all_reduce of %d fp32 perturber grads per step" % pgrad.numel())
+                                  collective=(("one-shot NVLink peer-memory all-reduce (rpc_allreduce_oneshot, in the step's graph)"
+                                               if par is not None else "nccl all_reduce") +
+                                              " of %d fp32 perturber grads per step" % pgrad.numel())
                                   if world > 1 else "none"),
             "clocks": clocks,
             "e2e": {"value": round(total_pts / (e2e_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
@@ -475,6 +524,8 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="sweeps per GPU (default: 6 KITTI, 4 nuScenes)")
     ap.add_argument("--points", type=int, default=0, help="points per sweep (default: the preset's; BASELINE.json configs[4] sweep)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: perturber-gradient all-reduce through this library's one-shot NVLink kernel or NCCL")
     ap.add_argument("--flush", default="write", choices=["write", "write+read"],
                     help="L2 flush between steps: 512 MiB overwrite, optionally followed by a 256 MiB read sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

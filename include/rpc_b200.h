@@ -208,6 +208,22 @@ int rpc_perturb_apply_fwd(const float *x, const float *raw, const rpc_perturb_cf
 int rpc_perturb_apply_bwd(const float *grad_p, const float *raw, const rpc_perturb_cfg *pc /*[host]*/,
                           int64_t K, const int32_t *k_dev, int C, float *grad_raw, void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * One-shot all-reduce (sum) of the perturber's flat parameter-gradient buffer over NVLink peer memory:
+ * the path's only exchange (the reference gets it from mmengine's DDP wrapper, custom_hook.py:24-28,
+ * configs/adversarial/adversarial-centerpoint_voxel-nuscenes.py:110).  stage0 / stage1 / peer_flags are HOST
+ * arrays of `world` device pointers valid on this GPU (peer-mapped symmetric buffers, index = rank): two
+ * staging buffers of n floats (rounded up to 4) and rpc_allreduce_flag_bytes() of flags per rank, flags and
+ * `counter` (2 x uint32, local) zero-initialised once before the first call on any rank.  Every rank calls it
+ * the same number of times.  out[i] = sum over ranks of src[i], added in rank order (bit-identical on all
+ * ranks); out may alias src.  The launch parameters do not change between calls: capturable in a CUDA graph.
+ * *status (device int32) is set to 1 if a peer did not arrive within 2 s.
+ * ------------------------------------------------------------------------------------------------- */
+size_t rpc_allreduce_flag_bytes(void);
+int rpc_allreduce_oneshot(float *const *stage0 /*[host]*/, float *const *stage1 /*[host]*/,
+                          uint32_t *const *peer_flags /*[host]*/, int rank, int world, int64_t n, const float *src,
+                          float *out, uint32_t *counter, int32_t *status, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -10,6 +10,7 @@
 #include "hard_fwd.cuh"
 #include "rows.cuh"
 #include "dyn_scatter.cuh"
+#include "allreduce.cuh"
 
 using namespace rpc;
 
@@ -650,6 +651,34 @@ RPC_API int rpc_perturb_apply_bwd(const float *grad_p, const float *raw, const r
     memset(&pd, 0, sizeof(pd));
     for (int c = 0; c < C; ++c) { pd.eb[c] = pc->eb[c]; pd.fb[c] = pc->fb[c]; }
     k_perturb_apply_bwd<<<stream_blocks(K * C), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(grad_p, raw, pd, K, k_dev, C, grad_raw);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+// ------------------------------------------------------------------ perturber-gradient all-reduce over peer memory
+RPC_API size_t rpc_allreduce_flag_bytes(void) { return (size_t)kArCtas * kArMaxWorld * sizeof(uint32_t); }
+
+RPC_API int rpc_allreduce_oneshot(float *const *stage0, float *const *stage1, uint32_t *const *peer_flags, int rank,
+                                  int world, int64_t n, const float *src, float *out, uint32_t *counter,
+                                  int32_t *status, void *stream)
+{
+    if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world || n < 0) return RPC_ERR_CONFIG;
+    if (n == 0) return RPC_OK;
+    if (!stage0 || !stage1 || !peer_flags || !src || !out || !counter || !status) return RPC_ERR_NULL;
+    ArParams p;
+    memset(&p, 0, sizeof(p));
+    for (int r = 0; r < world; ++r) {
+        if (!stage0[r] || !stage1[r] || !peer_flags[r]) return RPC_ERR_NULL;
+        if (misaligned(stage0[r]) || misaligned(stage1[r])) return RPC_ERR_ALIGN;
+        p.stage[0][r] = stage0[r];
+        p.stage[1][r] = stage1[r];
+        p.flags[r] = peer_flags[r];
+    }
+    if (misaligned(out) || misaligned(src)) return RPC_ERR_ALIGN;
+    p.src = src; p.out = out; p.ctr = counter; p.status = status; p.n = n; p.rank = rank; p.world = world;
+    int64_t ctas = ((n >> 2) + kArThreads - 1) / kArThreads;
+    if (ctas > kArCtas) ctas = kArCtas;
+    if (ctas < 1) ctas = 1;
+    k_allreduce_oneshot<<<(int)ctas, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
