@@ -160,3 +160,40 @@ def test_vfe_mean_standalone():
         g = rng.normal(size=(M, F)).astype(np.float32)
         gb = ops.vfe_mean_bwd(torch.from_numpy(g).to(dev), torch.from_numpy(num).to(dev), P, C)
         assert np.array_equal(gb.cpu().numpy(), orc.vfe_mean_bwd(g, num, P, C))
+
+
+@pytest.mark.parametrize("C,P,F,V", [(3, 4, 3, 500), (8, 32, 3, 1500), (6, 64, 6, 300), (4, 1, 4, 100000), (5, 3, 4, 7)])
+def test_hard_voxelize_generic_shapes(C, P, F, V):
+    """feature widths 3..8, large and unit max_num_points, num_features < C, a cap of a few voxels"""
+    rng = np.random.default_rng(C * 100 + P)
+    vs, pcr = [0.4, 0.4, 0.5], [-20.0, -20.0, -2.0, 20.0, 20.0, 2.0]
+    clouds = []
+    for n in (6000, 1, 2049):
+        pts = rng.normal(0, 9, size=(n, C)).astype(np.float32)
+        pts[:, 2] = rng.uniform(-3, 3, n)
+        clouds.append(pts)
+    dev = torch.device("cuda:0")
+    cfg = VoxelCfg.make(vs, pcr, P, V, C, F)
+    out = ops.hard_voxelize(torch.from_numpy(np.concatenate(clouds)).to(dev), [len(c) for c in clouds], cfg,
+                            want_feats=True, want_maps=True)
+    gf = rng.normal(size=(out.capacity, F)).astype(np.float32)
+    g = ops.step_bwd(torch.from_numpy(gf).to(dev), out.num_points, out.point2voxel, cfg)
+    ref = _oracle_batch(clouds, None, None, None, vs, pcr, P, V, F, gf)
+    M = out.total()
+    assert out.voxel_num.cpu().tolist()[:-1] == ref["voxel_num"] and M == sum(ref["voxel_num"])
+    assert np.array_equal(out.coors[:M].cpu().numpy(), ref["coors"])
+    assert np.array_equal(out.num_points[:M].cpu().numpy(), ref["num_points"])
+    assert np.array_equal(out.voxels[:M].cpu().numpy(), ref["voxels"])
+    assert np.array_equal(out.point2voxel.cpu().numpy(), ref["p2v"])
+    assert np.array_equal(out.point2slot.cpu().numpy(), ref["p2s"])
+    assert np.array_equal(out.feats[:M].cpu().numpy(), ref["feats"][:, :F])
+    gref = ref["grad_raw"].copy()
+    _close(g.cpu().numpy()[:, :F], gref[:, :F])
+    assert not g.cpu().numpy()[:, F:].any()
+
+
+def test_hard_voxelize_max_batch():
+    """RPC_MAX_BATCH = 32 sweeps of ragged sizes in one launch"""
+    clouds = [synth.make_cloud("kitti", 300 + 37 * i, "lidar" if i % 2 else "clustered", 900 + i) for i in range(32)]
+    M, exact = _run_case(clouds, "kitti", 150, True)
+    assert M > 0 and exact

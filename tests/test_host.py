@@ -160,3 +160,26 @@ def test_flat_grad_allreduce_gloo_world2():
     n_params = sum(p.numel() for p in rpc.VoxelPerturber(hidden_channels=[8, 16, 32]).build(4).parameters())
     for rank, numel, err, gmax in res:
         assert numel == n_params and err < 1e-7 and gmax <= 0.1 + 1e-7
+
+
+def test_dynamic_and_allreduce_entries_without_gpu():
+    """argument validation of the round-1 additions happens on the host, before any launch"""
+    L = _lib.lib()
+    cfg = rpc.VoxelCfg.make([0.075, 0.075, 0.2], [-54, -54, -5, 54, 54, 3], 1, 1, 5)
+    n = _lib.counts([300000] * 4)
+    ws = L.rpc_dynamic_workspace_bytes(ctypes.byref(cfg), 4, n)
+    # per point: cell + slot words, a 32-byte fine group and an accumulator row at most
+    assert 1200000 * (4 + 4 + 32) < ws < 1200000 * 200
+    assert L.rpc_dynamic_stamps_offset(ctypes.byref(cfg), 4, n) > 0
+    assert L.rpc_dynamic_workspace_bytes(ctypes.byref(cfg), 40, n) == 0           # B > RPC_MAX_BATCH
+    args = [None] * 9
+    assert L.rpc_dynamic_scatter_mean_fwd(ctypes.byref(cfg), None, n, 4, None, None, *args[:7], None, 0, None) == -1
+    bad = rpc.VoxelCfg.make([0.075, -1.0, 0.2], [-54, -54, -5, 54, 54, 3], 1, 1, 5)
+    assert L.rpc_dynamic_scatter_mean_fwd(ctypes.byref(bad), None, n, 4, None, None, *args[:7], None, 0, None) == -2
+    assert L.rpc_allreduce_flag_bytes() >= 64 * 16 * 4
+    vp = ctypes.c_void_p
+    one = (vp * 1)(None)
+    assert L.rpc_allreduce_oneshot(one, one, one, 0, 17, 8, None, None, None, None, None) == -2   # world > 16
+    assert L.rpc_allreduce_oneshot(one, one, one, 1, 1, 8, None, None, None, None, None) == -2    # rank >= world
+    assert L.rpc_allreduce_oneshot(one, one, one, 0, 1, 8, None, None, None, None, None) == -1    # NULL pointers
+    assert L.rpc_allreduce_oneshot(one, one, one, 0, 1, 0, None, None, None, None, None) == 0     # nothing to do
