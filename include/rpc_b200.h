@@ -224,6 +224,25 @@ int rpc_allreduce_oneshot(float *const *stage0 /*[host]*/, float *const *stage1 
                           uint32_t *const *peer_flags /*[host]*/, int rank, int world, int64_t n, const float *src,
                           float *out, uint32_t *counter, int32_t *status, void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * The elementwise / reduction parts of VoxelPerturber.forward around its MLP, without host
+ * syncs.  `moments` is rpc_moments_bytes() of device scratch (fp64 accumulators, zeroed by the call).
+ *   rpc_normalize_fwd       xn = clamp(x / (std(x, dim 0) + 1e-6), -10, 10); NaN / Inf scale -> unit scaling
+ *                           (voxel_perturber.py:157-168)
+ *   rpc_perturb_losses_fwd  losses[4] = {l2_norm = mean_k ||p_k||, intensity_loss = mean_k |p_k3| (0 for C < 4),
+ *                           bias_loss = mean_c |mean_k p_kc|, imbalance_loss = std_c(std_k p_kc)}
+ *                           (voxel_perturber.py:268-299); consts[32] f32 keeps what the backward needs
+ *   rpc_perturb_losses_bwd  grad_p [K, C] from grad_losses[4] (device), torch's autograd rules (norm / std
+ *                           backward are 0 where the norm / std is 0)
+ * ------------------------------------------------------------------------------------------------- */
+size_t rpc_moments_bytes(void);
+int rpc_normalize_fwd(const float *x, int64_t K, const int32_t *k_dev, int C, double *moments, float *xn,
+                      void *stream);
+int rpc_perturb_losses_fwd(const float *p, int64_t K, const int32_t *k_dev, int C, double *moments, float *losses,
+                           float *consts, void *stream);
+int rpc_perturb_losses_bwd(const float *p, const float *consts, const float *grad_losses, int64_t K,
+                           const int32_t *k_dev, int C, float *grad_p, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -11,6 +11,7 @@
 #include "rows.cuh"
 #include "dyn_scatter.cuh"
 #include "allreduce.cuh"
+#include "perturber.cuh"
 
 using namespace rpc;
 
@@ -679,6 +680,63 @@ RPC_API int rpc_allreduce_oneshot(float *const *stage0, float *const *stage1, ui
     if (ctas > kArCtas) ctas = kArCtas;
     if (ctas < 1) ctas = 1;
     k_allreduce_oneshot<<<(int)ctas, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+// ------------------------------------------------------------------ perturber statistics
+static int moments_launch(const float *x, int64_t K, const int32_t *k_dev, int C, double *acc, cudaStream_t st)
+{
+    if (cudaMemsetAsync(acc, 0, sizeof(double) * kMomVals, st) != cudaSuccess) return RPC_ERR_CUDA;
+    int64_t blocks = (K + kThreads - 1) / kThreads;
+    if (blocks > kNumSM * 4) blocks = kNumSM * 4;
+    if (blocks < 1) blocks = 1;
+    switch (C) {
+#define RPC_CASE(CC) case CC: k_col_moments<CC><<<(int)blocks, kThreads, 0, st>>>(x, K, k_dev, acc); break;
+        RPC_CASE(1) RPC_CASE(2) RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+#undef RPC_CASE
+        default: return RPC_ERR_CONFIG;
+    }
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API size_t rpc_moments_bytes(void) { return sizeof(double) * kMomVals; }
+
+RPC_API int rpc_normalize_fwd(const float *x, int64_t K, const int32_t *k_dev, int C, double *moments, float *xn,
+                              void *stream)
+{
+    if (C < 1 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!x || !moments || !xn) return RPC_ERR_NULL;
+    if (C == 4 && misaligned(x)) return RPC_ERR_ALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = moments_launch(x, K, k_dev, C, moments, st);
+    if (rc) return rc;
+    k_normalize_fwd<<<stream_blocks(K * C), kThreads, 0, st>>>(x, moments, K, k_dev, C, xn);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_perturb_losses_fwd(const float *p, int64_t K, const int32_t *k_dev, int C, double *moments,
+                                   float *losses, float *consts, void *stream)
+{
+    if (C < 2 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (!p || !moments || !losses || !consts) return RPC_ERR_NULL;
+    if (C == 4 && misaligned(p)) return RPC_ERR_ALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = moments_launch(p, K, k_dev, C, moments, st);
+    if (rc) return rc;
+    k_losses_finalize<<<1, 32, 0, st>>>(moments, K, k_dev, C, losses, consts);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_perturb_losses_bwd(const float *p, const float *consts, const float *grad_losses, int64_t K,
+                                   const int32_t *k_dev, int C, float *grad_p, void *stream)
+{
+    if (C < 2 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!p || !consts || !grad_losses || !grad_p) return RPC_ERR_NULL;
+    int64_t blocks = (K + kThreads - 1) / kThreads;
+    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
+    k_losses_bwd<<<(int)blocks, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(p, consts, grad_losses, K, k_dev, C, grad_p);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 

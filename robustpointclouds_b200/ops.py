@@ -359,3 +359,40 @@ def perturb_apply_bwd(grad_p: torch.Tensor, raw: torch.Tensor, bounds: PerturbCf
                                           _stream(dev))
     _lib.check(st, "rpc_perturb_apply_bwd")
     return g
+
+
+# ------------------------------------------------------------------ perturber statistics
+def normalize_fwd(x: torch.Tensor) -> torch.Tensor:
+    """``clamp(x / (std(x, 0) + 1e-6), -10, 10)`` with the NaN / Inf scale guard, no host sync
+    (/root/reference/models/adversarial/voxel_perturber.py:157-168)."""
+    dev = _need_cuda(x)
+    x = _f32c(x)
+    K, C = x.shape
+    xn = torch.empty_like(x)
+    mom = torch.empty((_lib.lib().rpc_moments_bytes() // 8,), dtype=torch.float64, device=dev)
+    st = _lib.lib().rpc_normalize_fwd(_ptr(x), K, None, C, _ptr(mom), _ptr(xn), _stream(dev))
+    _lib.check(st, "rpc_normalize_fwd")
+    return xn
+
+
+def perturb_losses_fwd(p: torch.Tensor):
+    """(losses[4] = l2_norm, intensity_loss, bias_loss, imbalance_loss; consts[32]) of voxel_perturber.py:268-299."""
+    dev = _need_cuda(p)
+    p = _f32c(p)
+    K, C = p.shape
+    mom = torch.empty((_lib.lib().rpc_moments_bytes() // 8,), dtype=torch.float64, device=dev)
+    losses = torch.empty((4,), dtype=torch.float32, device=dev)
+    consts = torch.empty((32,), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_perturb_losses_fwd(_ptr(p), K, None, C, _ptr(mom), _ptr(losses), _ptr(consts), _stream(dev))
+    _lib.check(st, "rpc_perturb_losses_fwd")
+    return losses, consts
+
+
+def perturb_losses_bwd(p: torch.Tensor, consts: torch.Tensor, grad_losses: torch.Tensor) -> torch.Tensor:
+    dev = _need_cuda(p, consts, grad_losses)
+    p, grad_losses = _f32c(p), _f32c(grad_losses)
+    K, C = p.shape
+    g = torch.empty_like(p)
+    st = _lib.lib().rpc_perturb_losses_bwd(_ptr(p), _ptr(consts), _ptr(grad_losses), K, None, C, _ptr(g), _stream(dev))
+    _lib.check(st, "rpc_perturb_losses_bwd")
+    return g

@@ -1,8 +1,10 @@
 """``VoxelPerturber`` with the reference's API (/root/reference/models/adversarial/voxel_perturber.py:20-541)
 on top of the sm_100a kernels.
 
-What stays in PyTorch: the small MLP / attention (cuBLAS GEMMs) and the four loss
-scalars.  What runs in the hand-written kernels: the elementwise tail ``p = nan_to_num(clamp(raw * eb,
+What stays in PyTorch: the small MLP / attention (cuBLAS GEMMs).  What runs in the
+hand-written kernels: the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
+scalars and their gradient (``rpc_perturb_losses_fwd/bwd``; ``fused_stats=False`` keeps the ATen formulas), the
+elementwise tail ``p = nan_to_num(clamp(raw * eb,
 -fb, +fb)); y = x + p`` and its autograd (``rpc_perturb_apply_fwd/bwd``), and -- in the fused north-star
 order -- the whole perturb + voxelize + VFE step (``adversarial_step.py``).
 
@@ -76,6 +78,22 @@ class _PerturbApply(torch.autograd.Function):
         return grad_x, grad_raw, None
 
 
+class _PerturbLosses(torch.autograd.Function):
+    """The four regularisers of voxel_perturber.py:268-299 from one pass over p (``rpc_perturb_losses_fwd``) and a
+    streaming backward (``rpc_perturb_losses_bwd``)."""
+
+    @staticmethod
+    def forward(ctx, p: torch.Tensor):
+        losses, consts = ops.perturb_losses_fwd(p)
+        ctx.save_for_backward(p, consts)
+        return losses
+
+    @staticmethod
+    def backward(ctx, grad_losses):
+        p, consts = ctx.saved_tensors
+        return ops.perturb_losses_bwd(p, consts, grad_losses.contiguous())
+
+
 def _gradient_hook(grad):
     if grad is None:
         return grad
@@ -86,7 +104,7 @@ def _gradient_hook(grad):
 class VoxelPerturber(nn.Module):
     def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
                  use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
-                 nan_guards: bool = True):
+                 nan_guards: bool = True, fused_stats: bool = True):
         super().__init__()
         voxel_size = list(voxel_size)
         self.sensor_error_bound = sensor_error_bound
@@ -103,6 +121,7 @@ class VoxelPerturber(nn.Module):
         self.constraint_violations: List[float] = []
         self.perturbation_stats: List[Dict[str, float]] = []
         self.nan_guards = nan_guards          # False: no isnan().any() host syncs (the fused step's choice)
+        self.fused_stats = fused_stats        # std-normalise and the four losses through the sm_100a kernels
         self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
 
     # ------------------------------------------------------------------ construction
@@ -198,10 +217,13 @@ class VoxelPerturber(nn.Module):
         Returns ``raw`` [K, C] in [-1, 1] or ``None`` when a NaN guard trips (caller returns x unchanged)."""
         if self.nan_guards and torch.isnan(x).any():
             return None
-        scale = torch.std(x, dim=0, keepdim=True) + 1e-6
-        if self.nan_guards and (torch.isnan(scale).any() or torch.isinf(scale).any()):
-            scale = torch.ones_like(scale)
-        xn = torch.clamp(x / scale, -10.0, 10.0)
+        if self.fused_stats and x.is_cuda and x.shape[0] >= 2:
+            xn = ops.normalize_fwd(x.detach())                   # x carries no gradient into the network (:157-168)
+        else:
+            scale = torch.std(x, dim=0, keepdim=True) + 1e-6
+            if self.nan_guards and (torch.isnan(scale).any() or torch.isinf(scale).any()):
+                scale = torch.ones_like(scale)
+            xn = torch.clamp(x / scale, -10.0, 10.0)
         try:
             raw = self.model(xn)
         except RuntimeError:
@@ -214,9 +236,12 @@ class VoxelPerturber(nn.Module):
         return raw
 
     @staticmethod
-    def losses(p: torch.Tensor) -> Dict[str, torch.Tensor]:
+    def losses(p: torch.Tensor, fused: bool = False) -> Dict[str, torch.Tensor]:
         """The four regularisers of voxel_perturber.py:268-299 on the applied perturbation p [K, C]."""
         C = p.shape[1]
+        if fused and p.is_cuda and p.shape[0] >= 2 and C >= 4:
+            l2_norm, intensity, bias, imbalance = _PerturbLosses.apply(p).unbind(0)
+            return dict(l2_norm=l2_norm, intensity_loss=intensity, bias_loss=bias, imbalance_loss=imbalance)
         l2_norm = torch.norm(p, p=2, dim=1).mean()
         if C >= 4:
             intensity = p[:, 3].abs().mean()
@@ -236,7 +261,7 @@ class VoxelPerturber(nn.Module):
         if self.nan_guards and torch.isnan(raw).any():          # "NaN after scaling" guard (:259-262)
             return x, torch.tensor(0.0, device=x.device)
         y, p = _PerturbApply.apply(x, raw, cfg)
-        loss_dict = self.losses(p)
+        loss_dict = self.losses(p, self.fused_stats)
         if self.training:
             self._track_metrics(p, x, loss_dict["l2_norm"])
         return y, loss_dict

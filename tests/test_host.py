@@ -183,3 +183,16 @@ def test_dynamic_and_allreduce_entries_without_gpu():
     assert L.rpc_allreduce_oneshot(one, one, one, 1, 1, 8, None, None, None, None, None) == -2    # rank >= world
     assert L.rpc_allreduce_oneshot(one, one, one, 0, 1, 8, None, None, None, None, None) == -1    # NULL pointers
     assert L.rpc_allreduce_oneshot(one, one, one, 0, 1, 0, None, None, None, None, None) == 0     # nothing to do
+
+
+def test_perturber_statistics_entries_without_gpu():
+    L = _lib.lib()
+    assert L.rpc_moments_bytes() == 8 * 18                   # S_c, Q_c for 8 channels + the two row sums, fp64
+    assert L.rpc_normalize_fwd(None, 10, None, 0, None, None, None) == -2         # C out of range
+    assert L.rpc_normalize_fwd(None, 10, None, 9, None, None, None) == -2
+    assert L.rpc_normalize_fwd(None, 10, None, 4, None, None, None) == -1         # NULL pointers
+    assert L.rpc_normalize_fwd(None, 0, None, 4, None, None, None) == 0           # nothing to do
+    assert L.rpc_perturb_losses_fwd(None, 10, None, 1, None, None, None, None) == -2
+    assert L.rpc_perturb_losses_fwd(None, 10, None, 5, None, None, None, None) == -1
+    assert L.rpc_perturb_losses_bwd(None, None, None, 10, None, 5, None, None) == -1
+    assert L.rpc_perturb_losses_bwd(None, None, None, 0, None, 5, None, None) == 0
