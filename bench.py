@@ -42,6 +42,17 @@ L2_FLUSH_BYTES = 512 << 20
 POINTS_OVERRIDE = 0                            # --points
 
 
+def ncu_traffic(args, kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of this workload at its default
+    size (profiles/traffic.json, written by tools/ncu_traffic.py); null for any other size."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if args.batch or args.points or not os.path.exists(path):
+        return {}
+    with open(path) as f:
+        e = json.load(f).get("%s:%s" % (args.workload, kernel))
+    return {"traffic": e["bytes"], "traffic_source": e["source"]} if e else {}
+
+
 def measured_peak_gbs():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -477,6 +488,7 @@ def run_b200(args):
             "step": {"b_alg_bytes": balg, "achieved": round(balg / (ms_per_step * 1e-3) / 1e9, 2),
                      "frac": round(balg / (ms_per_step * 1e-3) / 1e9 / peak, 4)}}
     if dom is not None:
+        roof.update(ncu_traffic(args, dom))
         kb = kern_bytes.get(dom, balg)
         a = kb / (stage_us[dom] * 1e-6) / 1e9
         roof.update({"achieved": round(a, 2), "frac": round(a / peak, 4), "b_alg_bytes": kb})

@@ -104,7 +104,7 @@ def _gradient_hook(grad):
 class VoxelPerturber(nn.Module):
     def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
                  use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
-                 nan_guards: bool = True, fused_stats: bool = True):
+                 nan_guards=True, fused_stats: bool = True):
         super().__init__()
         voxel_size = list(voxel_size)
         self.sensor_error_bound = sensor_error_bound
@@ -120,7 +120,13 @@ class VoxelPerturber(nn.Module):
         self.l2_percentages: List[float] = []
         self.constraint_violations: List[float] = []
         self.perturbation_stats: List[Dict[str, float]] = []
-        self.nan_guards = nan_guards          # False: no isnan().any() host syncs (the fused step's choice)
+        # True: the reference's isnan().any() host checks (:150-153, :189-200, :259-262).  False: none.
+        # "device": the same conditions as a device flag -- the step returns x unchanged and zero losses where the
+        # reference would, without a host sync; metrics are kept on the device until flush_metrics() /
+        # save_l2_norms(); check_guards() reads the flag (one sync) and resets NaN weights like :197.
+        self.nan_guards = nan_guards
+        self.guard_tripped = None
+        self._pending_metrics: List[torch.Tensor] = []
         self.fused_stats = fused_stats        # std-normalise and the four losses through the sm_100a kernels
         self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
 
@@ -215,24 +221,31 @@ class VoxelPerturber(nn.Module):
     def raw_perturbation(self, x: torch.Tensor):
         """The network part of ``forward`` (:157-205): std-normalise, clamp +-10, MLP -> tanh, attention gate.
         Returns ``raw`` [K, C] in [-1, 1] or ``None`` when a NaN guard trips (caller returns x unchanged)."""
-        if self.nan_guards and torch.isnan(x).any():
+        host = self.nan_guards is True
+        if host and torch.isnan(x).any():
             return None
+        if self.nan_guards == "device":
+            self.guard_tripped = torch.isnan(x).any()
         if self.fused_stats and x.is_cuda and x.shape[0] >= 2:
             xn = ops.normalize_fwd(x.detach())                   # x carries no gradient into the network (:157-168)
         else:
             scale = torch.std(x, dim=0, keepdim=True) + 1e-6
-            if self.nan_guards and (torch.isnan(scale).any() or torch.isinf(scale).any()):
+            if self.nan_guards == "device":
+                scale = torch.where((torch.isnan(scale) | torch.isinf(scale)).any(), torch.ones_like(scale), scale)
+            elif host and (torch.isnan(scale).any() or torch.isinf(scale).any()):
                 scale = torch.ones_like(scale)
             xn = torch.clamp(x / scale, -10.0, 10.0)
         try:
             raw = self.model(xn)
         except RuntimeError:
             return None
-        if self.nan_guards and torch.isnan(raw).any():
+        if host and torch.isnan(raw).any():
             self._reset_problematic_weights()
             return None
         if self.use_spatial_attention:
             raw = raw * self.attention(xn)
+        if self.nan_guards == "device":
+            self.guard_tripped = self.guard_tripped | torch.isnan(raw).any()
         return raw
 
     @staticmethod
@@ -258,13 +271,25 @@ class VoxelPerturber(nn.Module):
         if raw is None:
             return x, torch.tensor(0.0, device=x.device)
         _, _, cfg = self.bounds(x.shape[1])
-        if self.nan_guards and torch.isnan(raw).any():          # "NaN after scaling" guard (:259-262)
+        if self.nan_guards is True and torch.isnan(raw).any():  # "NaN after scaling" guard (:259-262)
             return x, torch.tensor(0.0, device=x.device)
         y, p = _PerturbApply.apply(x, raw, cfg)
         loss_dict = self.losses(p, self.fused_stats)
+        if self.nan_guards == "device":
+            bad = self.guard_tripped
+            y = torch.where(bad, x, y)
+            loss_dict = {k: torch.where(bad, torch.zeros_like(v), v) for k, v in loss_dict.items()}
         if self.training:
             self._track_metrics(p, x, loss_dict["l2_norm"])
         return y, loss_dict
+
+    def check_guards(self) -> bool:
+        """``nan_guards="device"``: read the flag of the last forward (one host sync); on a trip reset NaN weights
+        like the reference does inside forward (:197)."""
+        tripped = self.guard_tripped is not None and bool(self.guard_tripped.item())
+        if tripped:
+            self._reset_problematic_weights()
+        return tripped
 
     # ------------------------------------------------------------------ metrics
     def _track_metrics(self, p: torch.Tensor, x: torch.Tensor, l2_norm: torch.Tensor) -> None:
@@ -273,7 +298,21 @@ class VoxelPerturber(nn.Module):
             ref = torch.norm(x, p=2, dim=1).mean()
             pa = p.abs()
             vals = torch.stack([l2_norm.detach(), l2_norm.detach() / (ref + 1e-8) * 100, pa.max(), pa.mean(),
-                                torch.std(p)]).tolist()
+                                torch.std(p)])
+        if self.nan_guards == "device":
+            self._pending_metrics.append(vals)                   # no host sync inside the step
+            return
+        self._append_metrics(vals.tolist())
+
+    def flush_metrics(self) -> None:
+        """Move the metrics kept on the device (``nan_guards="device"``) into the reference's lists: one sync."""
+        if self._pending_metrics:
+            rows = torch.stack(self._pending_metrics).tolist()
+            self._pending_metrics.clear()
+            for r in rows:
+                self._append_metrics(r)
+
+    def _append_metrics(self, vals) -> None:
         l2, pct, mx, mean, std = vals
         violation = max(0.0, mx - float(self.voxel_error_bound.max()))
         self.l2_norms.append(l2)
@@ -284,6 +323,7 @@ class VoxelPerturber(nn.Module):
                                             constraint_violation=violation))
 
     def save_l2_norms(self, filename: str = "l2_norms.csv") -> None:
+        self.flush_metrics()
         with open(filename, "w", newline="") as f:
             w = csv.writer(f)
             w.writerow(["L2 Norm", "L2 Percentage", "Constraint Violations"])

@@ -113,3 +113,38 @@ def test_module_fused_equals_aten_path(golden_dir):
         assert outs[0][1][k] == pytest.approx(outs[1][1][k], rel=1e-4, abs=1e-8)
     for a, b in zip(outs[0][2], outs[1][2]):
         np.testing.assert_allclose(a, b, rtol=1e-3, atol=1e-5)
+
+
+def test_device_nan_guards(golden_dir):
+    """nan_guards="device": same results as the host checks, decided by a device flag (no sync inside forward)"""
+    g = np.load(os.path.join(golden_dir, "perturber_kitti_train.npz"))
+    x = torch.from_numpy(g["x"]).to(DEV)
+    res = {}
+    for mode in (True, "device"):
+        torch.manual_seed(0)
+        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], nan_guards=mode).to(DEV)
+        adv.train()
+        y, ld = adv(x)
+        res[mode] = (y.detach().cpu().numpy(), {k: float(v.detach()) for k, v in ld.items()}, adv)
+    assert np.array_equal(res[True][0], res["device"][0]) and res[True][1] == res["device"][1]
+    adv = res["device"][2]
+    assert adv.l2_norms == [] and not adv.check_guards()            # metrics still on the device
+    adv.flush_metrics()
+    assert adv.l2_norms == pytest.approx(res[True][2].l2_norms) and len(adv.perturbation_stats) == 1
+    # a NaN in the input: the reference returns x unchanged and a zero loss (:150-153)
+    xb = x.clone()
+    xb[5, 2] = float("nan")
+    y, ld = adv(xb)
+    assert torch.equal(torch.nan_to_num(y, nan=-7.0), torch.nan_to_num(xb, nan=-7.0))
+    assert all(float(v.detach()) == 0.0 for v in ld.values())
+    assert adv.check_guards()
+    y2, ld2 = res[True][2](xb)
+    assert y2 is xb and float(ld2) == 0.0
+    # NaN weights: flagged on the device, reset by check_guards like :197
+    with torch.no_grad():
+        next(adv.model.parameters()).fill_(float("nan"))
+    y, ld = adv(x)
+    assert torch.equal(y, x) and adv.check_guards()
+    assert not any(torch.isnan(q).any() for q in adv.parameters())
+    y, ld = adv(x)
+    assert not adv.check_guards() and float(ld["l2_norm"].detach()) > 0.0
