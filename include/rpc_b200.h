@@ -225,6 +225,17 @@ int rpc_allreduce_oneshot(float *const *stage0 /*[host]*/, float *const *stage1 
                           float *out, uint32_t *counter, int32_t *status, void *stream);
 
 /* ---------------------------------------------------------------------------------------------------
+ * Hand-off to the middle encoder.  coors rows are already (batch, z, y, x) int32, the order
+ * spconv's SparseConvTensor takes (adversarial_voxelnet.py:140-141, adversarial_centerpoint.py:105-106), and
+ * the batch size is the caller's B (no coors[-1, 0].item()).  rpc_voxel_centers adds the `voxel_centers` output of
+ * mmdet3d Det3DDataPreprocessor.voxelize: centers[v] = (coors[v, (x, y, z)] + 0.5) * voxel_size + range_min,
+ * fp32, multiply and add unfused like the ATen expression; coors [M, ncol] with ncol 3 (z, y, x) or 4; only the
+ * first min(M, *m_dev) rows are written when m_dev (device) is given.
+ * ------------------------------------------------------------------------------------------------- */
+int rpc_voxel_centers(const rpc_voxel_cfg *cfg, const int32_t *coors, int ncol, int64_t M, const int32_t *m_dev,
+                      float *centers, void *stream);
+
+/* ---------------------------------------------------------------------------------------------------
  * The elementwise / reduction parts of VoxelPerturber.forward around its MLP, without host
  * syncs.  `moments` is rpc_moments_bytes() of device scratch (fp64 accumulators, zeroed by the call).
  *   rpc_normalize_fwd       xn = clamp(x / (std(x, dim 0) + 1e-6), -10, 10); NaN / Inf scale -> unit scaling

@@ -24,7 +24,7 @@ SYMBOLS = (
     "rpc_valid_rows_workspace_bytes", "rpc_valid_rows", "rpc_scatter_rows", "rpc_gather_rows",
     "rpc_perturb_apply_fwd", "rpc_perturb_apply_bwd",
     "rpc_dynamic_workspace_bytes", "rpc_dynamic_scatter_mean_fwd", "rpc_dynamic_stamps_offset", "rpc_allreduce_flag_bytes", "rpc_allreduce_oneshot",
-    "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
+    "rpc_voxel_centers", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
 )
 
 
@@ -108,6 +108,7 @@ def lib() -> ctypes.CDLL:
     L.rpc_perturb_apply_bwd.argtypes = [vp, vp, pcp, i64, vp, i32, vp, vp]
     L.rpc_allreduce_flag_bytes.restype = sz
     L.rpc_allreduce_oneshot.argtypes = [ctypes.POINTER(vp), ctypes.POINTER(vp), ctypes.POINTER(vp), i32, i32, i64, vp, vp, vp, vp, vp]
+    L.rpc_voxel_centers.argtypes = [ctypes.POINTER(VoxelCfg), vp, i32, i64, vp, vp, vp]
     L.rpc_moments_bytes.restype = sz
     L.rpc_normalize_fwd.argtypes = [vp, i64, vp, i32, vp, vp, vp]
     L.rpc_perturb_losses_fwd.argtypes = [vp, i64, vp, i32, vp, vp, vp, vp]

@@ -629,6 +629,20 @@ RPC_API int rpc_gather_rows(const float *src, const int32_t *row_idx, int64_t K,
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
+RPC_API int rpc_voxel_centers(const rpc_voxel_cfg *cfg, const int32_t *coors, int ncol, int64_t M, const int32_t *m_dev,
+                              float *centers, void *stream)
+{
+    int st = check_cfg(cfg, false);
+    if (st) return st;
+    if ((ncol != 3 && ncol != 4) || M < 0) return RPC_ERR_CONFIG;
+    if (M == 0) return RPC_OK;
+    if (!coors || !centers) return RPC_ERR_NULL;
+    CenterDesc cd;
+    for (int d = 0; d < 3; ++d) { cd.vs[d] = cfg->voxel_size[d]; cd.lo[d] = cfg->pcr[d]; }
+    k_voxel_centers<<<stream_blocks(M * 3), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(coors, ncol, M, m_dev, cd, centers);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
 RPC_API int rpc_perturb_apply_fwd(const float *x, const float *raw, const rpc_perturb_cfg *pc, int64_t K,
                                   const int32_t *k_dev, int C, float *y, float *p_out, void *stream)
 {

@@ -129,4 +129,20 @@ k_perturb_apply_bwd(const float *__restrict__ grad_p, const float *__restrict__ 
     }
 }
 
+// voxel_centers of Det3DDataPreprocessor.voxelize: (coors[:, [x, y, z]] + 0.5) * voxel_size + range_min, the same
+// fp32 operations in the same order as the ATen expression (separate multiply and add)
+struct CenterDesc { float vs[3], lo[3]; };
+__global__ void __launch_bounds__(kThreads)
+k_voxel_centers(const int *__restrict__ coors, int ncol, int64_t M, const int *__restrict__ m_dev,
+                const __grid_constant__ CenterDesc cd, float *__restrict__ out)
+{
+    if (m_dev) M = min(M, (int64_t)*m_dev);
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < M * 3; e += (int64_t)gridDim.x * kThreads) {
+        const int64_t v = e / 3;
+        const int d = (int)(e - v * 3);                              // 0: x, 1: y, 2: z; coors rows end in (z, y, x)
+        const float c = (float)__ldg(coors + v * ncol + (ncol - 1 - d));
+        out[e] = __fadd_rn(__fmul_rn(__fadd_rn(c, 0.5f), cd.vs[d]), cd.lo[d]);
+    }
+}
+
 }  // namespace rpc

@@ -396,3 +396,15 @@ def perturb_losses_bwd(p: torch.Tensor, consts: torch.Tensor, grad_losses: torch
     st = _lib.lib().rpc_perturb_losses_bwd(_ptr(p), _ptr(consts), _ptr(grad_losses), K, None, C, _ptr(g), _stream(dev))
     _lib.check(st, "rpc_perturb_losses_bwd")
     return g
+
+
+def voxel_centers(coors: torch.Tensor, cfg: VoxelCfg, m_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``voxel_centers`` of mmdet3d's ``Det3DDataPreprocessor.voxelize``: [M, 3] (x, y, z) centres of the voxels whose
+    coors rows end in (z, y, x)."""
+    dev = _need_cuda(coors)
+    coors = coors.contiguous()
+    M, ncol = coors.shape
+    out = torch.empty((M, 3), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_voxel_centers(ctypes.byref(cfg), _ptr(coors), ncol, M, _ptr(m_dev), _ptr(out), _stream(dev))
+    _lib.check(st, "rpc_voxel_centers")
+    return out

@@ -83,9 +83,7 @@ def voxelize(points: List[torch.Tensor], voxel_layer: Voxelization, voxel_type: 
         out = ops.hard_voxelize(cat, n, cfg)
         m = out.total() if sync else out.capacity
         coors = out.coors[:m]
-        vs = torch.tensor(voxel_layer.voxel_size, dtype=torch.float32, device=cat.device)
-        lo = torch.tensor(voxel_layer.point_cloud_range[:3], dtype=torch.float32, device=cat.device)
-        centers = (coors[:, [3, 2, 1]].float() + 0.5) * vs + lo
+        centers = ops.voxel_centers(coors, cfg, None if sync else out.voxel_num[-1:])
         d = dict(voxels=out.voxels[:m], coors=coors, num_points=out.num_points[:m], voxel_centers=centers)
         if not sync:
             d["voxel_num"] = out.voxel_num

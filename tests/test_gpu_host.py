@@ -164,6 +164,15 @@ def test_voxelize_batch_dict_vs_oracle(preset):
         for k in ("voxels", "coors", "num_points"):
             assert np.array_equal(d[k].cpu().numpy(), ref[k]), k
         _close(d["voxel_centers"].cpu().numpy(), ref["voxel_centers"])
+        # rpc_voxel_centers: bit-exact with the ATen expression of Det3DDataPreprocessor.voxelize
+        vs = torch.tensor(cfgd["voxel_size"], device=DEV)
+        lo = torch.tensor(cfgd["point_cloud_range"][:3], device=DEV)
+        aten = (d["coors"][:, [3, 2, 1]].float() + 0.5) * vs + lo
+        assert torch.equal(d["voxel_centers"], aten)
+        assert torch.equal(ops.voxel_centers(d["coors"][:, 1:].contiguous(), layer.cfg(clouds[0].shape[1])), aten)
+        lazy = rpc.voxelize(pts, layer, "hard", sync=False)              # capacity-sized, counted on the device
+        m = int(lazy["voxel_num"][-1])
+        assert m == d["coors"].shape[0] and torch.equal(lazy["voxel_centers"][:m], aten)
     # module API on one cloud: (voxels, coors zyx, num_points); dynamic: per-point coors
     v, c, n = layer(pts[0])
     rv, rc, rn = orc.hard_voxelize(clouds[0], cfgd["voxel_size"], cfgd["point_cloud_range"], cfgd["max_num_points"], 4000)

@@ -196,3 +196,7 @@ def test_perturber_statistics_entries_without_gpu():
     assert L.rpc_perturb_losses_fwd(None, 10, None, 5, None, None, None, None) == -1
     assert L.rpc_perturb_losses_bwd(None, None, None, 10, None, 5, None, None) == -1
     assert L.rpc_perturb_losses_bwd(None, None, None, 0, None, 5, None, None) == 0
+    cfg = rpc.VoxelCfg.make([0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1], 5, 16000, 4)
+    assert L.rpc_voxel_centers(ctypes.byref(cfg), None, 5, 10, None, None, None) == -2       # coors rows of 3 or 4
+    assert L.rpc_voxel_centers(ctypes.byref(cfg), None, 4, 10, None, None, None) == -1
+    assert L.rpc_voxel_centers(ctypes.byref(cfg), None, 4, 0, None, None, None) == 0
