@@ -254,6 +254,21 @@ int rpc_perturb_losses_fwd(const float *p, int64_t K, const int32_t *k_dev, int 
 int rpc_perturb_losses_bwd(const float *p, const float *consts, const float *grad_losses, int64_t K,
                            const int32_t *k_dev, int C, float *grad_p, void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Post-VFE perturbation variant: the elementwise part of
+ * StrongAdversarialVoxelNet.apply_enhanced_perturbations (models/detectors/strong_adversarial_voxelnet.py:156-180)
+ * on n = M * C features: sp = (y - x) * scaling [+ alpha * last] (last may be NULL: no momentum yet; y_is_delta != 0:
+ * the adversary returned the perturbation itself, :159-161, and y - x is replaced by y);
+ * out = x + sp; sp_out = sp (the next call's `last`); l2[0] = ||sp||_2 (device; sumsq: 8 bytes of device scratch).
+ * The backward takes the gradients on out (g_out, may be NULL) and on l2 (g_l2, device scalar, may be NULL) and
+ * writes grad_x and / or grad_y (either may be NULL).
+ * ------------------------------------------------------------------------------------------------- */
+int rpc_momentum_apply_fwd(const float *x, const float *y, const float *last, int y_is_delta, float scaling,
+                           float alpha, int64_t n, float *out, float *sp_out, double *sumsq, float *l2, void *stream);
+int rpc_momentum_apply_bwd(const float *g_out, const float *g_l2, const float *sp, const float *l2, int y_is_delta,
+                           float scaling,
+                           int64_t n, float *grad_x, float *grad_y, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

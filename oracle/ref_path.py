@@ -352,3 +352,39 @@ def build_mlp(C: int, hidden: Sequence[int], state: Optional[Dict[str, np.ndarra
         attention.load_state_dict({k[len("attention."):]: torch.from_numpy(np.asarray(v))
                                    for k, v in state.items() if k.startswith("attention.")})
     return model, attention
+
+
+# ------------------------------------------------------------------ post-VFE variant
+def adversarial_strength(epoch: int, iteration: int, history: Sequence[float], dynamic_scaling: bool = True,
+                         curriculum_learning: bool = True, max_scaling: float = 5.0) -> float:
+    """/root/reference/models/detectors/strong_adversarial_voxelnet.py:114-138"""
+    if not dynamic_scaling:
+        return 1.0
+    s = min(1.0 + epoch * 0.1, max_scaling)
+    if len(history) > 50:
+        avg = float(np.mean([abs(v) for v in history[-50:]]))
+        s *= 2.0 if avg < 0.1 else 1.5 if avg < 0.3 else 1.0
+    if curriculum_learning:
+        s *= min(1.0 + iteration / 10000.0, 2.0)
+    return min(s, max_scaling)
+
+
+def enhanced_perturbation(x: np.ndarray, y: np.ndarray, last: Optional[np.ndarray], scaling: float, alpha: float,
+                          y_is_delta: bool = False):
+    """strong_adversarial_voxelnet.py:152-180 in fp32: -> (perturbed, scaled_perturbations, l2 as float64)"""
+    x, y = _f32(x), _f32(y)
+    p = y if y_is_delta else (y - x)
+    sp = (p * np.float32(scaling)).astype(np.float32)
+    if last is not None and last.shape == sp.shape:
+        sp = (sp + (np.float32(alpha) * _f32(last)).astype(np.float32)).astype(np.float32)
+    return (x + sp).astype(np.float32), sp, float(np.sqrt(np.sum(sp.astype(np.float64) ** 2)))
+
+
+def enhanced_perturbation_bwd(g_out: np.ndarray, g_l2: float, sp: np.ndarray, scaling: float, y_is_delta: bool = False):
+    """autograd of the above: (grad_x, grad_y) in float64"""
+    sp64 = sp.astype(np.float64)
+    l2 = np.sqrt(np.sum(sp64 ** 2))
+    gsp = g_out.astype(np.float64) + (g_l2 * sp64 / l2 if l2 > 0 else 0.0)
+    gy = scaling * gsp
+    gx = g_out.astype(np.float64) if y_is_delta else g_out.astype(np.float64) - gy
+    return gx, gy

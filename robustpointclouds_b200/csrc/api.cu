@@ -754,4 +754,31 @@ RPC_API int rpc_perturb_losses_bwd(const float *p, const float *consts, const fl
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
+RPC_API int rpc_momentum_apply_fwd(const float *x, const float *y, const float *last, int y_is_delta, float scaling,
+                                   float alpha, int64_t n, float *out, float *sp_out, double *sumsq, float *l2, void *stream)
+{
+    if (n < 0) return RPC_ERR_CONFIG;
+    if (!sumsq || !l2) return RPC_ERR_NULL;
+    if (n > 0 && (!x || !y || !out || !sp_out)) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(sumsq, 0, sizeof(double), st) != cudaSuccess) return RPC_ERR_CUDA;
+    if (n > 0) {
+        int64_t blocks = (n + kThreads - 1) / kThreads;
+        if (blocks > kNumSM * 8) blocks = kNumSM * 8;
+        k_momentum_apply_fwd<<<(int)blocks, kThreads, 0, st>>>(x, y, last, y_is_delta, scaling, alpha, n, out, sp_out, sumsq);
+    }
+    k_momentum_l2<<<1, 32, 0, st>>>(sumsq, l2);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_momentum_apply_bwd(const float *g_out, const float *g_l2, const float *sp, const float *l2,
+                                   int y_is_delta, float scaling, int64_t n, float *grad_x, float *grad_y, void *stream)
+{
+    if (n < 0) return RPC_ERR_CONFIG;
+    if (n == 0) return RPC_OK;
+    if (!sp || !l2 || (!grad_x && !grad_y)) return RPC_ERR_NULL;
+    k_momentum_apply_bwd<<<stream_blocks(n), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(g_out, g_l2, sp, l2, y_is_delta, scaling, n, grad_x, grad_y);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
 }  // extern "C"

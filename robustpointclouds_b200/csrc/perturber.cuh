@@ -162,4 +162,58 @@ k_losses_bwd(const float *__restrict__ p, const float *__restrict__ consts, cons
     }
 }
 
+// ---- post-VFE variant: StrongAdversarialVoxelNet.apply_enhanced_perturbations
+// (/root/reference/models/detectors/strong_adversarial_voxelnet.py:156-180)
+//   sp = (y - x) * scaling [+ alpha * last]   (y_is_delta: the adversary returned the perturbation itself, sp = y * scaling ...)
+//    out = x + sp;  last' = sp;  l2 = ||sp||_2 over all elements
+// One pass instead of five ATen kernels; the elementwise results are the same fp32 operations in the same order.
+__global__ void __launch_bounds__(kThreads)
+k_momentum_apply_fwd(const float *__restrict__ x, const float *__restrict__ y, const float *__restrict__ last,
+                     int y_is_delta, float scaling, float alpha, int64_t n, float *__restrict__ out,
+                     float *__restrict__ sp_out, double *__restrict__ sumsq)
+{
+    double acc = 0.0;
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < n; e += (int64_t)gridDim.x * kThreads) {
+        const float xv = __ldg(x + e);
+        const float yv = __ldg(y + e);
+        float sp = __fmul_rn(y_is_delta ? yv : __fsub_rn(yv, xv), scaling);
+        if (last) sp = __fadd_rn(sp, __fmul_rn(alpha, __ldg(last + e)));
+        out[e] = __fadd_rn(xv, sp);
+        sp_out[e] = sp;
+        acc += (double)sp * (double)sp;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_down_sync(0xFFFFFFFFu, acc, d);
+    __shared__ double sh[kThreads / 32];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < kThreads / 32; ++w) t += sh[w];
+        atomicAdd(sumsq, t);
+    }
+}
+
+__global__ void k_momentum_l2(const double *__restrict__ sumsq, float *__restrict__ l2)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) *l2 = (float)sqrt(*sumsq);
+}
+
+// g_sp = g_out + g_l2 * sp / l2 (second term 0 when l2 == 0, torch's norm backward);  grad_y = scaling * g_sp;
+// grad_x = g_out - scaling * g_sp.  g_out or g_l2 may be NULL (no gradient arrived on that output).
+__global__ void __launch_bounds__(kThreads)
+k_momentum_apply_bwd(const float *__restrict__ g_out, const float *__restrict__ g_l2, const float *__restrict__ sp,
+                     const float *__restrict__ l2, int y_is_delta, float scaling, int64_t n,
+                     float *__restrict__ grad_x, float *__restrict__ grad_y)
+{
+    const float nrm = __ldg(l2);
+    const float w = (g_l2 && nrm > 0.0f) ? __ldg(g_l2) / nrm : 0.0f;
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < n; e += (int64_t)gridDim.x * kThreads) {
+        const float go = g_out ? __ldg(g_out + e) : 0.0f;
+        const float gsp = go + w * __ldg(sp + e);
+        if (grad_y) grad_y[e] = scaling * gsp;
+        if (grad_x) grad_x[e] = y_is_delta ? go : go - scaling * gsp;
+    }
+}
+
 }  // namespace rpc

@@ -408,3 +408,33 @@ def voxel_centers(coors: torch.Tensor, cfg: VoxelCfg, m_dev: Optional[torch.Tens
     st = _lib.lib().rpc_voxel_centers(ctypes.byref(cfg), _ptr(coors), ncol, M, _ptr(m_dev), _ptr(out), _stream(dev))
     _lib.check(st, "rpc_voxel_centers")
     return out
+
+
+def momentum_apply_fwd(x: torch.Tensor, y: torch.Tensor, last: Optional[torch.Tensor], scaling: float, alpha: float,
+                       y_is_delta: bool = False):
+    """(out = x + sp, sp = (y - x) * scaling [+ alpha * last], l2 = ||sp||_2 as a 0-d device tensor);
+    /root/reference/models/detectors/strong_adversarial_voxelnet.py:156-180."""
+    dev = _need_cuda(x, y, last)
+    x, y = _f32c(x), _f32c(y)
+    last = _f32c(last) if last is not None else None
+    out, sp = torch.empty_like(x), torch.empty_like(x)
+    sumsq = torch.empty((1,), dtype=torch.float64, device=dev)
+    l2 = torch.empty((), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_momentum_apply_fwd(_ptr(x), _ptr(y), _ptr(last), int(y_is_delta), scaling, alpha, x.numel(), _ptr(out), _ptr(sp),
+                                           _ptr(sumsq), _ptr(l2), _stream(dev))
+    _lib.check(st, "rpc_momentum_apply_fwd")
+    return out, sp, l2
+
+
+def momentum_apply_bwd(g_out: Optional[torch.Tensor], g_l2: Optional[torch.Tensor], sp: torch.Tensor, l2: torch.Tensor,
+                       scaling: float, want_x: bool = True, want_y: bool = True, y_is_delta: bool = False):
+    dev = _need_cuda(sp, l2)
+    g_out = _f32c(g_out) if g_out is not None else None
+    g_l2 = _f32c(g_l2) if g_l2 is not None else None
+    gx = torch.empty_like(sp) if want_x else None
+    gy = torch.empty_like(sp) if want_y else None
+    if want_x or want_y:
+        st = _lib.lib().rpc_momentum_apply_bwd(_ptr(g_out), _ptr(g_l2), _ptr(sp), _ptr(l2), int(y_is_delta), scaling, sp.numel(),
+                                               _ptr(gx), _ptr(gy), _stream(dev))
+        _lib.check(st, "rpc_momentum_apply_bwd")
+    return gx, gy

@@ -200,3 +200,17 @@ def test_perturber_statistics_entries_without_gpu():
     assert L.rpc_voxel_centers(ctypes.byref(cfg), None, 5, 10, None, None, None) == -2       # coors rows of 3 or 4
     assert L.rpc_voxel_centers(ctypes.byref(cfg), None, 4, 10, None, None, None) == -1
     assert L.rpc_voxel_centers(ctypes.byref(cfg), None, 4, 0, None, None, None) == 0
+    assert L.rpc_momentum_apply_fwd(None, None, None, 0, 1.0, 0.9, 10, None, None, None, None, None) == -1
+    assert L.rpc_momentum_apply_bwd(None, None, None, None, 0, 1.0, -1, None, None, None) == -2
+    assert L.rpc_momentum_apply_bwd(None, None, None, None, 0, 1.0, 0, None, None, None) == 0
+
+
+def test_strength_schedule_host_logic():
+    """strong_adversarial_voxelnet.py:114-138: epoch ramp, weak-attack boost, curriculum factor, cap"""
+    ep = rpc.EnhancedPerturbation(None)
+    assert ep.update_adversarial_strength() == 1.0
+    ep._epoch, ep._iteration = 10, 5000
+    assert ep.update_adversarial_strength() == pytest.approx(2.0 * 1.5)
+    ep._attack_history = [0.05] * 51
+    assert ep.update_adversarial_strength() == 5.0                       # 2.0 * 2.0 * 1.5 capped at max_scaling
+    assert ep.update_adversarial_strength() == orc.adversarial_strength(10, 5000, [0.05] * 51)
