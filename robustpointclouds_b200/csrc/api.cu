@@ -291,7 +291,7 @@ RPC_API int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points,
     if (raw && !pc) return RPC_ERR_NULL;
     if (workspace_bytes < pl.bytes) return RPC_ERR_WORKSPACE;
     if (misaligned(points) || misaligned(raw) || misaligned(voxels) || misaligned(coors) ||
-        misaligned(workspace) || misaligned(feats))
+        (reinterpret_cast<uintptr_t>(workspace) & 31u) != 0 || misaligned(feats))      // buckets are read as 32 bytes
         return RPC_ERR_ALIGN;
     PerturbDesc pd;
     fill_perturb(cfg, pc, &pd);
