@@ -93,7 +93,7 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
     size_t o = 0;
     pl->o_tab = o;   o += align_up(8 * (size_t)tab);
     pl->o_hslot = o; o += align_up(4 * (size_t)pts);
-    pl->o_tiles = o; o += align_up(4 * (size_t)(tiles + 2));       // + the gather task counter
+    pl->o_tiles = o; o += align_up(8 * (size_t)(tiles + 1));       // 8 per-warp byte counts per tile
     pl->o_slots = o; o += align_up(4 * (size_t)cap * cfg->max_points);
     pl->o_stamps = o; o += align_up(8 * 16 * 1024);
     pl->bytes = o;
@@ -190,7 +190,7 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     fp.pts = points; fp.raw = raw;
     fp.tab = reinterpret_cast<unsigned long long *>(w + pl.o_tab);
     fp.hslot = reinterpret_cast<uint32_t *>(w + pl.o_hslot);
-    fp.tile_cnt = reinterpret_cast<int *>(w + pl.o_tiles);
+    fp.wcnt = reinterpret_cast<unsigned long long *>(w + pl.o_tiles);
     fp.slots = reinterpret_cast<int *>(w + pl.o_slots);
     fp.stamps = g_prof.on ? reinterpret_cast<unsigned long long *>(w + pl.o_stamps) : nullptr;
     fp.voxels = voxels; fp.coors = coors; fp.num_points = num_points; fp.voxel_num = voxel_num;

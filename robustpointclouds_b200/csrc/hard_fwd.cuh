@@ -49,7 +49,7 @@ struct FwdParams {
     const float *pts, *raw;                     // [ntotal, C]
     unsigned long long *tab;                    // [tab_total] (cell << 32) | first index, later | voxel row
     uint32_t *hslot;                            // [ntotal]   table entry of each point + flag bits
-    int *tile_cnt;                              // [ntiles]   first points per tile
+    unsigned long long *wcnt;                   // [ntiles]   first points per warp of the tile, one byte each
     int *slots;                                 // [cap * P]  per voxel: point index per slot, kInf empty
     float *voxels; int *coors; int *num_points; int *voxel_num; int *p2v; int *p2s; float *feats;
     unsigned long long *stamps;                 // [gridDim][16] %globaltimer per CTA and phase, or NULL
@@ -128,6 +128,12 @@ __device__ __forceinline__ int my_tile(int ntiles, int it)
 {
     const int t = (int)blockIdx.x + (it * kSub + (int)(threadIdx.x >> 8)) * (int)gridDim.x;
     return t < ntiles ? t : -1;
+}
+
+// sum of the 8 per-warp byte counts of a tile (each <= 32)
+__device__ __forceinline__ int tile_first_points(unsigned long long w8)
+{
+    return (int)(__vsadu4((uint32_t)w8, 0u) + __vsadu4((uint32_t)(w8 >> 32), 0u));
 }
 
 // exclusive rank of every flagged thread within its tile (8 warps) and the tile total.  sm: 32 ints.
@@ -377,9 +383,11 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         const uint32_t lo = (hs != kDropped && (hs & kCandBit)) ? (uint32_t)__ldcg(p.tab + (hs & kEntryMask)) : 0xFFFFFFFEu;
         const bool f = lo == (uint32_t)idx;
         if (f) p.hslot[idx] = hs | kFirstBit;
-        int rank, total;
-        tile_rank_flags(f, rank, total, sm);
-        if ((tid & (kTile - 1)) == 0 && tile >= 0) p.tile_cnt[tile] = total;
+        // first points per warp, one byte per warp of the tile: no CTA barrier in this phase, and P3 gets both
+        // the tile total and the warp's offset inside the tile from one 8-byte load
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, f);
+        if (wlane == 0 && tile >= 0)
+            reinterpret_cast<unsigned char *>(p.wcnt)[(size_t)tile * 8 + (wid & 7)] = (unsigned char)__popc(bal);
     }
     if (p.stamps) __syncthreads();
     stamp(p, 10);
@@ -393,11 +401,20 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     {
         const int per = (p.ntiles + kPT - 1) / kPT;
         const int j0 = tid * per, j1 = min(j0 + per, p.ntiles);
-        int s = 0;
-        for (int j = j0; j < j1; ++j) s += __ldcg(p.tile_cnt + j);
+        constexpr int kKeep = 6;                                     // counts kept in registers between the two passes
+        int s = 0, c[kKeep];
+#pragma unroll
+        for (int q = 0; q < kKeep; ++q) {
+            c[q] = j0 + q < j1 ? tile_first_points(__ldcg(p.wcnt + j0 + q)) : 0;
+            s += c[q];
+        }
+        for (int j = j0 + kKeep; j < j1; ++j) s += tile_first_points(__ldcg(p.wcnt + j));
         int tot;
         int run = block_excl_scan<kPT>(s, sm, &tot);
-        for (int j = j0; j < j1; ++j) { prefix[j] = run; run += __ldcg(p.tile_cnt + j); }
+#pragma unroll
+        for (int q = 0; q < kKeep; ++q)
+            if (j0 + q < j1) { prefix[j0 + q] = run; run += c[q]; }
+        for (int j = j0 + kKeep; j < j1; ++j) { prefix[j] = run; run += tile_first_points(__ldcg(p.wcnt + j)); }
         if (tid == kPT - 1) prefix[p.ntiles] = tot;
         __syncthreads();
         if (tid == 0) {
@@ -413,6 +430,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         __syncthreads();
     }
+    const int lvl_step = kTile % P;
     for (int it = 0; it < iters; ++it) {
         TileRange tr;
         const int tile = my_range(it, tr);
@@ -424,15 +442,24 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             if (tr.begin + (tid & (kTile - 1)) < tr.end) { idx = tr.begin + (tid & (kTile - 1)); hs = __ldcg(p.hslot + idx); }
         }
         const bool f = hs != kDropped && (hs & kFirstBit);
-        int rank, total;
-        tile_rank_flags(f, rank, total, sm);
-        // slot lists of the tile's admitted voxels: rows [voff+base, voff+min(base+total, V)) := kInf
+        // rank of a first point inside its tile = first points of the tile's earlier warps (the bytes P2 wrote)
+        // + earlier lanes of this warp; no CTA barrier
+        const unsigned long long w8 = tile >= 0 ? __ldcg(p.wcnt + tile) : 0ull;
+        const int total = tile_first_points(w8);
+        const int rank = tile_first_points(w8 & ((1ull << (8 * (wid & 7))) - 1ull)) +
+                         __popc(__ballot_sync(0xFFFFFFFFu, f) & ((1u << wlane) - 1u));
+        // slot lists of the tile's admitted voxels: rows [voff+base, voff+min(base+total, V)), levels 1.. := kInf
+        // (level 0 is written by the first point's own thread below, so the two need no ordering)
         {
             const int r0 = min(base, V), r1 = min(base + total, V);
             int *sl = p.slots + (int64_t)(voff + r0) * P;
-            for (int t = tid & (kTile - 1); t < (r1 - r0) * P; t += kTile) sl[t] = kInf;
+            int lvl = (tid & (kTile - 1)) % P;                       // level of element t, kept without a division
+            for (int t = tid & (kTile - 1); t < (r1 - r0) * P; t += kTile) {
+                if (lvl) sl[t] = kInf;
+                lvl += lvl_step;
+                if (lvl >= P) lvl -= P;
+            }
         }
-        __syncthreads();
         if (f) {
             const int r = base + rank;
             uint32_t *lo = reinterpret_cast<uint32_t *>(p.tab + (hs & kEntryMask));   // low word
