@@ -36,6 +36,7 @@ constexpr int kPT = 1024;                       // threads per CTA of the persis
 constexpr int kTile = 256;                      // points per tile: the unit that is dealt to the CTAs
 constexpr int kSub = kPT / kTile;               // tiles a CTA works on per iteration (8 warps each)
 constexpr int kCtasPerSM = 2;                   // resident CTAs per SM (register cap 32 at 1024 threads)
+constexpr int kOptProbes = 2;                   // blind CAS probes of the insert phase before it starts loading buckets
 constexpr int kTrCache = 128;                    // tile ranges cached in shared memory per CTA (2 KB)
 constexpr int kMaxTiles = 24576;                // tile counts are scanned in shared memory (96 KB per CTA)
 constexpr uint32_t kDropped = 0xFFFFFFFFu;      // hslot: point outside the range
@@ -325,9 +326,35 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         if constexpr (kTma) __syncwarp();                            // the stage may be refilled from here on
         if (p.stamps && it == 0) { __syncthreads(); stamp(p, 13); }
-        uint32_t bkt = cell >= 0 ? probe_start((uint32_t)cell, nb) : 0u;
-        int j0 = 0;                                                  // first slot of the bucket still to look at
+        // Probe order of a cell: linear over the entries from its home entry.  The first kOptProbes probes are
+        // blind CASes (claim-or-find in ONE L2 round trip: at LiDAR load factors ~0.3 the home entry is free or
+        // already the cell's own for most points); whoever is still pending goes on in the same order with
+        // 32-byte bucket loads, which look at up to four entries per round trip.
+        uint32_t pos = cell >= 0 ? probe_start((uint32_t)cell, nb << 2) : 0u;
         bool pend = cell >= 0;
+        const unsigned long long mine = ((unsigned long long)(uint32_t)cell << 32) | (uint32_t)idx;
+#pragma unroll 1
+        for (int k = 0; k < kOptProbes; ++k) {
+            if (pend) {
+                uint32_t h = off + pos;
+                const unsigned long long old = atomicCAS(&p.tab[h], kEmpty64, mine);
+                if (old == kEmpty64) {
+                    p.hslot[idx] = h | kCandBit;                     // claimed: first so far
+                    pend = false;
+                } else if ((uint32_t)(old >> 32) == (uint32_t)cell) {
+                    if ((uint32_t)old > (uint32_t)idx) {
+                        atomicMin(&p.tab[h], mine);
+                        h |= kCandBit;                               // displaced a later point
+                    }
+                    p.hslot[idx] = h;
+                    pend = false;
+                } else {
+                    pos = pos + 1 == (nb << 2) ? 0u : pos + 1;
+                }
+            }
+        }
+        uint32_t bkt = pos >> 2;
+        int j0 = (int)(pos & 3u);                                    // first slot of the bucket still to look at
         while (pend) {
 #ifndef RPC_NO_LD256
             unsigned long long e[4];                                 // the whole 32-byte bucket with one 256-bit load
@@ -345,7 +372,6 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             if (j == 4) { bkt = bkt + 1 == nb ? 0 : bkt + 1; j0 = 0; continue; }
             unsigned long long old = j == 0 ? e[0] : j == 1 ? e[1] : j == 2 ? e[2] : e[3];
             j0 = j;
-            const unsigned long long mine = ((unsigned long long)(uint32_t)cell << 32) | (uint32_t)idx;
             if (old == kEmpty64) {
                 old = atomicCAS(&p.tab[off + 4 * bkt + j], kEmpty64, mine);
                 if (old != kEmpty64 && (uint32_t)(old >> 32) != (uint32_t)cell) {
