@@ -36,7 +36,12 @@ constexpr int kPT = 1024;                       // threads per CTA of the persis
 constexpr int kTile = 256;                      // points per tile: the unit that is dealt to the CTAs
 constexpr int kSub = kPT / kTile;               // tiles a CTA works on per iteration (8 warps each)
 constexpr int kCtasPerSM = 2;                   // resident CTAs per SM (register cap 32 at 1024 threads)
-constexpr int kOptProbes = 2;                   // blind CAS probes of the insert phase before it starts loading buckets
+#ifndef RPC_OPT_PROBES
+#define RPC_OPT_PROBES 2
+#endif
+constexpr int kOptProbes = RPC_OPT_PROBES;                   // blind CAS probes of the insert phase before it starts loading buckets
+constexpr int kIlp = 4;                          // iterations of the rank phase taken together per thread ...
+constexpr int kIlpMinP = 8;                      // ... when the slot lists are at least this long
 constexpr int kTrCache = 128;                    // tile ranges cached in shared memory per CTA (2 KB)
 constexpr int kMaxTiles = 24576;                // tile counts are scanned in shared memory (96 KB per CTA)
 constexpr uint32_t kDropped = 0xFFFFFFFFu;      // hslot: point outside the range
@@ -508,7 +513,10 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // minimum of a level is carried exactly once, so level q ends up holding the (q+1)-th smallest
     // index regardless of interleaving.  Slot 0 is the first point (already known).  An index
     // larger than the current last level can never enter the list, which prunes crowded voxels.
-    if (P > 1) {
+    // kIlp iterations of a thread are taken together, stage by stage (entry words, voxel rows, last levels, then
+    // the chains level by level), so that their L2 round trips overlap instead of adding up.
+    if (P > 1 && P < kIlpMinP) {
+        // short lists (KITTI: P = 5, most cells refused by the cap): one point at a time measured faster
         for (int it = 0; it < iters; ++it) {
             TileRange tr;
             const int tile = my_range(it, tr);
@@ -516,7 +524,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             const int idx = tr.begin + (tid & (kTile - 1));
             if (idx >= tr.end) continue;
             const uint32_t hs = __ldcg(p.hslot + idx);
-            if (hs == kDropped || (hs & kFirstBit)) continue;
+            if (hs & kFirstBit) continue;                                // first point or dropped (kDropped has the bit)
             const uint32_t v = (uint32_t)__ldcg(p.tab + (hs & kEntryMask));
             if (v == kRefused) continue;
             int *sl = p.slots + (int64_t)v * P;
@@ -524,9 +532,50 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             int carry = idx;
             for (int q = 1; q < P && carry != kInf; ++q) {
                 const int old = atomicMin(sl + q, carry);
-                if (old > carry) carry = old;                       // displaced (kInf: was free)
+                if (old > carry) carry = old;                           // displaced (kInf: was free)
             }
         }
+    } else if (P > 1) {
+        for (int it0 = 0; it0 < iters; it0 += kIlp) {
+            int carry[kIlp];
+            uint32_t v[kIlp];
+#pragma unroll
+            for (int u = 0; u < kIlp; ++u) {
+                carry[u] = kInf;
+                v[u] = kDropped;                                       // here: the point's hslot word
+                if (it0 + u < iters) {
+                    TileRange tr;
+                    const int tile = my_range(it0 + u, tr);
+                    const int idx = tr.begin + (tid & (kTile - 1));
+                    if (tile >= 0 && idx < tr.end) { carry[u] = idx; v[u] = __ldcg(p.hslot + idx); }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kIlp; ++u)                             // voxel row of the point's cell
+                v[u] = (v[u] & kFirstBit) ? kRefused : (uint32_t)__ldcg(p.tab + (v[u] & kEntryMask));   // kDropped has the bit
+            {
+                int last[kIlp];
+#pragma unroll
+                for (int u = 0; u < kIlp; ++u) last[u] = v[u] != kRefused ? __ldcg(p.slots + (int64_t)v[u] * P + P - 1) : 0;
+#pragma unroll
+                for (int u = 0; u < kIlp; ++u)
+                    if (last[u] <= carry[u]) carry[u] = kInf;           // cannot enter the list (or nothing to do)
+            }
+            for (int q = 1; q < P; ++q) {
+                bool any = false;
+#pragma unroll
+                for (int u = 0; u < kIlp; ++u) {
+                    if (carry[u] != kInf) {
+                        const int old = atomicMin(p.slots + (int64_t)v[u] * P + q, carry[u]);
+                        if (old > carry[u]) carry[u] = old;             // displaced (kInf: was free)
+                        any |= carry[u] != kInf;
+                    }
+                }
+                if (!any) break;
+            }
+        }
+    }
+    if (P > 1) {
         if (p.stamps) __syncthreads();
         stamp(p, 12);
         grid.sync();
