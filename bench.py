@@ -324,10 +324,10 @@ def run_b200(args):
         bwd()
 
     par = None
-    if world > 1 and args.allreduce == "p2p":
+    if world > 1 and args.allreduce in ("ll", "p2p"):
         from robustpointclouds_b200 import PeerAllReduce
         try:
-            par = PeerAllReduce(pgrad.numel(), dev)
+            par = PeerAllReduce(pgrad.numel(), dev, mode="ll" if args.allreduce == "ll" else "oneshot")
         except Exception as e:                          # no peer mapping on this box: every rank falls back together
             print(f"[bench] rank {rank}: peer all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
             par = None
@@ -505,7 +505,9 @@ def run_b200(args):
             "config": config_dict(args.workload, p, B, l2="flushed between steps, outside the per-step CUDA-event pairs: 512 MiB overwrite" +
                                   (" then a 256 MiB read-only sweep (L2 left full of clean lines)"
                                    if args.flush == "write+read" else ""), cuda_graph=graph is not None, voxels=M, kept_points=K,
-                                  collective=(("one-shot NVLink peer-memory all-reduce (rpc_allreduce_oneshot, in the step's graph)"
+                                  collective=((("low-latency NVLink peer-memory all-reduce (rpc_allreduce_ll: value + call number pushed as one 8-byte store, in the step's graph)"
+                                                if args.allreduce == "ll" else
+                                                "one-shot NVLink peer-memory all-reduce (rpc_allreduce_oneshot, in the step's graph)")
                                                if par is not None else "nccl all_reduce") +
                                               " of %d fp32 perturber grads per step" % pgrad.numel())
                                   if world > 1 else "none"),
@@ -536,7 +538,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="sweeps per GPU (default: 6 KITTI, 4 nuScenes)")
     ap.add_argument("--points", type=int, default=0, help="points per sweep (default: the preset's; BASELINE.json configs[4] sweep)")
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
+    ap.add_argument("--allreduce", default="ll", choices=["ll", "p2p", "nccl"],
                     help="N > 1: perturber-gradient all-reduce through this library's one-shot NVLink kernel or NCCL")
     ap.add_argument("--flush", default="write", choices=["write", "write+read"],
                     help="L2 flush between steps: 512 MiB overwrite, optionally followed by a 256 MiB read sweep")

@@ -224,6 +224,14 @@ int rpc_allreduce_oneshot(float *const *stage0 /*[host]*/, float *const *stage1 
                           uint32_t *const *peer_flags /*[host]*/, int rank, int world, int64_t n, const float *src,
                           float *out, uint32_t *counter, int32_t *status, void *stream);
 
+/* Low-latency variant of the same exchange: every rank pushes each value together with the call number as one
+ * 8-byte word into every peer's receive area and polls its own -- one one-way NVLink latency per call, no flag
+ * round trips.  recv[r] (host array of `world` device pointers) = rank r's peer-mapped receive area of
+ * rpc_allreduce_ll_bytes(world, n) bytes, zeroed once before the first call; counter / status as above. */
+size_t rpc_allreduce_ll_bytes(int world, int64_t n);
+int rpc_allreduce_ll(void *const *recv /*[host]*/, int rank, int world, int64_t n, const float *src, float *out,
+                     uint32_t *counter, int32_t *status, void *stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * Hand-off to the middle encoder.  coors rows are already (batch, z, y, x) int32, the order
  * spconv's SparseConvTensor takes (adversarial_voxelnet.py:140-141, adversarial_centerpoint.py:105-106), and

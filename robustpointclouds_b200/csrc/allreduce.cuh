@@ -21,6 +21,7 @@ namespace rpc {
 
 constexpr int kArCtas = 64;                       // at most; one float4 per thread at the named sizes
 constexpr int kArThreads = 256;
+constexpr int kArLLCtas = 136;                    // low-latency variant: one element per thread at the named sizes
 constexpr int kArMaxWorld = 16;
 
 struct ArParams {
@@ -85,6 +86,79 @@ k_allreduce_oneshot(const __grid_constant__ ArParams p)
         const long long i = (n4 << 2) + tid;
         float s = 0.0f;
         for (int r = 0; r < p.world; ++r) s = __fadd_rn(s, __ldcv(p.stage[buf][r] + i));
+        p.out[i] = s;
+    }
+    // 3. completion
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t t = atomicAdd(p.ctr + 1, 1u);
+        if (t == gridDim.x - 1) {
+            p.ctr[1] = 0u;
+            __threadfence();
+            *reinterpret_cast<volatile uint32_t *>(p.ctr) = e;
+        }
+    }
+}
+
+// ---- low-latency variant: data and flag travel in the same 8-byte store -------------------------------------------
+// k_allreduce_oneshot above needs three dependent trips over NVLink per call (release flag stores, acquire flag
+// loads, then the remote data loads): ~16 us per step at 2-8 GPUs.  Here every rank PUSHES: element i of rank r goes
+// as one 8-byte word {bits(value), call number e} straight into slot [r][i] of every peer's receive area (and of its
+// own), an aligned 8-byte store cannot tear, so a receiver that polls its LOCAL slot until the call number matches
+// has the value -- no fence, no flag round trip, one one-way NVLink latency in total.  Sums are taken in rank order
+// (bit-identical on every rank).  Receive areas are double-buffered by the parity of e, for the same reason as above:
+// a rank can only start call e + 2 after every peer has sent for call e + 1, i.e. has finished polling call e.
+struct ArLLParams {
+    uint2 *recv[2][kArMaxWorld];         // [buffer][destination rank]: that rank's receive area, [world][npad] words
+    const float *src;
+    float *out;                          // may alias src
+    uint32_t *ctr;                       // local: [0] completed calls, [1] CTA ticket
+    int *status;                         // local: set to 1 on timeout
+    long long n, npad;
+    int rank, world;
+};
+
+__global__ void __launch_bounds__(kArThreads)
+k_allreduce_ll(const __grid_constant__ ArLLParams p)
+{
+    __shared__ uint32_t s_e;
+    const int tid = threadIdx.x;
+    if (tid == 0) s_e = *reinterpret_cast<volatile uint32_t *>(p.ctr) + 1u;
+    __syncthreads();
+    const uint32_t e = s_e;
+    const int buf = (int)(e & 1u);
+    const long long stride = (long long)gridDim.x * kArThreads;
+    const long long i0 = (long long)blockIdx.x * kArThreads + tid;
+    // 1. push my values to everybody (peers first, my own area last)
+    for (long long i = i0; i < p.n; i += stride) {
+        const uint32_t bits = __float_as_uint(__ldg(p.src + i));
+#pragma unroll
+        for (int k = 1; k <= kArMaxWorld; ++k) {
+            if (k <= p.world) {
+                const int r = (p.rank + k) % p.world;
+                uint2 *dst = p.recv[buf][r] + (long long)p.rank * p.npad + i;
+                asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(dst), "r"(bits), "r"(e) : "memory");
+            }
+        }
+    }
+    // 2. poll my own area, add in rank order
+    const uint2 *mine = p.recv[buf][p.rank];
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    for (long long i = i0; i < p.n; i += stride) {
+        float s = 0.0f;
+        for (int r = 0; r < p.world; ++r) {
+            const uint2 *w = mine + (long long)r * p.npad + i;
+            uint32_t v, f;
+            for (;;) {
+                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(w) : "memory");
+                if (f == e) break;
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 2000000000ull) { *p.status = 1; v = 0u; break; }   // 2 s: a peer died; do not hang the GPU
+            }
+            s = __fadd_rn(s, __uint_as_float(v));
+        }
         p.out[i] = s;
     }
     // 3. completion

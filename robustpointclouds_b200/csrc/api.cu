@@ -697,6 +697,35 @@ RPC_API int rpc_allreduce_oneshot(float *const *stage0, float *const *stage1, ui
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
+RPC_API size_t rpc_allreduce_ll_bytes(int world, int64_t n)
+{
+    if (world < 1 || world > kArMaxWorld || n < 0) return 0;
+    const int64_t npad = (n + 1) / 2 * 2;                           // slots of a source rank stay 16-byte aligned
+    return (size_t)2 * world * npad * sizeof(uint2);
+}
+
+RPC_API int rpc_allreduce_ll(void *const *recv, int rank, int world, int64_t n, const float *src, float *out,
+                             uint32_t *counter, int32_t *status, void *stream)
+{
+    if (world < 1 || world > kArMaxWorld || rank < 0 || rank >= world || n < 0) return RPC_ERR_CONFIG;
+    if (n == 0) return RPC_OK;
+    if (!recv || !src || !out || !counter || !status) return RPC_ERR_NULL;
+    ArLLParams p;
+    memset(&p, 0, sizeof(p));
+    p.npad = (n + 1) / 2 * 2;
+    for (int r = 0; r < world; ++r) {
+        if (!recv[r]) return RPC_ERR_NULL;
+        if (misaligned(recv[r])) return RPC_ERR_ALIGN;
+        p.recv[0][r] = static_cast<uint2 *>(recv[r]);
+        p.recv[1][r] = static_cast<uint2 *>(recv[r]) + (int64_t)world * p.npad;
+    }
+    p.src = src; p.out = out; p.ctr = counter; p.status = status; p.n = n; p.rank = rank; p.world = world;
+    int64_t ctas = (n + kArThreads - 1) / kArThreads;
+    if (ctas > kArLLCtas) ctas = kArLLCtas;
+    k_allreduce_ll<<<(int)ctas, kArThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
 // ------------------------------------------------------------------ perturber statistics
 static int moments_launch(const float *x, int64_t K, const int32_t *k_dev, int C, double *acc, cudaStream_t st)
 {

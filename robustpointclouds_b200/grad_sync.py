@@ -23,18 +23,27 @@ class PeerAllReduce:
     symmetric, peer-mapped allocation comes from ``torch.distributed._symmetric_memory`` (plumbing); the
     exchange itself is this library's kernel.  One NCCL-free launch instead of a ~16 us NCCL all-reduce."""
 
-    def __init__(self, numel: int, device: torch.device, group: Optional[dist.ProcessGroup] = None):
+    def __init__(self, numel: int, device: torch.device, group: Optional[dist.ProcessGroup] = None,
+                 mode: str = "ll"):
+        """``mode="ll"``: push variant, value + call number in one 8-byte store (``rpc_allreduce_ll``, one one-way
+        NVLink latency); ``mode="oneshot"``: staged buffers + flags, peers read (``rpc_allreduce_oneshot``)."""
         import ctypes
 
         import torch.distributed._symmetric_memory as symm_mem
 
         from . import _lib
-        self._lib, self._ct = _lib, ctypes
+        if mode not in ("ll", "oneshot"):
+            raise ValueError(mode)
+        self._lib, self._ct, self.mode = _lib, ctypes, mode
         self.group = group if group is not None else dist.group.WORLD
         self.n = int(numel)
         self.npad = (self.n + 3) // 4 * 4
-        flag_words = _lib.lib().rpc_allreduce_flag_bytes() // 4
-        self.sym = symm_mem.empty(2 * self.npad + flag_words, dtype=torch.float32, device=device)
+        world = dist.get_world_size(self.group)
+        if mode == "ll":
+            words = _lib.lib().rpc_allreduce_ll_bytes(world, self.n) // 4
+        else:
+            words = 2 * self.npad + _lib.lib().rpc_allreduce_flag_bytes() // 4
+        self.sym = symm_mem.empty(words, dtype=torch.float32, device=device)
         self.sym.zero_()
         self.hdl = symm_mem.rendezvous(self.sym, self.group)
         self.rank, self.world = self.hdl.rank, self.hdl.world_size
@@ -42,6 +51,7 @@ class PeerAllReduce:
         dist.barrier(self.group)                                       # every rank's flags are zero from here on
         ptrs = [int(q) for q in self.hdl.buffer_ptrs]
         vp = ctypes.c_void_p
+        self._recv = (vp * self.world)(*ptrs)
         self._stage = [(vp * self.world)(*[q + 4 * self.npad * b for q in ptrs]) for b in (0, 1)]
         self._flags = (vp * self.world)(*[q + 8 * self.npad for q in ptrs])
         self.state = torch.zeros(4, dtype=torch.int32, device=device)   # [0] completed calls, [1] ticket, [2] status
@@ -53,17 +63,22 @@ class PeerAllReduce:
         out = src if out is None else out
         if src.numel() != self.n or src.dtype != torch.float32 or not src.is_contiguous():
             raise ValueError(f"expected a contiguous fp32 tensor of {self.n} values")
+        stream = torch.cuda.current_stream(self.dev).cuda_stream
+        if self.mode == "ll":
+            st = self._lib.lib().rpc_allreduce_ll(self._recv, self.rank, self.world, self.n, src.data_ptr(),
+                                                 out.data_ptr(), self.state.data_ptr(), self.state.data_ptr() + 8, stream)
+            self._lib.check(st, "rpc_allreduce_ll")
+            return out
         st = self._lib.lib().rpc_allreduce_oneshot(self._stage[0], self._stage[1], self._flags, self.rank, self.world,
                                                   self.n, src.data_ptr(), out.data_ptr(), self.state.data_ptr(),
-                                                  self.state.data_ptr() + 8,
-                                                  torch.cuda.current_stream(self.dev).cuda_stream)
+                                                  self.state.data_ptr() + 8, stream)
         self._lib.check(st, "rpc_allreduce_oneshot")
         return out
 
     def check(self) -> None:
         """host sync: raise if a peer timed out in any call so far"""
         if int(self.state[2].item()) != 0:
-            raise RuntimeError("rpc_allreduce_oneshot: a peer did not arrive within 2 s")
+            raise RuntimeError("peer all-reduce: a peer did not arrive within 2 s")
 
 
 class FlatGradSync:

@@ -214,3 +214,15 @@ def test_strength_schedule_host_logic():
     ep._attack_history = [0.05] * 51
     assert ep.update_adversarial_strength() == 5.0                       # 2.0 * 2.0 * 1.5 capped at max_scaling
     assert ep.update_adversarial_strength() == orc.adversarial_strength(10, 5000, [0.05] * 51)
+
+
+def test_allreduce_ll_entries_without_gpu():
+    L = _lib.lib()
+    assert L.rpc_allreduce_ll_bytes(8, 34641) == 2 * 8 * 34642 * 8      # two parities x world x padded n x 8-byte words
+    assert L.rpc_allreduce_ll_bytes(17, 8) == 0 and L.rpc_allreduce_ll_bytes(0, 8) == 0
+    vp = ctypes.c_void_p
+    one = (vp * 1)(None)
+    assert L.rpc_allreduce_ll(one, 0, 17, 8, None, None, None, None, None) == -2      # world > 16
+    assert L.rpc_allreduce_ll(one, 2, 2, 8, None, None, None, None, None) == -2       # rank >= world
+    assert L.rpc_allreduce_ll(one, 0, 1, 8, None, None, None, None, None) == -1       # NULL pointers
+    assert L.rpc_allreduce_ll(one, 0, 1, 0, None, None, None, None, None) == 0        # nothing to do

@@ -6,8 +6,9 @@ from robustpointclouds_b200 import PeerAllReduce
 rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local); dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
-n = 34641
-par = PeerAllReduce(n, dev)
+n = int(os.environ.get("AR_N", 34641))
+mode = os.environ.get("AR_MODE", "ll")
+par = PeerAllReduce(n, dev, mode=mode)
 ok = True
 for it in range(20):
     x = torch.randn(n, device=dev, generator=torch.Generator(dev).manual_seed(100 * it + rank))
@@ -42,5 +43,5 @@ ref = x.clone(); dist.all_reduce(ref); torch.cuda.synchronize()
 ok &= bool(torch.allclose(y, ref, rtol=1e-5, atol=1e-5))
 par.check()
 if rank == 0:
-    print(f"world {dist.get_world_size()} n {n}: parity {'OK' if ok else 'FAIL'}  nccl {t_nccl:.1f} us  peer one-shot {t_peer:.1f} us (eager), {t_graph:.1f} us (graph replay)")
+    print(f"world {dist.get_world_size()} n {n}: parity {'OK' if ok else 'FAIL'}  nccl {t_nccl:.1f} us  peer {mode} {t_peer:.1f} us (eager), {t_graph:.1f} us (graph replay)")
 dist.barrier(); dist.destroy_process_group()
