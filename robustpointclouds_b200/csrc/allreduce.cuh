@@ -146,19 +146,27 @@ k_allreduce_ll(const __grid_constant__ ArLLParams p)
     unsigned long long t0;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
     for (long long i = i0; i < p.n; i += stride) {
-        float s = 0.0f;
-        for (int r = 0; r < p.world; ++r) {
-            const uint2 *w = mine + (long long)r * p.npad + i;
-            uint32_t v, f;
-            for (;;) {
-                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(f) : "l"(w) : "memory");
-                if (f == e) break;
-                unsigned long long t1;
-                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-                if (t1 - t0 > 2000000000ull) { *p.status = 1; v = 0u; break; }   // 2 s: a peer died; do not hang the GPU
+        uint32_t v[kArMaxWorld];
+        for (;;) {                                                  // all sources polled together: one L2 round trip
+            bool all = true;
+#pragma unroll
+            for (int r = 0; r < kArMaxWorld; ++r) {
+                if (r < p.world) {
+                    uint32_t f;
+                    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];"
+                                 : "=r"(v[r]), "=r"(f) : "l"(mine + (long long)r * p.npad + i) : "memory");
+                    all &= f == e;
+                }
             }
-            s = __fadd_rn(s, __uint_as_float(v));
+            if (all) break;
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 2000000000ull) { *p.status = 1; break; }   // 2 s: a peer died; do not hang the GPU
         }
+        float s = 0.0f;
+#pragma unroll
+        for (int r = 0; r < kArMaxWorld; ++r)
+            if (r < p.world) s = __fadd_rn(s, __uint_as_float(v[r]));
         p.out[i] = s;
     }
     // 3. completion
