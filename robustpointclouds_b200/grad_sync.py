@@ -18,8 +18,8 @@ def shard_batch(num_sweeps: int, rank: int, world_size: int) -> List[int]:
 
 
 class PeerAllReduce:
-    """One-shot sum all-reduce of a small fp32 buffer over NVLink peer memory (``rpc_allreduce_oneshot``,
-    csrc/allreduce.cuh): every rank reads all peers' buffers directly and adds them in rank order.  The
+    """Sum all-reduce of a small fp32 buffer over NVLink peer memory in ONE launch (``rpc_allreduce_ll`` /
+    ``rpc_allreduce_oneshot``, csrc/allreduce.cuh), sums taken in rank order (bit-identical on every rank).  The
     symmetric, peer-mapped allocation comes from ``torch.distributed._symmetric_memory`` (plumbing); the
     exchange itself is this library's kernel.  One NCCL-free launch instead of a ~16 us NCCL all-reduce."""
 
