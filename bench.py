@@ -272,6 +272,8 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    from robustpointclouds_b200.hostmem import bind_to_gpu_numa
+    numa_cpus = None if args.no_numa else bind_to_gpu_numa(local)      # pinned host buffers on the GPU's own NUMA node
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -515,7 +517,8 @@ def run_b200(args):
             "e2e": {"value": round(total_pts / (e2e_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                     "ms_per_step": round(e2e_ms / e2e_steps, 5),
-                    "how": "StepPipeline: pinned host in/out, H2D | kernels | D2H on three streams, depth 2"},
+                    "how": "StepPipeline: pinned host in/out, H2D | kernels | D2H on three streams, depth 2" +
+                           ("; process bound to the %d CPUs local to the GPU" % len(numa_cpus) if numa_cpus else "")},
             "gpu_launches": launches_per_step * args.steps,
             "roofline": roof,
         }
@@ -538,6 +541,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="sweeps per GPU (default: 6 KITTI, 4 nuScenes)")
     ap.add_argument("--points", type=int, default=0, help="points per sweep (default: the preset's; BASELINE.json configs[4] sweep)")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-numa", action="store_true", help="do not bind the process to the GPU's local CPUs")
     ap.add_argument("--allreduce", default="ll", choices=["ll", "p2p", "nccl"],
                     help="N > 1: perturber-gradient all-reduce through this library's one-shot NVLink kernel or NCCL")
     ap.add_argument("--flush", default="write", choices=["write", "write+read"],
