@@ -263,6 +263,15 @@ int rpc_perturb_losses_bwd(const float *p, const float *consts, const float *gra
                            const int32_t *k_dev, int C, float *grad_p, void *stream);
 
 /* ---------------------------------------------------------------------------------------------------
+ * Pre-path pipeline op: mmdet3d PointsRangeFilter (configs/_base_/kitti-3d-car.py:62-64 of the
+ * reference) = points[BasePoints.in_range_3d(range)], the OPEN box lo < p < hi on x, y, z (NaN dropped), order kept.
+ * out_points [N, C] (first count[0] rows written; may be NULL), out_index [N] = source row of every kept point,
+ * count[0] on the device; workspace of rpc_valid_rows_workspace_bytes(N, 1).  range6 is a HOST array.
+ * ------------------------------------------------------------------------------------------------- */
+int rpc_points_range_filter(const float *points, int64_t N, int C, const float *range6 /*[host]*/, float *out_points,
+                            int32_t *out_index, int32_t *count, void *workspace, size_t workspace_bytes, void *stream);
+
+/* ---------------------------------------------------------------------------------------------------
  * Post-VFE perturbation variant: the elementwise part of
  * StrongAdversarialVoxelNet.apply_enhanced_perturbations (models/detectors/strong_adversarial_voxelnet.py:156-180)
  * on n = M * C features: sp = (y - x) * scaling [+ alpha * last] (last may be NULL: no momentum yet; y_is_delta != 0:

@@ -388,3 +388,13 @@ def enhanced_perturbation_bwd(g_out: np.ndarray, g_l2: float, sp: np.ndarray, sc
     gy = scaling * gsp
     gx = g_out.astype(np.float64) if y_is_delta else g_out.astype(np.float64) - gy
     return gx, gy
+
+
+def points_range_filter(points: np.ndarray, pcr) -> np.ndarray:
+    """mmdet3d PointsRangeFilter = points[BasePoints.in_range_3d(pcr)]: the open box on x, y, z
+    (pipeline of /root/reference/configs/_base_/kitti-3d-car.py:62-64)"""
+    p = _f32(points)
+    lo, hi = np.asarray(pcr[:3], np.float32), np.asarray(pcr[3:], np.float32)
+    with np.errstate(invalid="ignore"):
+        m = (p[:, 0] > lo[0]) & (p[:, 1] > lo[1]) & (p[:, 2] > lo[2]) & (p[:, 0] < hi[0]) & (p[:, 1] < hi[1]) & (p[:, 2] < hi[2])
+    return p[m]

@@ -569,15 +569,10 @@ RPC_API size_t rpc_valid_rows_workspace_bytes(int64_t M, int P)
     return align_up(4 * (size_t)((M * P + kRowTile - 1) / kRowTile + 1));
 }
 
-RPC_API int rpc_valid_rows(const float *voxels, const int32_t *num_points, int64_t M, int P, int C, int mode,
-                           const int32_t *m_dev, int32_t *row_idx, int32_t *row2k, float *rows_out,
-                           int32_t *count, void *workspace, size_t workspace_bytes, void *stream)
+static int launch_valid_rows(const float *voxels, const int32_t *num_points, int64_t M, int P, int C, int mode,
+                             const int32_t *m_dev, int32_t *row_idx, int32_t *row2k, float *rows_out, int32_t *count,
+                             void *workspace, size_t workspace_bytes, const RangeDesc &rd, cudaStream_t st)
 {
-    if (P < 1 || C < 1 || M < 0 || (mode != 0 && mode != 1)) return RPC_ERR_CONFIG;
-    if (!count) return RPC_ERR_NULL;
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (M == 0) return cudaMemsetAsync(count, 0, 4, st) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
-    if (!voxels || !num_points || !row_idx || !workspace) return RPC_ERR_NULL;
     const int64_t R = M * P;
     if (R > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
     int ntiles = (int)((R + kRowTile - 1) / kRowTile);
@@ -595,10 +590,41 @@ RPC_API int rpc_valid_rows(const float *voxels, const int32_t *num_points, int64
     }
     int grid = device_sms();
     if (grid > ntiles) grid = ntiles;
-    void *args[] = {&voxels, &num_points, &M, &m_dev, &P, &C, &mode, &ntiles, &tile_cnt, &row_idx, &row2k, &rows_out, &count};
+    RangeDesc rdc = rd;
+    void *args[] = {&voxels, &num_points, &M, &m_dev, &P, &C, &mode, &ntiles, &tile_cnt, &row_idx, &row2k, &rows_out, &count, &rdc};
     if (cudaLaunchCooperativeKernel((void *)k_valid_rows, dim3(grid), dim3(kRowTile), args, smem, st) != cudaSuccess)
         return RPC_ERR_CUDA;
     return RPC_OK;
+}
+
+RPC_API int rpc_valid_rows(const float *voxels, const int32_t *num_points, int64_t M, int P, int C, int mode,
+                           const int32_t *m_dev, int32_t *row_idx, int32_t *row2k, float *rows_out,
+                           int32_t *count, void *workspace, size_t workspace_bytes, void *stream)
+{
+    if (P < 1 || C < 1 || M < 0 || (mode != 0 && mode != 1)) return RPC_ERR_CONFIG;
+    if (!count) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (M == 0) return cudaMemsetAsync(count, 0, 4, st) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    if (!voxels || !num_points || !row_idx || !workspace) return RPC_ERR_NULL;
+    RangeDesc rd;
+    memset(&rd, 0, sizeof(rd));
+    return launch_valid_rows(voxels, num_points, M, P, C, mode, m_dev, row_idx, row2k, rows_out, count, workspace,
+                             workspace_bytes, rd, st);
+}
+
+RPC_API int rpc_points_range_filter(const float *points, int64_t N, int C, const float *range6, float *out_points,
+                                    int32_t *out_index, int32_t *count, void *workspace, size_t workspace_bytes,
+                                    void *stream)
+{
+    if (C < 3 || N < 0) return RPC_ERR_CONFIG;
+    if (!count || !range6) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (N == 0) return cudaMemsetAsync(count, 0, 4, st) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    if (!points || !out_index || !workspace) return RPC_ERR_NULL;
+    RangeDesc rd;
+    for (int d = 0; d < 3; ++d) { rd.lo[d] = range6[d]; rd.hi[d] = range6[3 + d]; }
+    return launch_valid_rows(points, nullptr, N, 1, C, 2, nullptr, out_index, nullptr, out_points, count, workspace,
+                             workspace_bytes, rd, st);
 }
 
 static inline int stream_blocks(int64_t total)

@@ -16,12 +16,18 @@ namespace rpc {
 
 constexpr int kRowTile = 1024;                  // rows per tile of the compaction
 
+struct RangeDesc { float lo[3], hi[3]; };       // mode 2: open box, mmdet3d BasePoints.in_range_3d
+
 // row r of the [M*P, C] view is valid?  rowsum: fp32 sum left to right != 0 (torch sum over 4-5 floats)
 __device__ __forceinline__ bool row_valid(const float *__restrict__ vox, const int *__restrict__ num,
-                                          int64_t r, int P, int C, int mode)
+                                          int64_t r, int P, int C, int mode, const RangeDesc &rd)
 {
     if (mode == 1) return (int)(r % P) < __ldg(num + r / P);
     const float *x = vox + r * C;
+    if (mode == 2) {                                            // NaN compares false: dropped, like the ATen mask
+        const float a = __ldg(x), b = __ldg(x + 1), c = __ldg(x + 2);
+        return a > rd.lo[0] && b > rd.lo[1] && c > rd.lo[2] && a < rd.hi[0] && b < rd.hi[1] && c < rd.hi[2];
+    }
     float s = __ldg(x);
     for (int c = 1; c < C; ++c) s = __fadd_rn(s, __ldg(x + c));
     return s != 0.0f;
@@ -33,7 +39,8 @@ __device__ __forceinline__ bool row_valid(const float *__restrict__ vox, const i
 __global__ void __launch_bounds__(kRowTile)
 k_valid_rows(const float *__restrict__ vox, const int *__restrict__ num, int64_t M, const int *__restrict__ m_dev,
              int P, int C, int mode, int ntiles, int *__restrict__ tile_cnt, int *__restrict__ row_idx,
-             int *__restrict__ row2k, float *__restrict__ rows_out, int *__restrict__ count)
+             int *__restrict__ row2k, float *__restrict__ rows_out, int *__restrict__ count,
+             const __grid_constant__ RangeDesc rd)
 {
     namespace cg = cooperative_groups;
     extern __shared__ int prefix[];                               // [ntiles + 1]
@@ -43,7 +50,7 @@ k_valid_rows(const float *__restrict__ vox, const int *__restrict__ num, int64_t
     const int tid = threadIdx.x;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t r = (int64_t)tile * kRowTile + tid;
-        const bool v = r < R && row_valid(vox, num, r, P, C, mode);
+        const bool v = r < R && row_valid(vox, num, r, P, C, mode, rd);
         const int c = __syncthreads_count(v);
         if (tid == 0) tile_cnt[tile] = c;
     }
@@ -61,7 +68,7 @@ k_valid_rows(const float *__restrict__ vox, const int *__restrict__ num, int64_t
     }
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t r = (int64_t)tile * kRowTile + tid;
-        const bool v = r < R && row_valid(vox, num, r, P, C, mode);
+        const bool v = r < R && row_valid(vox, num, r, P, C, mode, rd);
         int tot;
         const int k = prefix[tile] + block_excl_scan<kRowTile>(v ? 1 : 0, sm, &tot);
         if (r < R && row2k) row2k[r] = v ? k : -1;

@@ -438,3 +438,23 @@ def momentum_apply_bwd(g_out: Optional[torch.Tensor], g_l2: Optional[torch.Tenso
                                                _ptr(gx), _ptr(gy), _stream(dev))
         _lib.check(st, "rpc_momentum_apply_bwd")
     return gx, gy
+
+
+def points_range_filter(points: torch.Tensor, point_cloud_range: Sequence[float]):
+    """mmdet3d ``PointsRangeFilter``: rows with ``lo < (x, y, z) < hi`` in their original order.  Returns
+    ``(out [N, C], index [N] int32, count [1] int32)``: the first ``count`` rows of ``out`` / ``index`` are the kept
+    points and their source rows (no host sync; slice with ``int(count)`` when a tight tensor is needed)."""
+    dev = _need_cuda(points)
+    points = _f32c(points)
+    N, C = points.shape
+    L = _lib.lib()
+    out = torch.empty_like(points)
+    index = torch.empty((N,), dtype=torch.int32, device=dev)
+    count = torch.zeros((1,), dtype=torch.int32, device=dev)
+    rng = (ctypes.c_float * 6)(*[float(v) for v in point_cloud_range])
+    nbytes = L.rpc_valid_rows_workspace_bytes(N, 1)
+    ws = _default_ws.get(nbytes, dev)
+    st = L.rpc_points_range_filter(_ptr(points), N, C, rng, _ptr(out), _ptr(index), _ptr(count), ws.data_ptr(),
+                                   ws.numel(), _stream(dev))
+    _lib.check(st, "rpc_points_range_filter")
+    return out, index, count

@@ -86,3 +86,27 @@ def test_strength_schedule_matches_oracle():
         ep._epoch, ep._iteration, ep._attack_history = epoch, it, list(hist)
         assert ep.update_adversarial_strength() == orc.adversarial_strength(epoch, it, hist)
     assert EnhancedPerturbation(None, dynamic_scaling=False).update_adversarial_strength() == 1.0
+
+
+@pytest.mark.parametrize("preset,N", [("kitti", 120000), ("nuscenes", 300001), ("kitti", 1), ("kitti", 1025)])
+def test_points_range_filter_and_shuffle(preset, N):
+    """pipeline transforms in front of the voxelizer (kitti-3d-car.py:62-64): bit-exact, order kept"""
+    from robustpointclouds_b200 import PointShuffle, PointsRangeFilter, synth
+    pcr = synth.PRESETS[preset]["point_cloud_range"]
+    pts = synth.make_cloud(preset, N, "lidar", 3)
+    pts[::97, 0] = pcr[0]                                            # exactly on the lower face: dropped (open box)
+    pts[5::101, 1] = pcr[4]                                          # exactly on the upper face: dropped
+    if N > 10:
+        pts[7, 2] = np.nan
+    ref = orc.points_range_filter(pts, pcr)
+    t = torch.from_numpy(pts).to(DEV)
+    d = PointsRangeFilter(pcr)({"points": t})
+    assert np.array_equal(d["points"].cpu().numpy(), ref, equal_nan=True)
+    out, index, count = ops.points_range_filter(t, pcr)
+    k = int(count)
+    assert k == len(ref) and np.array_equal(pts[index[:k].cpu().numpy()], ref, equal_nan=True)
+    g = torch.Generator(DEV).manual_seed(5)
+    sh = PointShuffle(g).shuffle(t)
+    perm = torch.randperm(N, device=DEV, generator=torch.Generator(DEV).manual_seed(5))
+    assert torch.equal(torch.nan_to_num(sh, nan=-1.0), torch.nan_to_num(t[perm], nan=-1.0))
+    assert ops.points_range_filter(torch.zeros((0, 4), device=DEV), pcr)[2].item() == 0

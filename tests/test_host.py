@@ -226,3 +226,12 @@ def test_allreduce_ll_entries_without_gpu():
     assert L.rpc_allreduce_ll(one, 2, 2, 8, None, None, None, None, None) == -2       # rank >= world
     assert L.rpc_allreduce_ll(one, 0, 1, 8, None, None, None, None, None) == -1       # NULL pointers
     assert L.rpc_allreduce_ll(one, 0, 1, 0, None, None, None, None, None) == 0        # nothing to do
+
+
+def test_range_filter_entry_without_gpu():
+    L = _lib.lib()
+    rng = (ctypes.c_float * 6)(0, -40, -3, 70.4, 40, 1)
+    assert L.rpc_points_range_filter(None, 10, 2, rng, None, None, None, None, 0, None) == -2      # needs x, y, z
+    assert L.rpc_points_range_filter(None, 10, 4, rng, None, None, None, None, 0, None) == -1      # NULL pointers
+    pts = np.array([[1, 0, 0, 1], [0, 0, 0, 1], [70.4, 0, 0, 1], [5, -40, 0, 1], [np.nan, 0, 0, 1], [3, 3, 0.5, 1]], np.float32)
+    assert orc.points_range_filter(pts, [0, -40, -3, 70.4, 40, 1]).tolist() == [[1, 0, 0, 1], [3, 3, 0.5, 1]]
