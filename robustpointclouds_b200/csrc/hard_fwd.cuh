@@ -230,36 +230,8 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         if (tile >= 0) tr = tile_range(p, tile);
         return tile;
     };
-    // pull this CTA's point / perturbation tiles into L2 while the table is being cleared
-    for (int it = 0; it < iters; ++it) {
-        TileRange tr;
-        const int tile = my_range(it, tr);
-        if (tile < 0) continue;
-        const size_t b0 = (size_t)tr.begin * C * 4, b1 = (size_t)tr.end * C * 4;
-        for (size_t o = (b0 & ~size_t(127)) + (size_t)(tid & (kTile - 1)) * 128; o < b1; o += (size_t)kTile * 128) {
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(p.pts) + o));
-            if constexpr (PERTURB)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(p.raw) + o));
-        }
-    }
-    {
-        uint4 *t4 = reinterpret_cast<uint4 *>(p.tab);
-        const long long n4 = p.tab_total >> 1;
-        for (long long i = (long long)blockIdx.x * kPT + tid; i < n4; i += (long long)nct * kPT)
-            t4[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
-    }
-    if (p.stamps) __syncthreads();
-    stamp(p, 8);
-    grid.sync();
-    stamp(p, 1);
-
-    // ------------------------------------------------------------------------------- P1 insert
-    // coordinate loads -> cell; 32-byte bucket load -> local scan; CAS only where a slot looked empty,
-    // atomicMin only where the holder has a larger index.
-    // C == 4: every WARP runs its own two-stage TMA pipeline -- lane 0 fetches the warp's 32 rows (512 bytes
-    // per array, contiguous and 16-byte aligned) of iteration it + 1 into the other shared-memory stage and
-    // arms that stage's mbarrier with the byte count while iteration it probes the table.  Per warp, not per
-    // CTA: a CTA-wide stage (one barrier per iteration) made every warp wait for the slowest probe chain.
+    // (the staging pipeline of P1 is set up here, and the rows of iteration 0 are requested before the table is
+    // cleared: they travel while this phase and its barrier run)
     constexpr bool kTma = (C == 4);
     constexpr int kArr = PERTURB ? 2 : 1;                            // arrays staged per warp
     const int wlane = tid & 31, wid = tid >> 5;
@@ -292,6 +264,36 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         __syncwarp();
     }
+    // pull this CTA's point / perturbation tiles into L2 while the table is being cleared
+    for (int it = 0; it < iters; ++it) {
+        TileRange tr;
+        const int tile = my_range(it, tr);
+        if (tile < 0) continue;
+        const size_t b0 = (size_t)tr.begin * C * 4, b1 = (size_t)tr.end * C * 4;
+        for (size_t o = (b0 & ~size_t(127)) + (size_t)(tid & (kTile - 1)) * 128; o < b1; o += (size_t)kTile * 128) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(p.pts) + o));
+            if constexpr (PERTURB)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(p.raw) + o));
+        }
+    }
+    {
+        uint4 *t4 = reinterpret_cast<uint4 *>(p.tab);
+        const long long n4 = p.tab_total >> 1;
+        for (long long i = (long long)blockIdx.x * kPT + tid; i < n4; i += (long long)nct * kPT)
+            t4[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+    }
+    if (p.stamps) __syncthreads();
+    stamp(p, 8);
+    grid.sync();
+    stamp(p, 1);
+
+    // ------------------------------------------------------------------------------- P1 insert
+    // coordinate loads -> cell; 32-byte bucket load -> local scan; CAS only where a slot looked empty,
+    // atomicMin only where the holder has a larger index.
+    // C == 4: every WARP runs its own two-stage TMA pipeline -- lane 0 fetches the warp's 32 rows (512 bytes
+    // per array, contiguous and 16-byte aligned) of iteration it + 1 into the other shared-memory stage and
+    // arms that stage's mbarrier with the byte count while iteration it probes the table.  Per warp, not per
+    // CTA: a CTA-wide stage (one barrier per iteration) made every warp wait for the slowest probe chain.
     for (int it = 0; it < iters; ++it) {
         TileRange tr;
         const int tile = my_range(it, tr);
