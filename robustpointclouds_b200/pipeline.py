@@ -13,6 +13,7 @@ device buffers, ordered by events only (no host synchronisation until a result i
 """
 from __future__ import annotations
 
+import dataclasses
 from typing import Dict, List, Optional, Sequence
 
 import torch
@@ -22,6 +23,8 @@ from ._lib import PerturbCfg, VoxelCfg
 
 
 class StepPipeline:
+    _HOST_FIELDS = ("voxels", "coors", "voxel_coors", "num_points", "voxel_num", "feats")
+
     def __init__(self, cfg: VoxelCfg, bounds: PerturbCfg, n_per_sample: Sequence[int], device: torch.device,
                  depth: int = 2, dynamic: bool = False, use_graph: bool = True, pre_step=None):
         """``pre_step``: optional callable run on the compute stream in front of every step (bench.py's L2 flush)."""
@@ -31,20 +34,39 @@ class StepPipeline:
         N, C, F = sum(self.n), cfg.C, cfg.F
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(device) for _ in range(3))
         f32 = dict(dtype=torch.float32, device=device)
-        self.d_pts = [torch.empty((N, C), **f32) for _ in range(depth)]
-        self.d_raw = [torch.empty((N, C), **f32) for _ in range(depth)]
-        self.graw = [torch.empty((N, C), **f32) for _ in range(depth)]
+        # points and raw of a slot are the two halves of ONE device buffer, every result of a slot lives in ONE
+        # packed device buffer with the same layout as its pinned host twin: one PCIe copy per direction and step
+        # (measured on this pool: 0.50 ms for 23 MB each way as single copies, 0.56 ms split 2 + 6 ways)
+        self.d_in = [torch.empty((2, N, C), **f32) for _ in range(depth)]
+        self.d_pts = [b[0] for b in self.d_in]
+        self.d_raw = [b[1] for b in self.d_in]
         self.outs: List = []
         self.graphs: List[Optional[torch.cuda.CUDAGraph]] = [None] * depth
         self._gf: List[Optional[torch.Tensor]] = [None] * depth
+        self.d_pack: List[torch.Tensor] = []
+        self.graw: List[torch.Tensor] = []
+        self._layout: Dict[str, tuple] = {}
         with torch.cuda.stream(self.s_cmp):
             for k in range(depth):
-                self.d_pts[k].zero_(); self.d_raw[k].zero_()
-                self.outs.append(self._fwd(k, None))
+                self.d_in[k].zero_()
+                o = self._fwd(k, None)                                   # shapes of the outputs at capacity
+                named = {f.name: getattr(o, f.name) for f in dataclasses.fields(o)
+                         if isinstance(getattr(o, f.name), torch.Tensor) and f.name in self._HOST_FIELDS}
+                named["grad_raw"] = torch.empty((N, C), **f32)
+                if not self._layout:
+                    off = 0
+                    for name, t in named.items():
+                        self._layout[name] = (off, t.numel() * t.element_size(), t.dtype, tuple(t.shape))
+                        off = (off + t.numel() * t.element_size() + 255) // 256 * 256
+                    self._pack_bytes = off
+                pack = torch.empty((self._pack_bytes,), dtype=torch.uint8, device=device)
+                views = self._views(pack)
+                self.d_pack.append(pack)
+                self.graw.append(views.pop("grad_raw"))
+                self.outs.append(dataclasses.replace(o, **views))
         torch.cuda.synchronize(device)
-        self.h_out: List[Dict[str, torch.Tensor]] = [
-            {name: torch.empty_like(t, device="cpu").pin_memory() for name, t in self._device_results(k).items()}
-            for k in range(depth)]
+        self.h_pack = [torch.empty((self._pack_bytes,), dtype=torch.uint8).pin_memory() for _ in range(depth)]
+        self.h_out: List[Dict[str, torch.Tensor]] = [self._views(h) for h in self.h_pack]
         ev = lambda: [torch.cuda.Event() for _ in range(depth)]          # noqa: E731
         self.ev_in, self.ev_cmp, self.ev_out = ev(), ev(), ev()
         self.use_graph = use_graph
@@ -59,13 +81,15 @@ class StepPipeline:
                                      want_feats=True, want_maps=True, want_slots=False)
         return ops.hard_voxelize(self.d_pts[k], self.n, self.cfg, raw=self.d_raw[k], bounds=self.bounds, out=out)
 
-    def _device_results(self, k: int) -> Dict[str, torch.Tensor]:
-        o = self.outs[k]
-        if self.dynamic:
-            return dict(coors=o.coors, voxel_coors=o.voxel_coors, num_points=o.num_points, voxel_num=o.voxel_num,
-                        feats=o.feats, grad_raw=self.graw[k])
-        return dict(voxels=o.voxels, coors=o.coors, num_points=o.num_points, voxel_num=o.voxel_num, feats=o.feats,
-                    grad_raw=self.graw[k])
+    def _views(self, pack: torch.Tensor) -> Dict[str, torch.Tensor]:
+        return {name: pack[off:off + nbytes].view(dtype).view(shape)
+                for name, (off, nbytes, dtype, shape) in self._layout.items()}
+
+    def alloc_host_inputs(self):
+        """(h_points, h_raw): the two halves of one pinned [2, N, C] buffer -- ``submit`` moves such a pair with a
+        single copy"""
+        h = torch.empty(tuple(self.d_in[0].shape), dtype=torch.float32).pin_memory()
+        return h[0], h[1]
 
     def _path(self, k: int, grad_feats: torch.Tensor):
         o = self._fwd(k, self.outs[k])
@@ -90,7 +114,7 @@ class StepPipeline:
 
     @property
     def d2h_bytes(self) -> int:
-        return sum(t.numel() * t.element_size() for t in self.h_out[0].values())
+        return int(self._pack_bytes)                                 # what the one device->host copy moves
 
     def submit(self, h_points: torch.Tensor, h_raw: torch.Tensor, grad_feats: torch.Tensor) -> int:
         """Enqueue one step: ``h_points`` / ``h_raw`` pinned host [sum n, C]; ``grad_feats`` device [cap, F] (the
@@ -98,8 +122,14 @@ class StepPipeline:
         k = self.count % self.depth
         with torch.cuda.stream(self.s_in):
             self.s_in.wait_event(self.ev_cmp[k])                         # kernels that read this slot's inputs are done
-            self.d_pts[k].copy_(h_points, non_blocking=True)
-            self.d_raw[k].copy_(h_raw, non_blocking=True)
+            nb = h_points.numel() * h_points.element_size()
+            if (h_raw.data_ptr() == h_points.data_ptr() + nb and h_points.is_contiguous() and h_raw.is_contiguous()
+                    and h_points.dtype == torch.float32 and h_raw.dtype == torch.float32):
+                both = torch.as_strided(h_points, tuple(self.d_in[k].shape), self.d_in[k].stride())
+                self.d_in[k].copy_(both, non_blocking=True)              # the halves of one pinned buffer: one copy
+            else:
+                self.d_pts[k].copy_(h_points, non_blocking=True)
+                self.d_raw[k].copy_(h_raw, non_blocking=True)
             self.ev_in[k].record(self.s_in)
         with torch.cuda.stream(self.s_cmp):
             self.s_cmp.wait_event(self.ev_in[k])
@@ -110,8 +140,7 @@ class StepPipeline:
             self.ev_cmp[k].record(self.s_cmp)
         with torch.cuda.stream(self.s_out):
             self.s_out.wait_event(self.ev_cmp[k])
-            for name, t in self._device_results(k).items():
-                self.h_out[k][name].copy_(t, non_blocking=True)
+            self.h_pack[k].copy_(self.d_pack[k], non_blocking=True)
             self.ev_out[k].record(self.s_out)
         self.count += 1
         return self.count - 1

@@ -27,8 +27,14 @@ def test_pipeline_matches_direct_calls(dynamic, use_graph):
     for s in range(5):
         clouds = [synth.make_cloud("kitti", m, "lidar", 50 + 10 * s + i) for i, m in enumerate(n)]
         raws = [synth.make_raw(c, 70 + 10 * s + i) for i, c in enumerate(clouds)]
-        batches.append((torch.from_numpy(np.concatenate(clouds)).pin_memory(),
-                        torch.from_numpy(np.concatenate(raws)).pin_memory()))
+        if s % 2:                                            # the halves of one pinned buffer: moved by one copy
+            hp, hr = pipe.alloc_host_inputs()
+            hp.copy_(torch.from_numpy(np.concatenate(clouds)))
+            hr.copy_(torch.from_numpy(np.concatenate(raws)))
+            batches.append((hp, hr))
+        else:                                                # two unrelated pinned tensors: two copies
+            batches.append((torch.from_numpy(np.concatenate(clouds)).pin_memory(),
+                            torch.from_numpy(np.concatenate(raws)).pin_memory()))
     tickets, got = [], []
     for s, (hp, hr) in enumerate(batches):
         tickets.append(pipe.submit(hp, hr, gf))
