@@ -456,6 +456,10 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     h2d, d2h = pipe.h2d_bytes, pipe.d2h_bytes
+    # a peer that did not arrive within 2 s sets a status word instead of hanging the GPU: report it, do not hide it
+    ar_timeouts = (int(par.state[2].item()) + int(sync_par.state[2].item())) if par is not None else 0
+    if ar_timeouts:
+        print(f"[bench] rank {rank}: peer all-reduce saw a timeout", file=sys.stderr)
 
     # ---- per-kernel durations (CUDA events inside the library, same steps, cold L2, no graph)
     stages, phases = {}, {}
@@ -515,7 +519,7 @@ def run_b200(args):
                                                 "one-shot NVLink peer-memory all-reduce (rpc_allreduce_oneshot, in the step's graph)")
                                                if par is not None else "nccl all_reduce") +
                                               " of %d fp32 perturber grads per step" % pgrad.numel())
-                                  if world > 1 else "none"),
+                                  if world > 1 else "none", collective_timeouts=ar_timeouts),
             "clocks": clocks,
             "e2e": {"value": round(total_pts / (e2e_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
