@@ -3,26 +3,30 @@
 //
 // Replaces mmcv `hard_voxelize_forward` with a parallel formulation that gives the SAME
 // result as the serial CPU walk.  At the named sizes the path moves ~30-200 MB, i.e. 5-30 us at HBM
-// speed, so the forward is one launch of one 1024-thread CTA per SM that walks through six phases
+// speed, so the forward is one launch of two 1024-thread CTAs per SM that walk through six phases
 // separated by grid-wide barriers; all intermediate state (hash table, per-point entry, slot lists)
 // stays L2-resident between phases.  Measured on B200 the scatter/gather phases are bound by the
 // per-SM L1/LSU rate of one 128-byte line per cycle, not by HBM, so every phase is laid out to touch as
 // few distinct lines per warp instruction as possible and points are dealt to CTAs in interleaved
-// 1024-point tiles (a contiguous split leaves the in-range work on a few SMs).
+// 256-point tiles (a contiguous split leaves the in-range work on a few SMs).
 //
-//   P0 clear     64-bit hash entries := EMPTY (also makes the table L2-resident for the atomics of P1)
-//   P1 insert    per point: [perturb] -> cell id -> claim / find the cell's entry with ONE 64-bit CAS
-//                ((cell << 32) | point index); an entry already held by the cell with a larger index
-//                gets an atomicMin -> entry.lo = index of the FIRST point of the cell.  Points that
-//                saw a smaller index can never be first and are not looked at again in P2.
-//   P2 flag      candidates: first-of-cell flag (entry.lo == index); first points counted per tile
-//   P3 assign    exclusive scan over tiles in point order = mmcv's voxel index; rank >= V -> cell
-//                refused for good; entry.lo := voxel row; slot lists initialised (coalesced fill)
+//   P0 clear     tile ranges of this CTA -> shared memory; TMA request for the rows of P1's first iteration;
+//                64-bit hash entries := EMPTY (also makes the table L2-resident for the atomics of P1)
+//   P1 insert    per point: [perturb] -> cell id -> claim / find the cell's entry: two blind 64-bit CASes of
+//                ((cell << 32) | point index) along the linear probe order, then 32-byte bucket loads for whoever is
+//                still pending; an entry already held by the cell with a larger index gets an atomicMin ->
+//                entry.lo = index of the FIRST point of the cell.  Points that saw a smaller index can never be
+//                first and are not looked at again in P2.
+//   P2 flag      candidates: first-of-cell flag (entry.lo == index); first points counted per WARP, one byte each
+//   P3 assign    exclusive scan over tiles in point order = mmcv's voxel index; rank >= V -> cell refused for
+//                good; entry.lo := voxel row; slot lists initialised (coalesced fill)
 //   P4 rank      per kept cell the P smallest point indices, by an atomicMin insertion chain (level k
 //                keeps the k-th smallest; losers carry to level k+1)
-//   P5 gather    per voxel: gather the <= P points in slot order into shared memory and to the
-//                zero-padded [P,C] rows (coalesced), coors from the first point, num_points,
-//                point2voxel/slot and the mean
+//   P5 gather    per voxel (one lane each, 32 voxel rows per warp task): zero-fill the padded [P,C] rows
+//                (coalesced), then gather the <= P points in slot order over the padding; coors from the first
+//                point, num_points, point2voxel/slot and the mean
+// What bounds it is the L2's rate of scattered transactions (~7-8 per point), not HBM: DESIGN.md 4.1 and
+// tools/micro/atomics.cu.
 #pragma once
 #include <cooperative_groups.h>
 
