@@ -11,6 +11,11 @@ status of each piece) plus restatements of the Python-level glue of the referenc
                              pinned against the real class by tests/golden/perturber_*.npz
 * ``extract_feat_ref``    -- flatten / mask / perturb / scatter-back / HardSimpleVFE of
                              adversarial_voxelnet.py:81-137 and adversarial_centerpoint.py:68-102
+* ``adversarial_strength`` / ``enhanced_perturbation(_bwd)`` -- the schedule and the momentum arithmetic of
+                             /root/reference/models/detectors/strong_adversarial_voxelnet.py:114-192.  PARITY
+                             UNPINNED: the reference class needs mmdet3d to import; restated from the source lines
+* ``points_range_filter`` -- mmdet3d ``PointsRangeFilter`` (third-party, not vendored; pipeline of
+                             /root/reference/configs/_base_/kitti-3d-car.py:62-64).  PARITY UNPINNED
 
 Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import this module.
 """
