@@ -19,6 +19,7 @@ namespace {
 
 constexpr int kNumSM = 148;                       // B200
 constexpr size_t kAlign = 256;
+constexpr int kMinCtas = 16;                      // smallest grid of the persistent forward
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 int check_cfg(const rpc_voxel_cfg *cfg, bool hard)
@@ -161,8 +162,15 @@ int launch_hard_t(FwdParams &fp, size_t smem, cudaStream_t st)
         attr_done[dev] = true;
     }
     void *args[] = {&fp};
+    // one CTA per kSub tiles is all a small batch can use, and a grid barrier over few CTAs is cheaper; the
+    // per-CTA stamps are read for the full grid, so profiling keeps it
+    int grid = device_sms() * kCtasPerSM;
+    if (!fp.stamps) {
+        const int need = (fp.ntiles + kSub - 1) / kSub;
+        grid = need < kMinCtas ? (grid < kMinCtas ? grid : kMinCtas) : (need < grid ? need : grid);
+    }
     g_prof.begin(st);
-    if (cudaLaunchCooperativeKernel((void *)kern, dim3(device_sms() * kCtasPerSM), dim3(kPT), args, smem, st) != cudaSuccess)
+    if (cudaLaunchCooperativeKernel((void *)kern, dim3(grid), dim3(kPT), args, smem, st) != cudaSuccess)
         return RPC_ERR_CUDA;
     g_prof.stage("k_hard_fwd", st);
     return RPC_OK;
