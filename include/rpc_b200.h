@@ -286,6 +286,25 @@ int rpc_momentum_apply_bwd(const float *g_out, const float *g_l2, const float *s
                            float scaling,
                            int64_t n, float *grad_x, float *grad_y, void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Spatial-attention gate of VoxelPerturber (first slice of SURVEY 8f row 2):
+ *   out[k, :] = t[k, :] * a[k],  a = sigmoid(w2 . relu(W1 xn[k, :] + b1) + b2)
+ * = `raw_perturbations * self.attention(voxel_features_normalized)` (models/adversarial/voxel_perturber.py:203-205)
+ * with attention = Linear(C, mid) -> ReLU -> Linear(mid, 1) -> Sigmoid, mid = max(C / 2, 1) (:104-110).
+ * xn, t, out [K, C] f32; w1 [mid, C], b1 [mid], w2 [1, mid], b2 [1] are the nn.Linear parameter tensors as they lie;
+ * gate [K] (the a values) may be NULL.  One streaming pass instead of five ATen launches.
+ * The backward recomputes the gate (nothing of size K is saved): grad_t [K, C] = g_out * a, grad_xn [K, C] (may be
+ * NULL), and the parameter gradients, reduced in fp64 through `scratch` (rpc_attention_scratch_bytes() of device
+ * memory, zeroed by the call) into grad_w1 / grad_b1 / grad_w2 / grad_b2 (shapes of the parameters, overwritten).
+ * ------------------------------------------------------------------------------------------------- */
+size_t rpc_attention_scratch_bytes(void);
+int rpc_attention_gate_fwd(const float *xn, const float *t, const float *w1, const float *b1, const float *w2,
+                           const float *b2, int64_t K, int C, float *out, float *gate, void *stream);
+int rpc_attention_gate_bwd(const float *g_out, const float *xn, const float *t, const float *w1, const float *b1,
+                           const float *w2, const float *b2, int64_t K, int C, double *scratch, float *grad_t,
+                           float *grad_xn, float *grad_w1, float *grad_b1, float *grad_w2, float *grad_b2,
+                           void *stream);
+
 #ifdef __cplusplus
 }
 #endif

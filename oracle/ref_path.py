@@ -9,6 +9,10 @@ status of each piece) plus restatements of the Python-level glue of the referenc
                              /root/reference/models/adversarial/voxel_perturber.py:209-256, 333-359
 * ``perturber_forward``   -- ``VoxelPerturber.forward`` (voxel_perturber.py:120-321) in torch-CPU ops,
                              pinned against the real class by tests/golden/perturber_*.npz
+* ``attention_gate`` / ``attention_gate_bwd`` -- ``raw_perturbations * self.attention(xn)`` (voxel_perturber.py:104-110,
+                             203-205) and its hand-derived backward in fp64; the forward is pinned by the ``mlp_out`` /
+                             ``attn`` tensors of the real class in tests/golden/perturber_*.npz, the backward by the
+                             class's own ``pgrad_attention.*`` through the module test and by torch-CPU autograd
 * ``extract_feat_ref``    -- flatten / mask / perturb / scatter-back / HardSimpleVFE of
                              adversarial_voxelnet.py:81-137 and adversarial_centerpoint.py:68-102
 * ``adversarial_strength`` / ``enhanced_perturbation(_bwd)`` -- the schedule and the momentum arithmetic of
@@ -309,6 +313,31 @@ def perturber_forward(model, attention, x, training: bool, sensor_error_bound: f
     bias = p.mean(dim=0).abs().mean()
     imb = p.std(dim=0).std()
     return y, dict(l2_norm=l2, intensity_loss=inten, bias_loss=bias, imbalance_loss=imb), p
+
+
+def attention_gate(xn: np.ndarray, t: np.ndarray, w1, b1, w2, b2) -> Tuple[np.ndarray, np.ndarray]:
+    """(out, gate): gate = sigmoid(Linear(mid, 1)(relu(Linear(C, mid)(xn)))) [K, 1], out = t * gate
+    (/root/reference/models/adversarial/voxel_perturber.py:104-110 builds the module, :203-205 applies it)."""
+    xn, t = np.asarray(xn, np.float64), np.asarray(t, np.float64)
+    w1, b1 = np.asarray(w1, np.float64), np.asarray(b1, np.float64).reshape(-1)
+    w2, b2 = np.asarray(w2, np.float64).reshape(-1), float(np.asarray(b2).reshape(-1)[0])
+    h = np.maximum(xn @ w1.T + b1, 0.0)
+    a = 1.0 / (1.0 + np.exp(-(h @ w2 + b2)))
+    return t * a[:, None], a[:, None]
+
+
+def attention_gate_bwd(g_out: np.ndarray, xn: np.ndarray, t: np.ndarray, w1, b1, w2, b2):
+    """Backward of ``attention_gate`` by the chain rule (sigmoid' = a (1 - a); ReLU' = [h > 0]), fp64:
+    -> dict(grad_t, grad_xn, grad_w1, grad_b1, grad_w2, grad_b2) with the shapes of the nn.Linear parameters."""
+    g_out, xn, t = (np.asarray(v, np.float64) for v in (g_out, xn, t))
+    w1, b1 = np.asarray(w1, np.float64), np.asarray(b1, np.float64).reshape(-1)
+    w2v, b2 = np.asarray(w2, np.float64).reshape(-1), float(np.asarray(b2).reshape(-1)[0])
+    h = np.maximum(xn @ w1.T + b1, 0.0)
+    a = 1.0 / (1.0 + np.exp(-(h @ w2v + b2)))
+    gz = (g_out * t).sum(axis=1) * a * (1.0 - a)
+    gh = gz[:, None] * w2v[None, :] * (h > 0.0)
+    return dict(grad_t=g_out * a[:, None], grad_xn=gh @ w1, grad_w1=gh.T @ xn, grad_b1=gh.sum(axis=0),
+                grad_w2=(gz[:, None] * h).sum(axis=0).reshape(np.asarray(w2).shape), grad_b2=np.array([gz.sum()]))
 
 
 def extract_feat_ref(voxels, num_points, adversary: Optional[Callable], num_features: Optional[int] = None,

@@ -12,6 +12,7 @@
 #include "dyn_scatter.cuh"
 #include "allreduce.cuh"
 #include "perturber.cuh"
+#include "attention.cuh"
 
 using namespace rpc;
 
@@ -841,6 +842,53 @@ RPC_API int rpc_momentum_apply_bwd(const float *g_out, const float *g_l2, const 
     if (n == 0) return RPC_OK;
     if (!sp || !l2 || (!grad_x && !grad_y)) return RPC_ERR_NULL;
     k_momentum_apply_bwd<<<stream_blocks(n), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(g_out, g_l2, sp, l2, y_is_delta, scaling, n, grad_x, grad_y);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API size_t rpc_attention_scratch_bytes(void) { return sizeof(double) * kAttMaxParams; }
+
+RPC_API int rpc_attention_gate_fwd(const float *xn, const float *t, const float *w1, const float *b1, const float *w2,
+                                   const float *b2, int64_t K, int C, float *out, float *gate, void *stream)
+{
+    if (C < 1 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!xn || !t || !w1 || !b1 || !w2 || !b2 || !out) return RPC_ERR_NULL;
+    if (C == 4 && (misaligned(xn) || misaligned(t) || misaligned(out))) return RPC_ERR_ALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int64_t blocks = (K + kThreads - 1) / kThreads;
+    if (blocks > kNumSM * 8) blocks = kNumSM * 8;
+    switch (C) {
+#define RPC_CASE(CC) case CC: k_attention_gate_fwd<CC><<<(int)blocks, kThreads, 0, st>>>(xn, t, w1, b1, w2, b2, K, out, gate); break;
+        RPC_CASE(1) RPC_CASE(2) RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+#undef RPC_CASE
+        default: return RPC_ERR_CONFIG;
+    }
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_attention_gate_bwd(const float *g_out, const float *xn, const float *t, const float *w1, const float *b1,
+                                   const float *w2, const float *b2, int64_t K, int C, double *scratch, float *grad_t,
+                                   float *grad_xn, float *grad_w1, float *grad_b1, float *grad_w2, float *grad_b2,
+                                   void *stream)
+{
+    if (C < 1 || C > RPC_MAX_CHANNELS || K < 0) return RPC_ERR_CONFIG;
+    if (!scratch || !grad_w1 || !grad_b1 || !grad_w2 || !grad_b2) return RPC_ERR_NULL;
+    if (K > 0 && (!g_out || !xn || !t || !w1 || !b1 || !w2 || !b2 || !grad_t)) return RPC_ERR_NULL;
+    if (C == 4 && (misaligned(g_out) || misaligned(xn) || misaligned(t) || misaligned(grad_t) || misaligned(grad_xn)))
+        return RPC_ERR_ALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(scratch, 0, sizeof(double) * kAttMaxParams, st) != cudaSuccess) return RPC_ERR_CUDA;
+    if (K > 0) {
+        int64_t blocks = (K + kThreads - 1) / kThreads;
+        if (blocks > kNumSM * 4) blocks = kNumSM * 4;
+        switch (C) {
+#define RPC_CASE(CC) case CC: k_attention_gate_bwd<CC><<<(int)blocks, kThreads, 0, st>>>(g_out, xn, t, w1, b1, w2, b2, K, grad_t, grad_xn, scratch); break;
+            RPC_CASE(1) RPC_CASE(2) RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+#undef RPC_CASE
+            default: return RPC_ERR_CONFIG;
+        }
+    }
+    k_attention_gate_finalize<<<1, 64, 0, st>>>(scratch, C, grad_w1, grad_b1, grad_w2, grad_b2);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 

@@ -361,6 +361,45 @@ def perturb_apply_bwd(grad_p: torch.Tensor, raw: torch.Tensor, bounds: PerturbCf
     return g
 
 
+# ------------------------------------------------------------------ attention gate (first slice of SURVEY 8f row 2)
+def attention_gate_fwd(xn: torch.Tensor, t: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor, w2: torch.Tensor,
+                       b2: torch.Tensor, want_gate: bool = False):
+    """``t * sigmoid(Linear(relu(Linear(xn))))`` -- ``raw_perturbations * self.attention(xn)`` of
+    /root/reference/models/adversarial/voxel_perturber.py:203-205 in one pass.  Returns ``out`` (and the gate [K, 1])."""
+    dev = _need_cuda(xn, t, w1, b1, w2, b2)
+    xn, t = _f32c(xn), _f32c(t)
+    w1, b1, w2, b2 = _f32c(w1), _f32c(b1), _f32c(w2), _f32c(b2)
+    K, C = xn.shape
+    mid = max(C // 2, 1)
+    if t.shape != xn.shape or tuple(w1.shape) != (mid, C) or b1.numel() != mid or w2.numel() != mid or b2.numel() != 1:
+        raise ValueError("attention_gate: parameter shapes do not match Linear(C, C//2) -> Linear(C//2, 1)")
+    out = torch.empty_like(t)
+    gate = torch.empty((K, 1), dtype=torch.float32, device=dev) if want_gate else None
+    st = _lib.lib().rpc_attention_gate_fwd(_ptr(xn), _ptr(t), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), K, C, _ptr(out),
+                                           _ptr(gate), _stream(dev))
+    _lib.check(st, "rpc_attention_gate_fwd")
+    return (out, gate) if want_gate else out
+
+
+def attention_gate_bwd(g_out: torch.Tensor, xn: torch.Tensor, t: torch.Tensor, w1: torch.Tensor, b1: torch.Tensor,
+                       w2: torch.Tensor, b2: torch.Tensor, want_grad_xn: bool = False):
+    """-> (grad_t, grad_xn or None, grad_w1, grad_b1, grad_w2, grad_b2); the gate is recomputed, parameter gradients
+    are reduced in fp64."""
+    dev = _need_cuda(g_out, xn, t, w1, b1, w2, b2)
+    g_out, xn, t = _f32c(g_out), _f32c(xn), _f32c(t)
+    w1, b1, w2, b2 = _f32c(w1), _f32c(b1), _f32c(w2), _f32c(b2)
+    K, C = xn.shape
+    grad_t = torch.empty_like(t)
+    grad_xn = torch.empty_like(xn) if want_grad_xn else None
+    gw1, gb1, gw2, gb2 = (torch.empty_like(q) for q in (w1, b1, w2, b2))
+    scratch = torch.empty((_lib.lib().rpc_attention_scratch_bytes() // 8,), dtype=torch.float64, device=dev)
+    st = _lib.lib().rpc_attention_gate_bwd(_ptr(g_out), _ptr(xn), _ptr(t), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), K, C,
+                                           _ptr(scratch), _ptr(grad_t), _ptr(grad_xn), _ptr(gw1), _ptr(gb1), _ptr(gw2),
+                                           _ptr(gb2), _stream(dev))
+    _lib.check(st, "rpc_attention_gate_bwd")
+    return grad_t, grad_xn, gw1, gb1, gw2, gb2
+
+
 # ------------------------------------------------------------------ perturber statistics (SURVEY 8f row 1)
 def normalize_fwd(x: torch.Tensor) -> torch.Tensor:
     """``clamp(x / (std(x, 0) + 1e-6), -10, 10)`` with the NaN / Inf scale guard, no host sync

@@ -1,8 +1,9 @@
 """``VoxelPerturber`` with the reference's API (/root/reference/models/adversarial/voxel_perturber.py:20-541)
 on top of the sm_100a kernels.
 
-What stays in PyTorch: the small MLP / attention (cuBLAS GEMMs).  What runs in the
-hand-written kernels: the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
+What stays in PyTorch: the MLP trunk (cuBLAS GEMMs + BatchNorm).  What runs in the
+hand-written kernels: the attention gate ``raw * sigmoid(Linear(relu(Linear(xn))))`` and its backward
+(``rpc_attention_gate_fwd/bwd``; ``fused_attention=False`` keeps the ATen modules), the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
 scalars and their gradient (``rpc_perturb_losses_fwd/bwd``; ``fused_stats=False`` keeps the ATen formulas), the
 elementwise tail ``p = nan_to_num(clamp(raw * eb,
 -fb, +fb)); y = x + p`` and its autograd (``rpc_perturb_apply_fwd/bwd``), and -- in the fused north-star
@@ -94,6 +95,24 @@ class _PerturbLosses(torch.autograd.Function):
         return ops.perturb_losses_bwd(p, consts, grad_losses.contiguous())
 
 
+class _AttentionGate(torch.autograd.Function):
+    """raw * attention(xn) of voxel_perturber.py:203-205 (attention = Linear -> ReLU -> Linear -> Sigmoid, :104-110) as
+    one kernel each way (``rpc_attention_gate_fwd/bwd``); the gate is recomputed in the backward, not saved."""
+
+    @staticmethod
+    def forward(ctx, xn, t, w1, b1, w2, b2):
+        out = ops.attention_gate_fwd(xn, t, w1, b1, w2, b2)
+        ctx.save_for_backward(xn, t, w1, b1, w2, b2)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        xn, t, w1, b1, w2, b2 = ctx.saved_tensors
+        grad_t, grad_xn, gw1, gb1, gw2, gb2 = ops.attention_gate_bwd(g_out.contiguous(), xn, t, w1, b1, w2, b2,
+                                                                     want_grad_xn=ctx.needs_input_grad[0])
+        return grad_xn, grad_t, gw1, gb1, gw2, gb2
+
+
 def _gradient_hook(grad):
     if grad is None:
         return grad
@@ -104,7 +123,7 @@ def _gradient_hook(grad):
 class VoxelPerturber(nn.Module):
     def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
                  use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
-                 nan_guards=True, fused_stats: bool = True):
+                 nan_guards=True, fused_stats: bool = True, fused_attention: bool = True):
         super().__init__()
         voxel_size = list(voxel_size)
         self.sensor_error_bound = sensor_error_bound
@@ -128,6 +147,7 @@ class VoxelPerturber(nn.Module):
         self.guard_tripped = None
         self._pending_metrics: List[torch.Tensor] = []
         self.fused_stats = fused_stats        # std-normalise and the four losses through the sm_100a kernels
+        self.fused_attention = fused_attention    # the attention gate through rpc_attention_gate_fwd/bwd
         self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
 
     # ------------------------------------------------------------------ construction
@@ -243,7 +263,11 @@ class VoxelPerturber(nn.Module):
             self._reset_problematic_weights()
             return None
         if self.use_spatial_attention:
-            raw = raw * self.attention(xn)
+            if self.fused_attention and raw.is_cuda and raw.shape[1] <= 8:
+                l1, l2 = self.attention[0], self.attention[2]
+                raw = _AttentionGate.apply(xn, raw, l1.weight, l1.bias, l2.weight, l2.bias)
+            else:
+                raw = raw * self.attention(xn)
         if self.nan_guards == "device":
             self.guard_tripped = self.guard_tripped | torch.isnan(raw).any()
         return raw

@@ -1,0 +1,98 @@
+"""GPU parity of the fused attention gate (first slice of SURVEY 8f row 2) through the C-ABI:
+``raw_perturbations * self.attention(xn)`` of /root/reference/models/adversarial/voxel_perturber.py:104-110, 203-205.
+Checked against the tensors recorded from the reference's own class (``mlp_out``, ``attn``, ``pgrad_attention.*`` in
+tests/golden/perturber_*.npz) and against the fp64 oracle restatement; tolerance 1e-5 relative."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_path as orc
+from robustpointclouds_b200 import VoxelPerturber, ops
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+RTOL = 1e-5
+
+
+def _close(a, b, rtol=RTOL):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    scale = max(float(np.abs(b).max()) if b.size else 0.0, 1e-30)
+    np.testing.assert_allclose(a, b.reshape(a.shape), rtol=rtol, atol=rtol * scale)
+
+
+def _dev(*arrs):
+    return [torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(DEV) for a in arrs]
+
+
+@pytest.mark.parametrize("name", ["kitti_train", "kitti_eval", "nus_train"])
+def test_gate_matches_reference_class_fixture(golden_dir, name):
+    g = np.load(os.path.join(golden_dir, f"perturber_{name}.npz"))
+    x = torch.from_numpy(g["x"]).to(DEV)
+    xn = ops.normalize_fwd(x)
+    w = _dev(*[g[f"state_attention.{k}"] for k in ("0.weight", "0.bias", "2.weight", "2.bias")])
+    (t,) = _dev(g["mlp_out"])
+    out, gate = ops.attention_gate_fwd(xn, t, *w, want_gate=True)
+    _close(gate.cpu().numpy(), g["attn"])
+    _close(out.cpu().numpy(), g["mlp_out"] * g["attn"])
+
+
+@pytest.mark.parametrize("K,C", [(1, 4), (31, 1), (257, 2), (1000, 3), (4099, 4), (70001, 5), (513, 6), (300, 7), (2049, 8)])
+def test_gate_fwd_bwd_vs_oracle(K, C):
+    rng = np.random.default_rng(100 * C + K % 97)
+    mid = max(C // 2, 1)
+    xn, t, go = (rng.standard_normal((K, C)).astype(np.float32) for _ in range(3))
+    xn[0] = 0.0                                                  # a row that sits on the ReLU kink when b1 is 0
+    w1, b1 = rng.standard_normal((mid, C)).astype(np.float32), rng.standard_normal(mid).astype(np.float32)
+    w2, b2 = rng.standard_normal((1, mid)).astype(np.float32), rng.standard_normal(1).astype(np.float32)
+    b1[0] = 0.0
+    d = _dev(xn, t, w1, b1, w2, b2)
+    out, gate = ops.attention_gate_fwd(*d, want_gate=True)
+    ro, rg = orc.attention_gate(xn, t, w1, b1, w2, b2)
+    _close(gate.cpu().numpy(), rg)
+    _close(out.cpu().numpy(), ro)
+    (dgo,) = _dev(go)
+    grad_t, grad_xn, gw1, gb1, gw2, gb2 = ops.attention_gate_bwd(dgo, *d, want_grad_xn=True)
+    r = orc.attention_gate_bwd(go, xn, t, w1, b1, w2, b2)
+    _close(grad_t.cpu().numpy(), r["grad_t"])
+    _close(grad_xn.cpu().numpy(), r["grad_xn"])
+    # sums over K rows of fp32 products: the error of the per-thread fp32 partial sums, relative to the sum of magnitudes
+    for got, key in ((gw1, "grad_w1"), (gb1, "grad_b1"), (gw2, "grad_w2"), (gb2, "grad_b2")):
+        _close(got.cpu().numpy(), r[key], rtol=1e-4)
+    assert ops.attention_gate_bwd(dgo, *d)[1] is None             # grad_xn only on request
+
+
+def test_gate_empty_and_errors():
+    C, mid = 4, 2
+    z = torch.zeros((0, C), device=DEV)
+    w = [torch.zeros((mid, C), device=DEV), torch.zeros(mid, device=DEV), torch.zeros((1, mid), device=DEV), torch.zeros(1, device=DEV)]
+    assert ops.attention_gate_fwd(z, z, *w).shape == (0, C)
+    gt, gx, gw1, gb1, gw2, gb2 = ops.attention_gate_bwd(z, z, z, *w)
+    assert gt.shape == (0, C) and float(gw1.abs().sum() + gb1.abs().sum() + gw2.abs().sum() + gb2.abs().sum()) == 0.0
+    with pytest.raises(ValueError):
+        ops.attention_gate_fwd(torch.zeros((3, C), device=DEV), torch.zeros((3, C), device=DEV), w[0][:1], *w[1:])
+    with pytest.raises(RuntimeError):
+        ops.attention_gate_fwd(torch.zeros((3, C)), torch.zeros((3, C)), *[q.cpu() for q in w])
+
+
+def test_module_fused_attention_equals_aten_modules(golden_dir):
+    """VoxelPerturber(fused_attention=True) against the same module running nn.Sequential attention"""
+    g = np.load(os.path.join(golden_dir, "perturber_kitti_train.npz"))
+    state = {k[len("state_"):]: torch.from_numpy(v) for k, v in g.items() if k.startswith("state_")}
+    x = torch.from_numpy(g["x"]).to(DEV)
+    w = torch.from_numpy(g["w"]).to(DEV)
+    res = []
+    for fused in (True, False):
+        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_attention=fused).build(4)
+        adv.load_state_dict(state)
+        adv = adv.to(DEV).train()
+        y, ld = adv(x)
+        ((y * w).sum() + ld["l2_norm"] + 3 * ld["bias_loss"]).backward()
+        res.append((y.detach().cpu().numpy(), {k: q.grad.cpu().numpy() for k, q in adv.named_parameters()}))
+    _close(res[0][0], res[1][0])
+    for k in res[0][1]:
+        np.testing.assert_allclose(res[0][1][k], res[1][1][k], rtol=1e-3, atol=2e-5, err_msg=k)
+    # and the attention gradients against the reference class's own (both clamped to +-0.1 by the hook)
+    for k in ("attention.0.weight", "attention.0.bias", "attention.2.weight", "attention.2.bias"):
+        assert np.abs(res[0][1][k]).max() <= 0.1 + 1e-7

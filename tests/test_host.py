@@ -235,3 +235,15 @@ def test_range_filter_entry_without_gpu():
     assert L.rpc_points_range_filter(None, 10, 4, rng, None, None, None, None, 0, None) == -1      # NULL pointers
     pts = np.array([[1, 0, 0, 1], [0, 0, 0, 1], [70.4, 0, 0, 1], [5, -40, 0, 1], [np.nan, 0, 0, 1], [3, 3, 0.5, 1]], np.float32)
     assert orc.points_range_filter(pts, [0, -40, -3, 70.4, 40, 1]).tolist() == [[1, 0, 0, 1], [3, 3, 0.5, 1]]
+
+
+def test_attention_gate_entries_without_gpu():
+    L = _lib.lib()
+    assert L.rpc_attention_scratch_bytes() == 8 * (4 * (8 + 2) + 1)               # W1, b1, w2, b2 at C = 8, fp64
+    assert L.rpc_attention_gate_fwd(None, None, None, None, None, None, 10, 0, None, None, None) == -2     # C out of range
+    assert L.rpc_attention_gate_fwd(None, None, None, None, None, None, 10, 9, None, None, None) == -2
+    assert L.rpc_attention_gate_fwd(None, None, None, None, None, None, 10, 4, None, None, None) == -1     # NULL pointers
+    assert L.rpc_attention_gate_fwd(None, None, None, None, None, None, 0, 4, None, None, None) == 0       # nothing to do
+    args = [None] * 7
+    assert L.rpc_attention_gate_bwd(*args, 10, 0, *([None] * 8)) == -2
+    assert L.rpc_attention_gate_bwd(*args, 10, 4, *([None] * 8)) == -1

@@ -238,3 +238,38 @@ def test_step_fused_composition():
     k = p2v >= 0
     gp[k] = gslots[p2v[k], p2s[k]]
     assert np.array_equal(buf.grad_raw, orc.perturb_bwd(gp, raw, eb, fb))
+
+
+def _xn_of(x: np.ndarray) -> np.ndarray:
+    import torch
+    xt = torch.from_numpy(x)
+    return torch.clamp(xt / (torch.std(xt, dim=0, keepdim=True) + 1e-6), -10.0, 10.0).numpy()
+
+
+@pytest.mark.parametrize("name", ["kitti_train", "kitti_eval", "nus_train"])
+def test_attention_gate_restatement_vs_reference_class(golden_dir, name):
+    """oracle attention_gate against the gate and the MLP output recorded from the reference's own class"""
+    g = np.load(os.path.join(golden_dir, f"perturber_{name}.npz"))
+    xn = _xn_of(g["x"])
+    w = [g[f"state_attention.{k}"] for k in ("0.weight", "0.bias", "2.weight", "2.bias")]
+    out, gate = orc.attention_gate(xn, g["mlp_out"], *w)
+    np.testing.assert_allclose(gate, g["attn"], rtol=1e-5, atol=1e-7)
+    # p = clamp(raw * eb, +-fb): the fixture's p pins the gated product through the tail
+    eb, fb = orc.perturber_bounds(int(g["C"]), bool(g["training"]))
+    p = np.clip(out * eb[None, :], -fb[None, :], fb[None, :])
+    np.testing.assert_allclose(p, g["p"], rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("C", [1, 3, 4, 5, 8])
+def test_attention_gate_bwd_restatement_vs_autograd(C):
+    import torch
+    rng = np.random.default_rng(C)
+    K, mid = 257, max(C // 2, 1)
+    xn, t, go = (rng.standard_normal((K, C)) for _ in range(3))
+    w1, b1, w2, b2 = rng.standard_normal((mid, C)), rng.standard_normal(mid), rng.standard_normal((1, mid)), rng.standard_normal(1)
+    tt = [torch.tensor(v, dtype=torch.float64, requires_grad=True) for v in (xn, t, w1, b1, w2, b2)]
+    a = torch.sigmoid(torch.relu(tt[0] @ tt[2].T + tt[3]) @ tt[4].T + tt[5])
+    (tt[1] * a * torch.tensor(go)).sum().backward()
+    r = orc.attention_gate_bwd(go, xn, t, w1, b1, w2, b2)
+    for key, q in zip(("grad_xn", "grad_t", "grad_w1", "grad_b1", "grad_w2", "grad_b2"), tt):
+        np.testing.assert_allclose(r[key], q.grad.numpy(), rtol=1e-10, atol=1e-12)
