@@ -24,10 +24,21 @@ from ._lib import PerturbCfg, VoxelCfg
 
 class StepPipeline:
     _HOST_FIELDS = ("voxels", "coors", "voxel_coors", "num_points", "voxel_num", "feats")
+    LEAN_FIELDS = ("coors", "voxel_coors", "num_points", "voxel_num", "feats")      # everything but the padded voxels
 
     def __init__(self, cfg: VoxelCfg, bounds: PerturbCfg, n_per_sample: Sequence[int], device: torch.device,
-                 depth: int = 2, dynamic: bool = False, use_graph: bool = True, pre_step=None):
-        """``pre_step``: optional callable run on the compute stream in front of every step (bench.py's L2 flush)."""
+                 depth: int = 2, dynamic: bool = False, use_graph: bool = True, pre_step=None,
+                 host_fields: Optional[Sequence[str]] = None):
+        """``pre_step``: optional callable run on the compute stream in front of every step (bench.py's L2 flush).
+        ``host_fields``: which outputs travel back to the host (default: all of ``_HOST_FIELDS``; ``grad_raw`` always
+        does).  The zero-padded ``voxels`` tensor is 35 % (KITTI) to 70 % (nuScenes) of the device->host bytes and is
+        only an intermediate once the VFE mean is fused -- what the reference hands on after HardSimpleVFE is
+        ``feats`` + ``coors`` (adversarial_voxelnet.py:135-140) -- so a caller that continues with the middle encoder
+        leaves it out: ``host_fields=StepPipeline.LEAN_FIELDS``.  Outputs left out stay device tensors in ``outs``."""
+        self.host_fields = tuple(self._HOST_FIELDS if host_fields is None else host_fields)
+        unknown = set(self.host_fields) - set(self._HOST_FIELDS)
+        if unknown:
+            raise ValueError(f"unknown host_fields {sorted(unknown)}; choose from {self._HOST_FIELDS}")
         self.cfg, self.bounds, self.n = cfg, bounds, [int(x) for x in n_per_sample]
         self.dev, self.depth, self.dynamic = device, depth, dynamic
         self.pre_step = pre_step
@@ -51,7 +62,7 @@ class StepPipeline:
                 self.d_in[k].zero_()
                 o = self._fwd(k, None)                                   # shapes of the outputs at capacity
                 named = {f.name: getattr(o, f.name) for f in dataclasses.fields(o)
-                         if isinstance(getattr(o, f.name), torch.Tensor) and f.name in self._HOST_FIELDS}
+                         if isinstance(getattr(o, f.name), torch.Tensor) and f.name in self.host_fields}
                 named["grad_raw"] = torch.empty((N, C), **f32)
                 if not self._layout:
                     off = 0

@@ -66,3 +66,30 @@ def test_pipeline_matches_direct_calls(dynamic, use_graph):
             torch.testing.assert_close(res["grad_raw"], graw.cpu(), rtol=1e-5, atol=1e-6)
         else:
             assert torch.equal(res["grad_raw"], graw.cpu())
+
+
+def test_pipeline_lean_host_fields():
+    """host_fields=LEAN_FIELDS: the padded voxels stay on the device, everything else arrives unchanged"""
+    dev = torch.device("cuda:0")
+    k = synth.KITTI
+    C, P, V = k["C"], k["max_num_points"], 3000
+    n = [6001, 4000]
+    cfg = VoxelCfg.make(k["voxel_size"], k["point_cloud_range"], P, V, C, C)
+    eb, fb = orc.perturber_bounds(C, True)
+    bounds = PerturbCfg.make(eb, fb)
+    full = StepPipeline(cfg, bounds, n, dev)
+    lean = StepPipeline(cfg, bounds, n, dev, host_fields=StepPipeline.LEAN_FIELDS)
+    assert lean.d2h_bytes < full.d2h_bytes - sum(min(x, V) for x in n) * P * C * 4 + 1024
+    gf = torch.randn((sum(min(x, V) for x in n), C), device=dev, generator=torch.Generator(dev).manual_seed(5))
+    hp, hr = full.alloc_host_inputs()
+    hp.copy_(torch.from_numpy(np.concatenate([synth.make_cloud("kitti", m, "lidar", 90 + i) for i, m in enumerate(n)])))
+    hr.copy_(torch.from_numpy(synth.make_raw(hp.numpy(), 91)))
+    a = full.result(full.submit(hp, hr, gf))
+    b = lean.result(lean.submit(hp, hr, gf))
+    assert "voxels" in a and "voxels" not in b
+    for name in b:
+        assert torch.equal(a[name], b[name]), name
+    M = int(a["voxel_num"][-1])
+    assert torch.equal(lean.outs[0].voxels[:M].cpu(), a["voxels"][:M])       # still produced, on the device
+    with pytest.raises(ValueError):
+        StepPipeline(cfg, bounds, n, dev, host_fields=("voxels", "nonsense"))
