@@ -108,6 +108,12 @@ def test_dynamic_scatter_full_size():
     assert _run(synth.make_batch("nuscenes", 4), "nuscenes", True) > 0
 
 
+@pytest.mark.parametrize("dist", ["lidar", "uniform"])
+def test_dynamic_scatter_sweep_top(dist):
+    """top of the configs[4] sweep: 2 sweeps of 2 M points"""
+    assert _run([synth.make_cloud("nuscenes", 2_000_000, dist, 60 + i) for i in range(2)], "nuscenes", True) > 0
+
+
 def test_dynamic_scatter_empty_and_all_dropped():
     dev = torch.device("cuda:0")
     cfgd = synth.NUSCENES

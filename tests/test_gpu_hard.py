@@ -111,6 +111,16 @@ def test_hard_voxelize_parity_full_size(preset, B):
     assert M > 0 and exact
 
 
+@pytest.mark.parametrize("preset", ["kitti", "nuscenes"])
+@pytest.mark.parametrize("dist", ["lidar", "uniform"])
+def test_hard_voxelize_parity_sweep_top(preset, dist):
+    """top of the BASELINE.json configs[4] sweep: 2 sweeps of 2 M points, every output against the oracle"""
+    V = synth.PRESETS[preset]["max_voxels"][0]
+    clouds = [synth.make_cloud(preset, 2_000_000, dist, 40 + i) for i in range(2)]
+    M, exact = _run_case(clouds, preset, V, True)
+    assert M > 0 and exact
+
+
 def test_edge_semantics():
     """boundaries, NaN / inf, duplicates beyond P, null returns, cap with late points joining"""
     vs, pcr = [0.05, 0.05, 0.1], [0, -40, -3, 70.4, 40, 1]
