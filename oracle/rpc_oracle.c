@@ -12,7 +12,7 @@
  *   - perturb / mask / scatter-back / VFE / backward  (a-U4): PINNED.
  *     The reference's own VoxelPerturber class is imported from /root/reference by
  *     tests/golden/make_golden.py and its outputs are committed under tests/golden/; this file is
- *     checked against them in tests/test_oracle_golden.py.
+ *     checked against them in tests/test_oracle.py.
  *   - hard / dynamic voxelization (rows a-U2, a-U3) and DynamicScatter mean: PARITY UNPINNED.
  *     The arithmetic lives in mmcv (requirements.txt:9 "mmcv>=2.0.0", un-pinned, absent from
  *     /root/reference and from this image) and mmdet3d @ 962f093736ffe55c089bc618842a8b8567318c8c
