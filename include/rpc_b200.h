@@ -305,6 +305,16 @@ int rpc_attention_gate_bwd(const float *g_out, const float *xn, const float *t, 
                            float *grad_xn, float *grad_w1, float *grad_b1, float *grad_w2, float *grad_b2,
                            void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Weight and bias gradient of one Linear layer of the perturber's MLP (second slice of SURVEY 8f row 2;
+ * models/adversarial/voxel_perturber.py:82-101 builds the layers, autograd's addmm backward is what the reference runs):
+ *   grad_w[m, n] = sum_k g[k, m] * a[k, n]   (nn.Linear weight layout [out = M, in = N]),  grad_b[m] = sum_k g[k, m]
+ * g [K, M] = gradient of the layer's output, a [K, N] = the layer's input, both row-major f32; M, N <= 128.
+ * grad_w [M, N] and grad_b [M] (may be NULL) are overwritten.  fp32 accumulation, split over the rows.
+ * ------------------------------------------------------------------------------------------------- */
+int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, int N, float *grad_w, float *grad_b,
+                     void *stream);
+
 #ifdef __cplusplus
 }
 #endif

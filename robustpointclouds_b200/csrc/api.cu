@@ -13,6 +13,7 @@
 #include "allreduce.cuh"
 #include "perturber.cuh"
 #include "attention.cuh"
+#include "linear.cuh"
 
 using namespace rpc;
 
@@ -889,6 +890,28 @@ RPC_API int rpc_attention_gate_bwd(const float *g_out, const float *xn, const fl
         }
     }
     k_attention_gate_finalize<<<1, 64, 0, st>>>(scratch, C, grad_w1, grad_b1, grad_w2, grad_b2);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, int N, float *grad_w, float *grad_b,
+                             void *stream)
+{
+    if (K < 0 || M < 1 || N < 1 || M > 128 || N > 128) return RPC_ERR_CONFIG;
+    if (!grad_w) return RPC_ERR_NULL;
+    if (K > 0 && (!g || !a)) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(grad_w, 0, sizeof(float) * M * N, st) != cudaSuccess) return RPC_ERR_CUDA;
+    if (grad_b && cudaMemsetAsync(grad_b, 0, sizeof(float) * M, st) != cudaSuccess) return RPC_ERR_CUDA;
+    if (K == 0) return RPC_OK;
+    // an equal chunk of rows per CTA, a multiple of the tile height; two CTAs per SM
+    int64_t ctas = 2 * (int64_t)device_sms();
+    int64_t chunk = ((K + ctas - 1) / ctas + kLinKT - 1) / kLinKT * kLinKT;
+    ctas = (K + chunk - 1) / chunk;
+    const int tm = M <= 16 ? 16 : M <= 64 ? 64 : 128, tn = N <= 16 ? 16 : N <= 64 ? 64 : 128;
+#define RPC_CASE(TM_, TN_) if (tm == TM_ && tn == TN_) k_linear_wgrad<TM_, TN_><<<(int)ctas, kLinThreads, 0, st>>>(g, a, K, M, N, chunk, grad_w, grad_b);
+    RPC_CASE(16, 16) RPC_CASE(16, 64) RPC_CASE(16, 128) RPC_CASE(64, 16) RPC_CASE(64, 64) RPC_CASE(64, 128)
+    RPC_CASE(128, 16) RPC_CASE(128, 64) RPC_CASE(128, 128)
+#undef RPC_CASE
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 

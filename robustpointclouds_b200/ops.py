@@ -400,6 +400,22 @@ def attention_gate_bwd(g_out: torch.Tensor, xn: torch.Tensor, t: torch.Tensor, w
     return grad_t, grad_xn, gw1, gb1, gw2, gb2
 
 
+def linear_wgrad(g: torch.Tensor, a: torch.Tensor, want_bias: bool = True):
+    """(grad_weight [M, N], grad_bias [M] or None) of ``out = a @ W.T + b`` from ``g = dL/d(out)`` [K, M] and the layer
+    input ``a`` [K, N]; M, N <= 128 (the Linear layers of /root/reference/models/adversarial/voxel_perturber.py:82-101)."""
+    dev = _need_cuda(g, a)
+    g, a = _f32c(g), _f32c(a)
+    K, M = g.shape
+    N = a.shape[1]
+    if a.shape[0] != K:
+        raise ValueError("linear_wgrad: g and a must have the same number of rows")
+    gw = torch.empty((M, N), dtype=torch.float32, device=dev)
+    gb = torch.empty((M,), dtype=torch.float32, device=dev) if want_bias else None
+    st = _lib.lib().rpc_linear_wgrad(_ptr(g), _ptr(a), K, M, N, _ptr(gw), _ptr(gb), _stream(dev))
+    _lib.check(st, "rpc_linear_wgrad")
+    return gw, gb
+
+
 # ------------------------------------------------------------------ perturber statistics (SURVEY 8f row 1)
 def normalize_fwd(x: torch.Tensor) -> torch.Tensor:
     """``clamp(x / (std(x, 0) + 1e-6), -10, 10)`` with the NaN / Inf scale guard, no host sync

@@ -3,7 +3,8 @@ on top of the sm_100a kernels.
 
 What stays in PyTorch: the MLP trunk (cuBLAS GEMMs + BatchNorm).  What runs in the
 hand-written kernels: the attention gate ``raw * sigmoid(Linear(relu(Linear(xn))))`` and its backward
-(``rpc_attention_gate_fwd/bwd``; ``fused_attention=False`` keeps the ATen modules), the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
+(``rpc_attention_gate_fwd/bwd``; ``fused_attention=False`` keeps the ATen modules), the weight / bias gradients of
+the trunk's Linear layers (``rpc_linear_wgrad``; ``fused_wgrad=False`` keeps nn.Linear), the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
 scalars and their gradient (``rpc_perturb_losses_fwd/bwd``; ``fused_stats=False`` keeps the ATen formulas), the
 elementwise tail ``p = nan_to_num(clamp(raw * eb,
 -fb, +fb)); y = x + p`` and its autograd (``rpc_perturb_apply_fwd/bwd``), and -- in the fused north-star
@@ -113,6 +114,38 @@ class _AttentionGate(torch.autograd.Function):
         return grad_xn, grad_t, gw1, gb1, gw2, gb2
 
 
+class _LinearFn(torch.autograd.Function):
+    """out = x @ W.T + b with cuBLAS; backward: grad_x with cuBLAS, grad_W and grad_b -- K-long reductions that cuBLAS
+    runs as under-filled split-K SIMT GEMMs -- through ``rpc_linear_wgrad``."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        return torch.nn.functional.linear(x, weight, bias)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, weight = ctx.saved_tensors
+        g = g.contiguous()
+        grad_x = g @ weight if ctx.needs_input_grad[0] else None
+        gw, gb = ops.linear_wgrad(g, x, want_bias=ctx.has_bias)
+        return grad_x, gw, gb
+
+
+class _WgradLinear(nn.Linear):
+    """nn.Linear (same parameters, same state-dict keys, same init) whose weight / bias gradient comes from the
+    sm_100a kernel when the layer is at most 128 wide and runs on CUDA; anything else takes nn.Linear's own path."""
+    fused = True
+
+    def forward(self, x):
+        if (self.fused and x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and self.in_features <= 128
+                and self.out_features <= 128 and torch.is_grad_enabled()
+                and (self.weight.requires_grad or x.requires_grad)):
+            return _LinearFn.apply(x, self.weight, self.bias)
+        return super().forward(x)
+
+
 def _gradient_hook(grad):
     if grad is None:
         return grad
@@ -123,7 +156,8 @@ def _gradient_hook(grad):
 class VoxelPerturber(nn.Module):
     def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
                  use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
-                 nan_guards=True, fused_stats: bool = True, fused_attention: bool = True):
+                 nan_guards=True, fused_stats: bool = True, fused_attention: bool = True,
+                 fused_wgrad: bool = True):
         super().__init__()
         voxel_size = list(voxel_size)
         self.sensor_error_bound = sensor_error_bound
@@ -148,6 +182,7 @@ class VoxelPerturber(nn.Module):
         self._pending_metrics: List[torch.Tensor] = []
         self.fused_stats = fused_stats        # std-normalise and the four losses through the sm_100a kernels
         self.fused_attention = fused_attention    # the attention gate through rpc_attention_gate_fwd/bwd
+        self.fused_wgrad = fused_wgrad            # weight / bias gradients of the MLP's Linear layers: rpc_linear_wgrad
         self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
 
     # ------------------------------------------------------------------ construction
@@ -158,8 +193,8 @@ class VoxelPerturber(nn.Module):
         dims = [num_features, h[0], h[1], h[2], h[1], h[0]]
         layers: List[nn.Module] = []
         for a, b in zip(dims[:-1], dims[1:]):
-            layers += [nn.Linear(a, b), nn.BatchNorm1d(b), nn.ReLU(inplace=True)]
-        layers += [nn.Linear(h[0], num_features), nn.Tanh()]
+            layers += [self._linear(a, b), nn.BatchNorm1d(b), nn.ReLU(inplace=True)]
+        layers += [self._linear(h[0], num_features), nn.Tanh()]
         self.model = nn.Sequential(*layers)
         if self.use_spatial_attention:
             mid = max(num_features // 2, 1)
@@ -167,6 +202,13 @@ class VoxelPerturber(nn.Module):
                                            nn.Linear(mid, 1), nn.Sigmoid())
         self._init_weights()
         self._hidden_channels = self.hidden_channels
+
+    def _linear(self, a: int, b: int) -> nn.Linear:
+        if not self.fused_wgrad:
+            return nn.Linear(a, b)
+        layer = _WgradLinear(a, b)
+        layer.fused = True
+        return layer
 
     def build(self, num_features: int, device=None) -> "VoxelPerturber":
         """Eager build with an explicit C, so that the weights exist before the optimizer / a checkpoint

@@ -96,3 +96,48 @@ def test_module_fused_attention_equals_aten_modules(golden_dir):
     # and the attention gradients against the reference class's own (both clamped to +-0.1 by the hook)
     for k in ("attention.0.weight", "attention.0.bias", "attention.2.weight", "attention.2.bias"):
         assert np.abs(res[0][1][k]).max() <= 0.1 + 1e-7
+
+
+# ------------------------------------------------------------------ rpc_linear_wgrad (second slice of SURVEY 8f row 2)
+@pytest.mark.parametrize("K,M,N", [(1, 64, 4), (15, 4, 64), (16, 64, 128), (4099, 128, 64), (70001, 64, 5), (70001, 5, 64),
+                                   (33, 8, 16), (1000, 32, 16), (131687, 128, 128), (257, 100, 77), (300000, 64, 64)])
+def test_linear_wgrad_vs_fp64(K, M, N):
+    gen = torch.Generator(DEV).manual_seed(K + M + N)
+    g = torch.randn((K, M), device=DEV, generator=gen)
+    a = torch.randn((K, N), device=DEV, generator=gen) + 0.25
+    gw, gb = ops.linear_wgrad(g, a)
+    rw, rb = g.double().T @ a.double(), g.double().sum(0)
+    # error of an fp32 sum of K products relative to the sum of magnitudes (what any split-K order is bounded by)
+    sw = float((g.double().abs().T @ a.double().abs()).max())
+    assert float((gw.double() - rw).abs().max()) <= 1e-5 * sw
+    assert float((gb.double() - rb).abs().max()) <= 1e-5 * float(g.double().abs().sum(0).max())
+    assert ops.linear_wgrad(g, a, want_bias=False)[1] is None
+
+
+def test_linear_wgrad_empty_and_errors():
+    gw, gb = ops.linear_wgrad(torch.zeros((0, 64), device=DEV), torch.zeros((0, 4), device=DEV))
+    assert gw.shape == (64, 4) and float(gw.abs().sum()) == 0.0 and float(gb.abs().sum()) == 0.0
+    with pytest.raises(Exception):
+        ops.linear_wgrad(torch.zeros((8, 129), device=DEV), torch.zeros((8, 4), device=DEV))
+    with pytest.raises(ValueError):
+        ops.linear_wgrad(torch.zeros((8, 64), device=DEV), torch.zeros((9, 4), device=DEV))
+
+
+def test_module_fused_wgrad_equals_nn_linear(golden_dir):
+    """VoxelPerturber(fused_wgrad=True) against nn.Linear's own backward, and state-dict compatibility"""
+    g = np.load(os.path.join(golden_dir, "perturber_kitti_train.npz"))
+    state = {k[len("state_"):]: torch.from_numpy(v) for k, v in g.items() if k.startswith("state_")}
+    x = torch.from_numpy(g["x"]).to(DEV)
+    w = torch.from_numpy(g["w"]).to(DEV)
+    grads = []
+    for fused in (True, False):
+        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_wgrad=fused).build(4)
+        assert set(adv.state_dict()) == set(state)
+        adv.load_state_dict(state)
+        adv = adv.to(DEV).train()
+        y, ld = adv(x)
+        ((y * w).sum() + ld["l2_norm"] + 2 * ld["intensity_loss"] + 3 * ld["bias_loss"] + 4 * ld["imbalance_loss"]).backward()
+        grads.append({k: q.grad.cpu().numpy() for k, q in adv.named_parameters()})
+    for k in grads[0]:
+        np.testing.assert_allclose(grads[0][k], grads[1][k], rtol=1e-3, atol=2e-5, err_msg=k)
+        np.testing.assert_allclose(grads[0][k], g[f"pgrad_{k}"], rtol=1e-2, atol=3e-4, err_msg=k)   # the reference class's own

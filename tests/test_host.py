@@ -247,3 +247,10 @@ def test_attention_gate_entries_without_gpu():
     args = [None] * 7
     assert L.rpc_attention_gate_bwd(*args, 10, 0, *([None] * 8)) == -2
     assert L.rpc_attention_gate_bwd(*args, 10, 4, *([None] * 8)) == -1
+
+
+def test_linear_wgrad_entry_without_gpu():
+    L = _lib.lib()
+    assert L.rpc_linear_wgrad(None, None, 10, 0, 4, None, None, None) == -2        # M out of range
+    assert L.rpc_linear_wgrad(None, None, 10, 64, 129, None, None, None) == -2     # N out of range
+    assert L.rpc_linear_wgrad(None, None, 10, 64, 4, None, None, None) == -1       # NULL pointers
