@@ -903,12 +903,39 @@ RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, i
     if (cudaMemsetAsync(grad_w, 0, sizeof(float) * M * N, st) != cudaSuccess) return RPC_ERR_CUDA;
     if (grad_b && cudaMemsetAsync(grad_b, 0, sizeof(float) * M, st) != cudaSuccess) return RPC_ERR_CUDA;
     if (K == 0) return RPC_OK;
-    // an equal chunk of rows per CTA, a multiple of the tile height; two CTAs per SM
-    int64_t ctas = 2 * (int64_t)device_sms();
-    int64_t chunk = ((K + ctas - 1) / ctas + kLinKT - 1) / kLinKT * kLinKT;
-    ctas = (K + chunk - 1) / chunk;
+    if (M <= 8 || N <= 8) {
+        // skinny layer: a stream over the wide operand; the wider of the two is "wide" (ties: g)
+        const bool wide_is_g = M >= N;
+        const int W = wide_is_g ? M : N, S = wide_is_g ? N : M;
+        const float *wide = wide_is_g ? g : a, *narrow = wide_is_g ? a : g;
+        if (S == 4 && misaligned(narrow)) return RPC_ERR_ALIGN;
+        const int groups = kSkinnyThreads / W;
+        int64_t blocks = (K + groups - 1) / groups;
+        if (blocks > (int64_t)device_sms() * 8) blocks = (int64_t)device_sms() * 8;
+#define RPC_CASE(S_)                                                                                                   \
+    case S_:                                                                                                           \
+        if (wide_is_g) k_linear_wgrad_skinny<S_, true><<<(int)blocks, kSkinnyThreads, 0, st>>>(wide, narrow, K, W, grad_w, grad_b);   \
+        else k_linear_wgrad_skinny<S_, false><<<(int)blocks, kSkinnyThreads, 0, st>>>(wide, narrow, K, W, grad_w, grad_b);            \
+        break;
+        switch (S) {
+            RPC_CASE(1) RPC_CASE(2) RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
+            default: return RPC_ERR_CONFIG;
+        }
+#undef RPC_CASE
+        return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    }
+    // every resident CTA slot of the device gets one equal chunk of rows (a multiple of the tile height)
     const int tm = M <= 16 ? 16 : M <= 64 ? 64 : 128, tn = N <= 16 ? 16 : N <= 64 ? 64 : 128;
-#define RPC_CASE(TM_, TN_) if (tm == TM_ && tn == TN_) k_linear_wgrad<TM_, TN_><<<(int)ctas, kLinThreads, 0, st>>>(g, a, K, M, N, chunk, grad_w, grad_b);
+#define RPC_CASE(TM_, TN_)                                                                                            \
+    if (tm == TM_ && tn == TN_) {                                                                                     \
+        int per_sm = 0;                                                                                               \
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_linear_wgrad<TM_, TN_>, LinTile<TM_, TN_>::NT, 0) != \
+                cudaSuccess || per_sm < 1) { cudaGetLastError(); per_sm = 1; }                                        \
+        int64_t ctas = (int64_t)device_sms() * per_sm;                                                                \
+        const int64_t chunk = ((K + ctas - 1) / ctas + kLinKT - 1) / kLinKT * kLinKT;                                 \
+        ctas = (K + chunk - 1) / chunk;                                                                               \
+        k_linear_wgrad<TM_, TN_><<<(int)ctas, LinTile<TM_, TN_>::NT, 0, st>>>(g, a, K, M, N, chunk, grad_w, grad_b);  \
+    }
     RPC_CASE(16, 16) RPC_CASE(16, 64) RPC_CASE(16, 128) RPC_CASE(64, 16) RPC_CASE(64, 64) RPC_CASE(64, 128)
     RPC_CASE(128, 16) RPC_CASE(128, 64) RPC_CASE(128, 128)
 #undef RPC_CASE

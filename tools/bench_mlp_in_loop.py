@@ -49,7 +49,10 @@ for preset in sys.argv[1:] or ["kitti", "nuscenes"]:
     M = int(vd0["voxels"].shape[0])
     w = torch.randn((M, C), device=dev, generator=torch.Generator(dev).manual_seed(1))
     res = {}
-    for name, fused, wgrad in (("fused", True, True), ("fused, nn.Linear backward", True, False), ("aten", False, False)):
+    variants = (("fused", True, True), ("fused, nn.Linear backward", True, False), ("aten", False, False))
+    if os.environ.get("RPC_BENCH_VARIANTS"):                        # e.g. "fused" for an ncu launch list of one variant
+        variants = tuple(v for v in variants if v[0] in os.environ["RPC_BENCH_VARIANTS"].split(";"))
+    for name, fused, wgrad in variants:
         torch.manual_seed(0)
         adv = rpc.VoxelPerturber(hidden_channels=[64, 128, 64], voxel_size=d["voxel_size"], nan_guards="device",
                                  fused_stats=fused, fused_attention=fused, fused_wgrad=wgrad).build(C, dev).train()
@@ -81,4 +84,5 @@ for preset in sys.argv[1:] or ["kitti", "nuscenes"]:
         adv.flush_metrics()
         print(f"{preset} B={B} N={N} M={M} K={K} [{name}]: step {tot * 1e3:.0f} us = {N / tot / 1e3:.1f} M points/s "
               f"(voxelize {tv * 1e3:.0f} us, perturb + VFE forward {tf * 1e3:.0f} us, backward {(tot - tv - tf) * 1e3:.0f} us)")
-    print(f"{preset}: fused kernels around the MLP vs ATen formulas: {res['aten'] / res['fused']:.2f}x")
+    if "aten" in res and "fused" in res:
+        print(f"{preset}: fused kernels around the MLP vs ATen formulas: {res['aten'] / res['fused']:.2f}x")
