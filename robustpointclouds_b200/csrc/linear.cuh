@@ -156,22 +156,32 @@ k_linear_wgrad_skinny(const float *__restrict__ wide, const float *__restrict__ 
 #pragma unroll
     for (int s = 0; s < S; ++s) { acc[s] = 0.0f; nsum[s] = 0.0f; }
     if (r < groups) {
-        for (int64_t k = (int64_t)blockIdx.x * groups + r; k < K; k += (int64_t)gridDim.x * groups) {
-            const float w = __ldg(wide + k * W + j);
-            float nv[S];
-            if constexpr (S == 4) {
-                const float4 t = __ldg(reinterpret_cast<const float4 *>(narrow) + k);
-                nv[0] = t.x; nv[1] = t.y; nv[2] = t.z; nv[3] = t.w;
-            } else {
+        constexpr int U = 4;                                        // rows in flight per thread
+        const int64_t stride = (int64_t)gridDim.x * groups;
+        for (int64_t k0 = (int64_t)blockIdx.x * groups + r; k0 < K; k0 += U * stride) {
+            float w[U], nv[U][S];
 #pragma unroll
-                for (int s = 0; s < S; ++s) nv[s] = __ldg(narrow + k * S + s);
+            for (int u = 0; u < U; ++u) {
+                const int64_t k = k0 + u * stride;
+                const bool ok = k < K;
+                w[u] = ok ? __ldg(wide + k * W + j) : 0.0f;
+                if constexpr (S == 4) {
+                    const float4 t = ok ? __ldg(reinterpret_cast<const float4 *>(narrow) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    nv[u][0] = t.x; nv[u][1] = t.y; nv[u][2] = t.z; nv[u][3] = t.w;
+                } else {
+#pragma unroll
+                    for (int s = 0; s < S; ++s) nv[u][s] = ok ? __ldg(narrow + k * S + s) : 0.0f;
+                }
             }
 #pragma unroll
-            for (int s = 0; s < S; ++s) acc[s] = fmaf(w, nv[s], acc[s]);
-            if constexpr (WIDE_IS_G) colsum += w;
-            else if (j == 0) {
+            for (int u = 0; u < U; ++u) {
 #pragma unroll
-                for (int s = 0; s < S; ++s) nsum[s] += nv[s];
+                for (int s = 0; s < S; ++s) acc[s] = fmaf(w[u], nv[u][s], acc[s]);
+                if constexpr (WIDE_IS_G) colsum += w[u];
+                else if (j == 0) {
+#pragma unroll
+                    for (int s = 0; s < S; ++s) nsum[s] += nv[u][s];
+                }
             }
         }
     }
