@@ -13,6 +13,8 @@ status of each piece) plus restatements of the Python-level glue of the referenc
                              203-205) and its hand-derived backward in fp64; the forward is pinned by the ``mlp_out`` /
                              ``attn`` tensors of the real class in tests/golden/perturber_*.npz, the backward by the
                              class's own ``pgrad_attention.*`` through the module test and by torch-CPU autograd
+* ``linear_wgrad``        -- autograd's weight / bias gradient of the MLP's nn.Linear layers (voxel_perturber.py:82-101)
+                             in fp64; pinned end to end by the class's own ``pgrad_model.*`` fixtures
 * ``extract_feat_ref``    -- flatten / mask / perturb / scatter-back / HardSimpleVFE of
                              adversarial_voxelnet.py:81-137 and adversarial_centerpoint.py:68-102
 * ``adversarial_strength`` / ``enhanced_perturbation(_bwd)`` -- the schedule and the momentum arithmetic of
@@ -338,6 +340,14 @@ def attention_gate_bwd(g_out: np.ndarray, xn: np.ndarray, t: np.ndarray, w1, b1,
     gh = gz[:, None] * w2v[None, :] * (h > 0.0)
     return dict(grad_t=g_out * a[:, None], grad_xn=gh @ w1, grad_w1=gh.T @ xn, grad_b1=gh.sum(axis=0),
                 grad_w2=(gz[:, None] * h).sum(axis=0).reshape(np.asarray(w2).shape), grad_b2=np.array([gz.sum()]))
+
+
+def linear_wgrad(g: np.ndarray, a: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """(grad_weight [M, N], grad_bias [M]) of ``out = a @ W.T + b`` given ``g = dL/d(out)`` [K, M] and the layer input
+    ``a`` [K, N] -- what autograd computes for the nn.Linear layers of
+    /root/reference/models/adversarial/voxel_perturber.py:82-101 -- in fp64."""
+    g, a = np.asarray(g, np.float64), np.asarray(a, np.float64)
+    return g.T @ a, g.sum(axis=0)
 
 
 def extract_feat_ref(voxels, num_points, adversary: Optional[Callable], num_features: Optional[int] = None,

@@ -122,6 +122,13 @@ class _LinearFn(torch.autograd.Function):
     def forward(ctx, x, weight, bias):
         ctx.save_for_backward(x, weight)
         ctx.has_bias = bias is not None
+        # Large batches: addmm on a contiguous W^T, not F.linear -- for [K, 64] x [64, 128] + bias F.linear goes through
+        # a cuBLASLt path with an extra full pass over the output (829 against 365 us at K = 835 k, 135 against 73 us
+        # at K = 131 k, measured on B200).  Below ~32 M output elements the step is bound by the host's launch rate
+        # and the extra transpose launch costs more than the kernel saves (KITTI forward 1.25 -> 1.31 ms).
+        if x.shape[0] * weight.shape[0] >= (1 << 25):
+            wt = weight.t().contiguous()
+            return torch.addmm(bias, x, wt) if bias is not None else torch.mm(x, wt)
         return torch.nn.functional.linear(x, weight, bias)
 
     @staticmethod

@@ -114,6 +114,16 @@ def test_linear_wgrad_vs_fp64(K, M, N):
     assert ops.linear_wgrad(g, a, want_bias=False)[1] is None
 
 
+@pytest.mark.parametrize("K,M,N", [(777, 64, 4), (777, 5, 64), (2050, 64, 128)])
+def test_linear_wgrad_vs_oracle(K, M, N):
+    rng = np.random.default_rng(K + M)
+    g, a = rng.standard_normal((K, M)).astype(np.float32), rng.standard_normal((K, N)).astype(np.float32)
+    gw, gb = ops.linear_wgrad(*_dev(g, a))
+    rw, rb = orc.linear_wgrad(g, a)
+    _close(gw.cpu().numpy(), rw)
+    _close(gb.cpu().numpy(), rb)
+
+
 def test_linear_wgrad_empty_and_errors():
     gw, gb = ops.linear_wgrad(torch.zeros((0, 64), device=DEV), torch.zeros((0, 4), device=DEV))
     assert gw.shape == (64, 4) and float(gw.abs().sum()) == 0.0 and float(gb.abs().sum()) == 0.0

@@ -273,3 +273,15 @@ def test_attention_gate_bwd_restatement_vs_autograd(C):
     r = orc.attention_gate_bwd(go, xn, t, w1, b1, w2, b2)
     for key, q in zip(("grad_xn", "grad_t", "grad_w1", "grad_b1", "grad_w2", "grad_b2"), tt):
         np.testing.assert_allclose(r[key], q.grad.numpy(), rtol=1e-10, atol=1e-12)
+
+
+@pytest.mark.parametrize("M,N", [(64, 4), (4, 64), (16, 32)])
+def test_linear_wgrad_restatement_vs_autograd(M, N):
+    rng = np.random.default_rng(M * N)
+    K = 301
+    x, go = rng.standard_normal((K, N)), rng.standard_normal((K, M))
+    lin = torch.nn.Linear(N, M).double()
+    lin(torch.tensor(x)).backward(torch.tensor(go))
+    gw, gb = orc.linear_wgrad(go, x)
+    np.testing.assert_allclose(gw, lin.weight.grad.numpy(), rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(gb, lin.bias.grad.numpy(), rtol=1e-10, atol=1e-12)
