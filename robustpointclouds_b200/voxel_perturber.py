@@ -114,6 +114,17 @@ class _AttentionGate(torch.autograd.Function):
         return grad_xn, grad_t, gw1, gb1, gw2, gb2
 
 
+def _linear_forward(x, weight, bias):
+    """x @ W.T + b.  Large batches: addmm on a contiguous W^T, not F.linear -- for [K, 64] x [64, 128] + bias F.linear
+    goes through a cuBLASLt path with an extra full pass over the output (829 against 365 us at K = 835 k, 135 against
+    73 us at K = 131 k, measured on B200).  Below ~32 M output elements the step is bound by the host's launch rate and
+    the extra transpose launch costs more than the kernel saves (KITTI forward 1.25 -> 1.31 ms)."""
+    if x.shape[0] * weight.shape[0] >= (1 << 25):
+        wt = weight.t().contiguous()
+        return torch.addmm(bias, x, wt) if bias is not None else torch.mm(x, wt)
+    return torch.nn.functional.linear(x, weight, bias)
+
+
 class _LinearFn(torch.autograd.Function):
     """out = x @ W.T + b with cuBLAS; backward: grad_x with cuBLAS, grad_W and grad_b -- K-long reductions that cuBLAS
     runs as under-filled split-K SIMT GEMMs -- through ``rpc_linear_wgrad``."""
@@ -122,14 +133,7 @@ class _LinearFn(torch.autograd.Function):
     def forward(ctx, x, weight, bias):
         ctx.save_for_backward(x, weight)
         ctx.has_bias = bias is not None
-        # Large batches: addmm on a contiguous W^T, not F.linear -- for [K, 64] x [64, 128] + bias F.linear goes through
-        # a cuBLASLt path with an extra full pass over the output (829 against 365 us at K = 835 k, 135 against 73 us
-        # at K = 131 k, measured on B200).  Below ~32 M output elements the step is bound by the host's launch rate
-        # and the extra transpose launch costs more than the kernel saves (KITTI forward 1.25 -> 1.31 ms).
-        if x.shape[0] * weight.shape[0] >= (1 << 25):
-            wt = weight.t().contiguous()
-            return torch.addmm(bias, x, wt) if bias is not None else torch.mm(x, wt)
-        return torch.nn.functional.linear(x, weight, bias)
+        return _linear_forward(x, weight, bias)
 
     @staticmethod
     def backward(ctx, g):
@@ -147,9 +151,10 @@ class _WgradLinear(nn.Linear):
 
     def forward(self, x):
         if (self.fused and x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and self.in_features <= 128
-                and self.out_features <= 128 and torch.is_grad_enabled()
-                and (self.weight.requires_grad or x.requires_grad)):
-            return _LinearFn.apply(x, self.weight, self.bias)
+                and self.out_features <= 128):
+            if torch.is_grad_enabled() and (self.weight.requires_grad or x.requires_grad):
+                return _LinearFn.apply(x, self.weight, self.bias)
+            return _linear_forward(x, self.weight, self.bias)          # eval / no_grad: same forward call choice
         return super().forward(x)
 
 

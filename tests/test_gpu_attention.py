@@ -151,3 +151,25 @@ def test_module_fused_wgrad_equals_nn_linear(golden_dir):
     for k in grads[0]:
         np.testing.assert_allclose(grads[0][k], grads[1][k], rtol=1e-3, atol=2e-5, err_msg=k)
         np.testing.assert_allclose(grads[0][k], g[f"pgrad_{k}"], rtol=1e-2, atol=3e-4, err_msg=k)   # the reference class's own
+
+
+@pytest.mark.parametrize("train", [True, False])
+def test_module_large_batch_forward_path(train):
+    """K large enough for the addmm-on-W^T forward (>= 32 M output elements per layer): same outputs as nn.Linear"""
+    K = 600_000
+    gen = torch.Generator(DEV).manual_seed(11)
+    x = torch.randn((K, 4), device=DEV, generator=gen) * torch.tensor([20.0, 20.0, 1.0, 0.3], device=DEV)
+    ys = []
+    for fused in (True, False):
+        torch.manual_seed(3)
+        adv = VoxelPerturber(hidden_channels=[64, 128, 64], fused_wgrad=fused, nan_guards=False).build(4, DEV).train(train)
+        if train:
+            y, _ = adv(x)
+            y.sum().backward()
+            ys.append((y.detach(), adv.model[3].weight.grad.clone()))
+        else:
+            with torch.no_grad():
+                ys.append((adv(x)[0], None))
+    torch.testing.assert_close(ys[0][0], ys[1][0], rtol=1e-5, atol=1e-5)
+    if train:
+        torch.testing.assert_close(ys[0][1], ys[1][1], rtol=1e-3, atol=1e-5)
