@@ -315,6 +315,22 @@ int rpc_attention_gate_bwd(const float *g_out, const float *xn, const float *t, 
 int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, int N, float *grad_w, float *grad_b,
                      void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Training-mode BatchNorm1d + ReLU of the perturber's MLP (third slice of SURVEY 8f row 2;
+ * `nn.BatchNorm1d(h), nn.ReLU(inplace=True)` of models/adversarial/voxel_perturber.py:84-98, eps / momentum as set at :461-462):
+ *   z = relu((y - mean) * invstd * gamma + beta), mean / biased variance over the K rows of y [K, H], H <= 128;
+ *   save_mean / save_invstd [H] for the backward; running_mean / running_var [H] (may be NULL) updated like torch
+ *   (momentum, unbiased variance).  `scratch` = rpc_bn_scratch_bytes() of device memory (fp64 sums, zeroed by the call).
+ * Backward: g = dL/dz; the ReLU mask is recomputed from y; grad_y [K, H], grad_gamma / grad_beta [H] (may be NULL).
+ * ------------------------------------------------------------------------------------------------- */
+size_t rpc_bn_scratch_bytes(void);
+int rpc_bn_relu_fwd(const float *y, int64_t K, int H, const float *gamma, const float *beta, float eps, float momentum,
+                    float *running_mean, float *running_var, double *scratch, float *save_mean, float *save_invstd,
+                    float *z, void *stream);
+int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, const float *save_invstd,
+                    const float *gamma, const float *beta, int64_t K, int H, double *scratch, float *grad_y,
+                    float *grad_gamma, float *grad_beta, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,7 @@ SYMBOLS = (
     "rpc_dynamic_workspace_bytes", "rpc_dynamic_scatter_mean_fwd", "rpc_dynamic_stamps_offset", "rpc_allreduce_flag_bytes", "rpc_allreduce_oneshot", "rpc_allreduce_ll_bytes", "rpc_allreduce_ll",
     "rpc_voxel_centers", "rpc_points_range_filter", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
     "rpc_attention_scratch_bytes", "rpc_attention_gate_fwd", "rpc_attention_gate_bwd", "rpc_linear_wgrad",
+    "rpc_bn_scratch_bytes", "rpc_bn_relu_fwd", "rpc_bn_relu_bwd",
 )
 
 
@@ -125,6 +126,10 @@ def lib() -> ctypes.CDLL:
     L.rpc_attention_gate_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp]
     L.rpc_attention_gate_bwd.argtypes = [vp] * 7 + [i64, i32] + [vp] * 8
     L.rpc_linear_wgrad.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp]
+    L.rpc_bn_scratch_bytes.restype = ctypes.c_size_t
+    L.rpc_bn_scratch_bytes.argtypes = []
+    L.rpc_bn_relu_fwd.argtypes = [vp, i64, i32, vp, vp, ctypes.c_float, ctypes.c_float, vp, vp, vp, vp, vp, vp, vp]
+    L.rpc_bn_relu_bwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp]
     L.rpc_profile_enable.restype = None
     L.rpc_profile_enable.argtypes = [i32]
     L.rpc_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]

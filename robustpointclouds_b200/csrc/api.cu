@@ -14,6 +14,7 @@
 #include "perturber.cuh"
 #include "attention.cuh"
 #include "linear.cuh"
+#include "bnrelu.cuh"
 
 using namespace rpc;
 
@@ -939,6 +940,46 @@ RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, i
     RPC_CASE(16, 16) RPC_CASE(16, 64) RPC_CASE(16, 128) RPC_CASE(64, 16) RPC_CASE(64, 64) RPC_CASE(64, 128)
     RPC_CASE(128, 16) RPC_CASE(128, 64) RPC_CASE(128, 128)
 #undef RPC_CASE
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+static int bn_blocks(int64_t K, int H)
+{
+    const int groups = kBnThreads / H;
+    int64_t blocks = (K + (int64_t)groups * kBnU - 1) / ((int64_t)groups * kBnU);
+    const int64_t cap = (int64_t)device_sms() * 8;
+    return (int)(blocks < 1 ? 1 : blocks > cap ? cap : blocks);
+}
+
+RPC_API size_t rpc_bn_scratch_bytes(void) { return sizeof(double) * 2 * kBnMaxH; }
+
+RPC_API int rpc_bn_relu_fwd(const float *y, int64_t K, int H, const float *gamma, const float *beta, float eps,
+                            float momentum, float *running_mean, float *running_var, double *scratch,
+                            float *save_mean, float *save_invstd, float *z, void *stream)
+{
+    if (K < 1 || H < 1 || H > kBnMaxH) return RPC_ERR_CONFIG;
+    if (!y || !gamma || !beta || !scratch || !save_mean || !save_invstd || !z) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * H, st) != cudaSuccess) return RPC_ERR_CUDA;
+    const int blocks = bn_blocks(K, H);
+    k_bn_moments<<<blocks, kBnThreads, 0, st>>>(y, K, H, scratch);
+    k_bn_relu_fwd<<<blocks, kBnThreads, 0, st>>>(y, scratch, K, H, gamma, beta, eps, momentum, running_mean, running_var,
+                                                 save_mean, save_invstd, z);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, const float *save_invstd,
+                            const float *gamma, const float *beta, int64_t K, int H, double *scratch, float *grad_y,
+                            float *grad_gamma, float *grad_beta, void *stream)
+{
+    if (K < 1 || H < 1 || H > kBnMaxH) return RPC_ERR_CONFIG;
+    if (!g || !y || !save_mean || !save_invstd || !gamma || !beta || !scratch || !grad_y) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * H, st) != cudaSuccess) return RPC_ERR_CUDA;
+    const int blocks = bn_blocks(K, H);
+    k_bn_relu_bwd_reduce<<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
+    k_bn_relu_bwd_elemt<<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H, grad_y,
+                                                       grad_gamma, grad_beta);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 

@@ -416,6 +416,41 @@ def linear_wgrad(g: torch.Tensor, a: torch.Tensor, want_bias: bool = True):
     return gw, gb
 
 
+def bn_relu_fwd(y: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, momentum: float,
+                running_mean: Optional[torch.Tensor] = None, running_var: Optional[torch.Tensor] = None):
+    """Training-mode ``relu(batch_norm(y))`` for y [K, H], H <= 128 (nn.BatchNorm1d -> nn.ReLU of
+    /root/reference/models/adversarial/voxel_perturber.py:84-98); running statistics updated in place.
+    Returns (z, save_mean, save_invstd)."""
+    dev = _need_cuda(y, gamma, beta, running_mean, running_var)
+    y = _f32c(y)
+    K, H = y.shape
+    z = torch.empty_like(y)
+    mean = torch.empty((H,), dtype=torch.float32, device=dev)
+    invstd = torch.empty((H,), dtype=torch.float32, device=dev)
+    scratch = torch.empty((_lib.lib().rpc_bn_scratch_bytes() // 8,), dtype=torch.float64, device=dev)
+    st = _lib.lib().rpc_bn_relu_fwd(_ptr(y), K, H, _ptr(_f32c(gamma)), _ptr(_f32c(beta)), float(eps), float(momentum),
+                                    _ptr(running_mean), _ptr(running_var), _ptr(scratch), _ptr(mean), _ptr(invstd),
+                                    _ptr(z), _stream(dev))
+    _lib.check(st, "rpc_bn_relu_fwd")
+    return z, mean, invstd
+
+
+def bn_relu_bwd(g: torch.Tensor, y: torch.Tensor, mean: torch.Tensor, invstd: torch.Tensor, gamma: torch.Tensor,
+                beta: torch.Tensor):
+    """-> (grad_y, grad_gamma, grad_beta) of ``bn_relu_fwd``; the ReLU mask is recomputed from y."""
+    dev = _need_cuda(g, y, mean, invstd, gamma, beta)
+    g, y = _f32c(g), _f32c(y)
+    K, H = y.shape
+    gy = torch.empty_like(y)
+    gg = torch.empty((H,), dtype=torch.float32, device=dev)
+    gb = torch.empty((H,), dtype=torch.float32, device=dev)
+    scratch = torch.empty((_lib.lib().rpc_bn_scratch_bytes() // 8,), dtype=torch.float64, device=dev)
+    st = _lib.lib().rpc_bn_relu_bwd(_ptr(g), _ptr(y), _ptr(mean), _ptr(invstd), _ptr(_f32c(gamma)), _ptr(_f32c(beta)), K, H,
+                                    _ptr(scratch), _ptr(gy), _ptr(gg), _ptr(gb), _stream(dev))
+    _lib.check(st, "rpc_bn_relu_bwd")
+    return gy, gg, gb
+
+
 # ------------------------------------------------------------------ perturber statistics (SURVEY 8f row 1)
 def normalize_fwd(x: torch.Tensor) -> torch.Tensor:
     """``clamp(x / (std(x, 0) + 1e-6), -10, 10)`` with the NaN / Inf scale guard, no host sync

@@ -4,7 +4,8 @@ on top of the sm_100a kernels.
 What stays in PyTorch: the MLP trunk (cuBLAS GEMMs + BatchNorm).  What runs in the
 hand-written kernels: the attention gate ``raw * sigmoid(Linear(relu(Linear(xn))))`` and its backward
 (``rpc_attention_gate_fwd/bwd``; ``fused_attention=False`` keeps the ATen modules), the weight / bias gradients of
-the trunk's Linear layers (``rpc_linear_wgrad``; ``fused_wgrad=False`` keeps nn.Linear), the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
+the trunk's Linear layers (``rpc_linear_wgrad``; ``fused_wgrad=False`` keeps nn.Linear), its training-mode
+BatchNorm1d + ReLU pairs (``rpc_bn_relu_fwd/bwd``; ``fused_bn=False`` keeps the ATen modules), the std-normalise + clamp in front of the MLP (``rpc_normalize_fwd``), the four loss
 scalars and their gradient (``rpc_perturb_losses_fwd/bwd``; ``fused_stats=False`` keeps the ATen formulas), the
 elementwise tail ``p = nan_to_num(clamp(raw * eb,
 -fb, +fb)); y = x + p`` and its autograd (``rpc_perturb_apply_fwd/bwd``), and -- in the fused north-star
@@ -158,6 +159,55 @@ class _WgradLinear(nn.Linear):
         return super().forward(x)
 
 
+class _BnReluFn(torch.autograd.Function):
+    """relu(batch_norm(y)) in training mode through ``rpc_bn_relu_fwd/bwd``: two passes each way, the ReLU mask
+    recomputed from y in the backward; running statistics updated in place like nn.BatchNorm1d."""
+
+    @staticmethod
+    def forward(ctx, y, gamma, beta, running_mean, running_var, eps, momentum):
+        z, mean, invstd = ops.bn_relu_fwd(y, gamma, beta, eps, momentum, running_mean, running_var)
+        ctx.save_for_backward(y, mean, invstd, gamma, beta)
+        return z
+
+    @staticmethod
+    def backward(ctx, g):
+        y, mean, invstd, gamma, beta = ctx.saved_tensors
+        gy, gg, gb = ops.bn_relu_bwd(g.contiguous(), y, mean, invstd, gamma, beta)
+        return gy, gg, gb, None, None, None, None
+
+
+class _FusedBnRelu(nn.BatchNorm1d):
+    """nn.BatchNorm1d (same parameters, buffers and state-dict keys) that, in training mode on CUDA, also applies the
+    ReLU that follows it in the Sequential; ``relu_applied`` tells that ReLU module (``_ReluAfter``) to pass through.
+    Eval mode, CPU tensors and anything else take nn.BatchNorm1d's own path."""
+    fused = True
+    relu_applied = False
+
+    def forward(self, x):
+        if (self.fused and self.training and x.is_cuda and x.dim() == 2 and x.dtype == torch.float32
+                and 2 <= x.shape[0] and x.shape[1] <= 128 and self.affine and self.track_running_stats
+                and self.momentum is not None):
+            self.num_batches_tracked.add_(1)
+            self.relu_applied = True
+            return _BnReluFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.eps,
+                                   self.momentum)
+        self.relu_applied = False
+        return super().forward(x)
+
+
+class _ReluAfter(nn.ReLU):
+    def __init__(self, bn: _FusedBnRelu):
+        super().__init__(inplace=True)
+        self._bn_ref = [bn]                                  # a list: not registered as a sub-module (state-dict keys)
+
+    def forward(self, x):
+        bn = self._bn_ref[0]
+        if bn.relu_applied:
+            bn.relu_applied = False
+            return x
+        return super().forward(x)
+
+
 def _gradient_hook(grad):
     if grad is None:
         return grad
@@ -169,7 +219,7 @@ class VoxelPerturber(nn.Module):
     def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
                  use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
                  nan_guards=True, fused_stats: bool = True, fused_attention: bool = True,
-                 fused_wgrad: bool = True):
+                 fused_wgrad: bool = True, fused_bn: bool = True):
         super().__init__()
         voxel_size = list(voxel_size)
         self.sensor_error_bound = sensor_error_bound
@@ -195,6 +245,7 @@ class VoxelPerturber(nn.Module):
         self.fused_stats = fused_stats        # std-normalise and the four losses through the sm_100a kernels
         self.fused_attention = fused_attention    # the attention gate through rpc_attention_gate_fwd/bwd
         self.fused_wgrad = fused_wgrad            # weight / bias gradients of the MLP's Linear layers: rpc_linear_wgrad
+        self.fused_bn = fused_bn                  # training-mode BatchNorm1d + ReLU of the MLP: rpc_bn_relu_fwd/bwd
         self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
 
     # ------------------------------------------------------------------ construction
@@ -205,7 +256,11 @@ class VoxelPerturber(nn.Module):
         dims = [num_features, h[0], h[1], h[2], h[1], h[0]]
         layers: List[nn.Module] = []
         for a, b in zip(dims[:-1], dims[1:]):
-            layers += [self._linear(a, b), nn.BatchNorm1d(b), nn.ReLU(inplace=True)]
+            if self.fused_bn:
+                bn = _FusedBnRelu(b)
+                layers += [self._linear(a, b), bn, _ReluAfter(bn)]
+            else:
+                layers += [self._linear(a, b), nn.BatchNorm1d(b), nn.ReLU(inplace=True)]
         layers += [self._linear(h[0], num_features), nn.Tanh()]
         self.model = nn.Sequential(*layers)
         if self.use_spatial_attention:

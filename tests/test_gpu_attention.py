@@ -173,3 +173,61 @@ def test_module_large_batch_forward_path(train):
     torch.testing.assert_close(ys[0][0], ys[1][0], rtol=1e-5, atol=1e-5)
     if train:
         torch.testing.assert_close(ys[0][1], ys[1][1], rtol=1e-3, atol=1e-5)
+
+
+# ------------------------------------------------------------------ rpc_bn_relu_fwd/bwd (third slice of SURVEY 8f row 2)
+@pytest.mark.parametrize("K,H", [(2, 64), (257, 8), (4099, 64), (70001, 128), (1000, 100), (300000, 64)])
+def test_bn_relu_vs_fp64(K, H):
+    gen = torch.Generator(DEV).manual_seed(K + H)
+    y = torch.randn((K, H), device=DEV, generator=gen) * 3 + 1.5
+    gamma = torch.randn(H, device=DEV, generator=gen)
+    beta = torch.randn(H, device=DEV, generator=gen) * 0.5
+    go = torch.randn((K, H), device=DEV, generator=gen)
+    rm, rv = torch.zeros(H, device=DEV), torch.ones(H, device=DEV)
+    z, mean, invstd = ops.bn_relu_fwd(y, gamma, beta, 1e-3, 0.1, rm, rv)
+    y64 = y.double().requires_grad_(True)
+    g64, b64 = gamma.double().requires_grad_(True), beta.double().requires_grad_(True)
+    rm64, rv64 = torch.zeros(H, device=DEV, dtype=torch.float64), torch.ones(H, device=DEV, dtype=torch.float64)
+    ref = torch.relu(torch.nn.functional.batch_norm(y64, rm64, rv64, g64, b64, True, 0.1, 1e-3))
+    torch.testing.assert_close(z.double(), ref, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(rm.double(), rm64, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(rv.double(), rv64, rtol=1e-5, atol=1e-6)
+    # backward where the fp32 and fp64 ReLU masks agree (elements within rounding of the kink may differ)
+    mask = ((ref > 1e-4) | (z == 0) & (ref == 0)).all()
+    ref.backward(go.double())
+    gy, gg, gb = ops.bn_relu_bwd(go, y, mean, invstd, gamma, beta)
+    scale = float(y64.grad.abs().max())
+    frac_bad = float(((gy.double() - y64.grad).abs() > 1e-4 * scale).double().mean())
+    assert frac_bad < 1e-3, frac_bad                             # rows at the kink only
+    if bool(mask):
+        torch.testing.assert_close(gg.double(), g64.grad, rtol=1e-4, atol=1e-4 * float(g64.grad.abs().max()))
+        torch.testing.assert_close(gb.double(), b64.grad, rtol=1e-4, atol=1e-4 * float(b64.grad.abs().max()))
+
+
+def test_module_fused_bn_equals_aten(golden_dir):
+    """VoxelPerturber(fused_bn=True) against nn.BatchNorm1d + nn.ReLU: outputs, parameter gradients, running statistics,
+    state-dict keys; eval mode goes through nn.BatchNorm1d itself"""
+    g = np.load(os.path.join(golden_dir, "perturber_kitti_train.npz"))
+    state = {k[len("state_"):]: torch.from_numpy(v) for k, v in g.items() if k.startswith("state_")}
+    x = torch.from_numpy(g["x"]).to(DEV)
+    w = torch.from_numpy(g["w"]).to(DEV)
+    res = []
+    for fused in (True, False):
+        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_bn=fused).build(4)
+        assert set(adv.state_dict()) == set(state)
+        adv.load_state_dict(state)
+        adv = adv.to(DEV).train()
+        y, ld = adv(x)
+        ((y * w).sum() + ld["l2_norm"] + 2 * ld["intensity_loss"] + 3 * ld["bias_loss"] + 4 * ld["imbalance_loss"]).backward()
+        adv.eval()
+        with torch.no_grad():
+            ye = adv(x)[0]
+        res.append((y.detach(), {k: q.grad.clone() for k, q in adv.named_parameters()},
+                    {k: v.clone() for k, v in adv.state_dict().items() if "running" in k or "tracked" in k}, ye))
+    torch.testing.assert_close(res[0][0], res[1][0], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(res[0][3], res[1][3], rtol=1e-5, atol=1e-6)
+    for k in res[0][1]:
+        np.testing.assert_allclose(res[0][1][k].cpu().numpy(), res[1][1][k].cpu().numpy(), rtol=1e-3, atol=2e-5, err_msg=k)
+        np.testing.assert_allclose(res[0][1][k].cpu().numpy(), g[f"pgrad_{k}"], rtol=1e-2, atol=3e-4, err_msg=k)
+    for k in res[0][2]:
+        torch.testing.assert_close(res[0][2][k].double(), res[1][2][k].double(), rtol=1e-5, atol=1e-6, msg=k)

@@ -254,3 +254,12 @@ def test_linear_wgrad_entry_without_gpu():
     assert L.rpc_linear_wgrad(None, None, 10, 0, 4, None, None, None) == -2        # M out of range
     assert L.rpc_linear_wgrad(None, None, 10, 64, 129, None, None, None) == -2     # N out of range
     assert L.rpc_linear_wgrad(None, None, 10, 64, 4, None, None, None) == -1       # NULL pointers
+
+
+def test_bn_relu_entries_without_gpu():
+    L = _lib.lib()
+    assert L.rpc_bn_scratch_bytes() == 8 * 2 * 128
+    assert L.rpc_bn_relu_fwd(None, 10, 0, None, None, 1e-3, 0.1, None, None, None, None, None, None, None) == -2
+    assert L.rpc_bn_relu_fwd(None, 10, 129, None, None, 1e-3, 0.1, None, None, None, None, None, None, None) == -2
+    assert L.rpc_bn_relu_fwd(None, 10, 64, None, None, 1e-3, 0.1, None, None, None, None, None, None, None) == -1
+    assert L.rpc_bn_relu_bwd(None, None, None, None, None, None, 10, 64, None, None, None, None, None) == -1

@@ -49,13 +49,14 @@ for preset in sys.argv[1:] or ["kitti", "nuscenes"]:
     M = int(vd0["voxels"].shape[0])
     w = torch.randn((M, C), device=dev, generator=torch.Generator(dev).manual_seed(1))
     res = {}
-    variants = (("fused", True, True), ("fused, nn.Linear backward", True, False), ("aten", False, False))
+    variants = (("fused", True, True, True), ("fused, ATen BatchNorm + ReLU", True, True, False),
+                ("fused, nn.Linear backward, ATen BatchNorm + ReLU", True, False, False), ("aten", False, False, False))
     if os.environ.get("RPC_BENCH_VARIANTS"):                        # e.g. "fused" for an ncu launch list of one variant
         variants = tuple(v for v in variants if v[0] in os.environ["RPC_BENCH_VARIANTS"].split(";"))
-    for name, fused, wgrad in variants:
+    for name, fused, wgrad, bn in variants:
         torch.manual_seed(0)
         adv = rpc.VoxelPerturber(hidden_channels=[64, 128, 64], voxel_size=d["voxel_size"], nan_guards="device",
-                                 fused_stats=fused, fused_attention=fused, fused_wgrad=wgrad).build(C, dev).train()
+                                 fused_stats=fused, fused_attention=fused, fused_wgrad=wgrad, fused_bn=bn).build(C, dev).train()
         adv._return_loss_dict = True
         state = {}
 
