@@ -943,9 +943,13 @@ RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, i
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
-static int bn_blocks(int64_t K, int H)
+// 16-byte columns per thread pay from ~32 M elements up (K = 835 k: 3.7 -> 4.2-4.6 TB/s); below that the kernels are
+// occupancy / latency bound and the scalar mapping with its 8 CTAs per SM is faster (K = 131 k: 67 vs 91 us)
+static bool bn_vec_pays(int64_t K, int H) { return H % 4 == 0 && K * (int64_t)H >= (int64_t(1) << 25); }
+
+static int bn_blocks(int64_t K, int H, int V)
 {
-    const int groups = kBnThreads / H;
+    const int groups = kBnThreads / (H / V);
     int64_t blocks = (K + (int64_t)groups * kBnU - 1) / ((int64_t)groups * kBnU);
     const int64_t cap = (int64_t)device_sms() * 8;
     return (int)(blocks < 1 ? 1 : blocks > cap ? cap : blocks);
@@ -961,10 +965,17 @@ RPC_API int rpc_bn_relu_fwd(const float *y, int64_t K, int H, const float *gamma
     if (!y || !gamma || !beta || !scratch || !save_mean || !save_invstd || !z) return RPC_ERR_NULL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * H, st) != cudaSuccess) return RPC_ERR_CUDA;
-    const int blocks = bn_blocks(K, H);
-    k_bn_moments<<<blocks, kBnThreads, 0, st>>>(y, K, H, scratch);
-    k_bn_relu_fwd<<<blocks, kBnThreads, 0, st>>>(y, scratch, K, H, gamma, beta, eps, momentum, running_mean, running_var,
-                                                 save_mean, save_invstd, z);
+    const bool vec = bn_vec_pays(K, H) && !misaligned(y) && !misaligned(z);
+    const int blocks = bn_blocks(K, H, vec ? 4 : 1);
+    if (vec) {
+        k_bn_moments<4><<<blocks, kBnThreads, 0, st>>>(y, K, H, scratch);
+        k_bn_relu_fwd<4><<<blocks, kBnThreads, 0, st>>>(y, scratch, K, H, gamma, beta, eps, momentum, running_mean,
+                                                        running_var, save_mean, save_invstd, z);
+    } else {
+        k_bn_moments<1><<<blocks, kBnThreads, 0, st>>>(y, K, H, scratch);
+        k_bn_relu_fwd<1><<<blocks, kBnThreads, 0, st>>>(y, scratch, K, H, gamma, beta, eps, momentum, running_mean,
+                                                        running_var, save_mean, save_invstd, z);
+    }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
@@ -976,10 +987,17 @@ RPC_API int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_me
     if (!g || !y || !save_mean || !save_invstd || !gamma || !beta || !scratch || !grad_y) return RPC_ERR_NULL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * H, st) != cudaSuccess) return RPC_ERR_CUDA;
-    const int blocks = bn_blocks(K, H);
-    k_bn_relu_bwd_reduce<<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
-    k_bn_relu_bwd_elemt<<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H, grad_y,
-                                                       grad_gamma, grad_beta);
+    const bool vec = bn_vec_pays(K, H) && !misaligned(g) && !misaligned(y) && !misaligned(grad_y);
+    const int blocks = bn_blocks(K, H, vec ? 4 : 1);
+    if (vec) {
+        k_bn_relu_bwd_reduce<4><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
+        k_bn_relu_bwd_elemt<4><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H,
+                                                              grad_y, grad_gamma, grad_beta);
+    } else {
+        k_bn_relu_bwd_reduce<1><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
+        k_bn_relu_bwd_elemt<1><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H,
+                                                              grad_y, grad_gamma, grad_beta);
+    }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
