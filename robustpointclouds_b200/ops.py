@@ -65,20 +65,57 @@ class HardVoxels:
 
 
 class Workspace:
-    """Grow-only scratch buffer per device, reused across calls (stream-ordered use only)."""
+    """Grow-only scratch buffers, one per (device, stream) and purpose, reused across calls.  Two ops that
+    run on different streams never share a buffer, and a buffer that is replaced by a larger one stays
+    alive (``_retired``): a captured CUDA graph may still hold its address."""
 
-    def __init__(self) -> None:
+    def __init__(self, headroom: float = 1.0) -> None:
         self._buf = {}
+        self._retired = []
+        self.headroom = headroom
+
+    def _key(self, dev: torch.device):
+        return (dev.index if dev.index is not None else torch.cuda.current_device(),
+                torch.cuda.current_stream(dev).cuda_stream)
 
     def get(self, nbytes: int, dev: torch.device) -> torch.Tensor:
-        b = self._buf.get(dev)
+        k = self._key(dev)
+        b = self._buf.get(k)
         if b is None or b.numel() < nbytes:
-            b = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
-            self._buf[dev] = b
+            if b is not None:
+                self._retired.append(b)
+            b = torch.empty(max(int(nbytes * self.headroom) + 256, 1), dtype=torch.uint8, device=dev)
+            self._buf[k] = b
         return b
+
+    def current(self, dev: torch.device) -> torch.Tensor:
+        return self._buf[self._key(dev)]
 
 
 _default_ws = Workspace()
+# rpc_voxelize_hard keeps its hash table, rows, lists and counters all-zero BETWEEN calls (every call restores what
+# it touched), so its workspace belongs to it alone: nothing else may write there.  A fresh (torch.empty) buffer is
+# recognised by the header and zeroed once by the kernel itself.  25 % headroom: ragged batches of a training run
+# change the layout a little every step without outgrowing the buffer.
+_hard_ws = Workspace(headroom=1.25)
+
+
+def hard_workspace_bytes(cfg: VoxelCfg, n_per_sample: Sequence[int]) -> int:
+    """``rpc_workspace_bytes``: smallest workspace ``hard_voxelize`` accepts for this batch.  A caller that keeps
+    its own workspace (a captured CUDA graph must) allocates it once with ``torch.empty`` -- the kernel recognises a
+    fresh buffer and zeroes it itself -- and never lets anything else write to it."""
+    n = _lib.lib().rpc_workspace_bytes(ctypes.byref(cfg), len(n_per_sample), _lib.counts(n_per_sample))
+    if n == 0:
+        raise _lib.RpcError(-2, "rpc_workspace_bytes")
+    return int(n)
+
+
+def dynamic_workspace_bytes(cfg: VoxelCfg, n_per_sample: Sequence[int]) -> int:
+    """``rpc_dynamic_workspace_bytes``: scratch of ``dynamic_scatter_mean`` for this batch"""
+    n = _lib.lib().rpc_dynamic_workspace_bytes(ctypes.byref(cfg), len(n_per_sample), _lib.counts(n_per_sample))
+    if n == 0:
+        raise _lib.RpcError(-2, "rpc_dynamic_workspace_bytes")
+    return int(n)
 
 
 def hard_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelCfg,
@@ -105,7 +142,7 @@ def hard_voxelize(points: torch.Tensor, n_per_sample: Sequence[int], cfg: VoxelC
     if cap < 0:
         raise _lib.RpcError(-2, "rpc_voxel_capacity")
     nbytes = L.rpc_workspace_bytes(ctypes.byref(cfg), B, n_arr)
-    ws = workspace if workspace is not None else _default_ws.get(nbytes, dev)
+    ws = workspace if workspace is not None else _hard_ws.get(nbytes, dev)
     N, P, C, F = points.shape[0], cfg.max_points, cfg.C, cfg.F
     if out is None:
         i32 = dict(dtype=torch.int32, device=dev)
@@ -247,7 +284,7 @@ def vfe_mean_bwd(grad_out: torch.Tensor, num_points: torch.Tensor, P: int, C: in
     return g
 
 
-PHASES = ("clear", "insert", "flag", "assign", "rank", "gather")
+PHASES = ("setup", "insert", "barrier", "scan", "emit", "tail")
 
 
 def phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Optional[torch.Tensor] = None,
@@ -258,7 +295,7 @@ def phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Option
     off = _lib.lib().rpc_workspace_stamps_offset(ctypes.byref(cfg), len(n_per_sample), n_arr)
     if off < 0:
         raise _lib.RpcError(-2, "rpc_workspace_stamps_offset")
-    ws = workspace if workspace is not None else _default_ws._buf[dev]
+    ws = workspace if workspace is not None else _hard_ws.current(dev)
     st = ws[off:off + 56].view(torch.int64).cpu().tolist()
     return {PHASES[k]: (st[k + 1] - st[k]) / 1e3 for k in range(6)}
 
@@ -273,7 +310,7 @@ def dyn_phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Op
     off = _lib.lib().rpc_dynamic_stamps_offset(ctypes.byref(cfg), len(n_per_sample), n_arr)
     if off < 0:
         raise _lib.RpcError(-2, "rpc_dynamic_stamps_offset")
-    ws = workspace if workspace is not None else _default_ws._buf[dev]
+    ws = workspace if workspace is not None else _default_ws.current(dev)
     st = ws[off:off + 80].view(torch.int64).cpu().tolist()
     return {DYN_PHASES[k]: (st[k + 1] - st[k]) / 1e3 for k in range(9)}
 

@@ -53,7 +53,12 @@ class StepPipeline:
         self.d_raw = [b[1] for b in self.d_in]
         self.outs: List = []
         self.graphs: List[Optional[torch.cuda.CUDAGraph]] = [None] * depth
-        self._gf: List[Optional[torch.Tensor]] = [None] * depth
+        # every slot owns its workspace (a captured graph bakes the address in, and rpc_voxelize_hard keeps its
+        # table clean between calls: nothing else may write there) and a persistent copy of the gradient the caller
+        # hands in, so that ONE capture per slot serves every step
+        ws_bytes = (ops.dynamic_workspace_bytes if dynamic else ops.hard_workspace_bytes)(cfg, self.n)
+        self.ws = [torch.empty((ws_bytes + 256,), dtype=torch.uint8, device=device) for _ in range(depth)]
+        self.d_gf: List[Optional[torch.Tensor]] = [None] * depth
         self.d_pack: List[torch.Tensor] = []
         self.graw: List[torch.Tensor] = []
         self._layout: Dict[str, tuple] = {}
@@ -86,11 +91,13 @@ class StepPipeline:
     # ---------------------------------------------------------------------------------------------
     def _fwd(self, k: int, out):
         if self.dynamic:
-            return ops.dynamic_scatter_mean(self.d_pts[k], self.n, self.cfg, raw=self.d_raw[k], bounds=self.bounds, out=out)
+            return ops.dynamic_scatter_mean(self.d_pts[k], self.n, self.cfg, raw=self.d_raw[k], bounds=self.bounds, out=out,
+                                            workspace=self.ws[k])
         if out is None:
             return ops.hard_voxelize(self.d_pts[k], self.n, self.cfg, raw=self.d_raw[k], bounds=self.bounds,
-                                     want_feats=True, want_maps=True, want_slots=False)
-        return ops.hard_voxelize(self.d_pts[k], self.n, self.cfg, raw=self.d_raw[k], bounds=self.bounds, out=out)
+                                     want_feats=True, want_maps=True, want_slots=False, workspace=self.ws[k])
+        return ops.hard_voxelize(self.d_pts[k], self.n, self.cfg, raw=self.d_raw[k], bounds=self.bounds, out=out,
+                                 workspace=self.ws[k])
 
     def _views(self, pack: torch.Tensor) -> Dict[str, torch.Tensor]:
         return {name: pack[off:off + nbytes].view(dtype).view(shape)
@@ -102,20 +109,26 @@ class StepPipeline:
         h = torch.empty(tuple(self.d_in[0].shape), dtype=torch.float32).pin_memory()
         return h[0], h[1]
 
-    def _path(self, k: int, grad_feats: torch.Tensor):
+    def _path(self, k: int):
         o = self._fwd(k, self.outs[k])
-        ops.step_bwd(grad_feats, o.num_points, o.point2voxel, self.cfg, raw=self.d_raw[k], bounds=self.bounds,
+        ops.step_bwd(self.d_gf[k], o.num_points, o.point2voxel, self.cfg, raw=self.d_raw[k], bounds=self.bounds,
                      out=self.graw[k])
 
     def _run(self, k: int, grad_feats: torch.Tensor):
+        # the gradient is copied into the slot's own buffer (stream-ordered after whatever produced it: submit makes
+        # s_cmp wait for the caller's stream), so the captured graph always reads the same address
+        if self.d_gf[k] is None or self.d_gf[k].shape != grad_feats.shape:
+            self.d_gf[k] = torch.empty(tuple(grad_feats.shape), dtype=torch.float32, device=self.dev)
+            self.graphs[k] = None
+        self.d_gf[k].copy_(grad_feats, non_blocking=True)
         if not self.use_graph:
-            return self._path(k, grad_feats)
-        if self.graphs[k] is None or self._gf[k] is not grad_feats:      # (re)capture for this gradient buffer
-            self._path(k, grad_feats)                                    # warm-up outside capture
+            return self._path(k)
+        if self.graphs[k] is None:
+            self._path(k)                                                # warm-up outside capture
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=self.s_cmp):
-                self._path(k, grad_feats)
-            self.graphs[k], self._gf[k] = g, grad_feats
+                self._path(k)
+            self.graphs[k] = g
         self.graphs[k].replay()
 
     # ---------------------------------------------------------------------------------------------
@@ -142,7 +155,9 @@ class StepPipeline:
                 self.d_pts[k].copy_(h_points, non_blocking=True)
                 self.d_raw[k].copy_(h_raw, non_blocking=True)
             self.ev_in[k].record(self.s_in)
+        caller = torch.cuda.current_stream(self.dev)                     # whatever produced grad_feats runs here
         with torch.cuda.stream(self.s_cmp):
+            self.s_cmp.wait_stream(caller)
             self.s_cmp.wait_event(self.ev_in[k])
             self.s_cmp.wait_event(self.ev_out[k])                        # this slot's previous results have left
             if self.pre_step is not None:

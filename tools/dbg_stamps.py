@@ -1,40 +1,65 @@
-import sys, numpy as np, torch, ctypes
-import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from oracle import ref_path as orc
-from robustpointclouds_b200 import PerturbCfg, VoxelCfg, _lib, ops, synth
-name = sys.argv[1] if len(sys.argv) > 1 else 'kitti'
-p = synth.PRESETS[name]; B = 6 if name == 'kitti' else 4
-C, P, V = p['C'], p['max_num_points'], p['max_voxels'][0]
-cfg = VoxelCfg.make(p['voxel_size'], p['point_cloud_range'], P, V, C, C)
-dist = sys.argv[2] if len(sys.argv) > 2 else 'lidar'
-clouds = synth.make_batch(name, B, dist=dist)
-if len(sys.argv) > 3:
-    for c in clouds: c[(c[:, :3] == 0).all(1), 0] = -1000.0   # move the null returns out of range
-raws = [synth.make_raw(c, 99+i) for i, c in enumerate(clouds)]
+"""Per-CTA phase stamps of k_hard_fwd (setup / insert / barrier / scan / emit / tail) on one workload:
+python tools/dbg_stamps.py [kitti|nuscenes] [lidar|uniform|clustered]
+env NOFLUSH=1: warm L2; NCTA: grid size; BATCH / POINTS: batch shape; RPC_SYNTH_NULL=0: no null returns"""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from robustpointclouds_b200 import PerturbCfg, VoxelCfg, _lib, ops, synth  # noqa: E402
+from robustpointclouds_b200.voxel_perturber import perturber_bounds  # noqa: E402
+
+name = sys.argv[1] if len(sys.argv) > 1 else "kitti"
+dist = sys.argv[2] if len(sys.argv) > 2 else "lidar"
+p = synth.PRESETS[name]
+B = int(os.environ.get("BATCH", "6" if name == "kitti" else "4"))
+N = int(os.environ.get("POINTS", str(p["N"])))
+C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
+cfg = VoxelCfg.make(p["voxel_size"], p["point_cloud_range"], P, V, C, C)
+clouds = synth.make_batch(name, B, N=N, dist=dist)
+raws = [synth.make_raw(c, 99 + i) for i, c in enumerate(clouds)]
 n = [len(c) for c in clouds]
-dev = torch.device('cuda:0')
-eb, fb = orc.perturber_bounds(C, True); bounds = PerturbCfg.make(eb, fb)
-pts = torch.from_numpy(np.concatenate(clouds)).to(dev); raw = torch.from_numpy(np.concatenate(raws)).to(dev)
+dev = torch.device("cuda:0")
+eb, fb = perturber_bounds(C, True)
+bounds = PerturbCfg.make(eb.tolist(), fb.tolist())
+pts = torch.from_numpy(np.concatenate(clouds)).to(dev)
+raw = torch.from_numpy(np.concatenate(raws)).to(dev)
 out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True)
 flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
 _lib.profile_enable(True)
-import os
 for it in range(4):
-    if not os.environ.get('NOFLUSH'): flush.zero_()
+    if not os.environ.get("NOFLUSH"):
+        flush.zero_()
     ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
     torch.cuda.synchronize()
-NC = int(os.environ.get('NCTA', '296'))
+NC = int(os.environ.get("NCTA", "296"))
 off = _lib.lib().rpc_workspace_stamps_offset(ctypes.byref(cfg), B, _lib.counts(n))
-ws = ops._default_ws._buf[dev]
-raw_st = ws[off:off + 8*16*NC].view(torch.int64).cpu().numpy().reshape(NC, 16)
+ws = ops._hard_ws.current(dev)
+raw_st = ws[off:off + 8 * 16 * NC].view(torch.int64).cpu().numpy().reshape(NC, 16)
 st = raw_st.astype(np.float64)
 t0 = st[:, 0].min()
 st = (st - t0) / 1e3
-names = ['clear', 'insert', 'flag', 'assign', 'rank', 'gather']
+names = ["setup", "insert", "barrier", "scan", "emit", "tail"]
 for k, nm in enumerate(names):
-    start = st[:, k]; arrive = st[:, 8 + k] if k < 5 else st[:, 6]
-    work = arrive - start
-    top = np.argsort(-work)[:8]
-    print(f"{nm:8s} start {start.min():7.2f}..{start.max():7.2f}  work min {work.min():6.2f} med {np.median(work):6.2f} p90 {np.percentile(work, 90):6.2f} max {work.max():6.2f}  all-arrived {arrive.max():7.2f}  slowest " + " ".join(f"{c}:{work[c]:.1f}" for c in top))
-print('insert: loads+cell of first batch done (cta-wide) med', np.median(st[:,13]), 'max', st[:,13].max())
-print('end', st[:, 6].max(), 'dist', dist, 'voxels', int(out.voxel_num[-1]), 'kept', int((out.point2voxel >= 0).sum()))
+    start, end = st[:, k], st[:, k + 1]
+    work = end - start
+    top = np.argsort(-work)[:6]
+    print(f"{nm:8s} start {start.min():7.2f}..{start.max():7.2f}  dur min {work.min():6.2f} med {np.median(work):6.2f} "
+          f"p90 {np.percentile(work, 90):6.2f} max {work.max():6.2f}  all-done {end.max():7.2f}  slowest " +
+          " ".join(f"{c}:{work[c]:.1f}" for c in top))
+smid = raw_st[:, 7]
+ins = st[:, 2] - st[:, 1]
+order = np.argsort(ins)
+print("insert by CTA (fastest 8): " + " ".join(f"{c}@sm{smid[c]}:{ins[c]:.1f}" for c in order[:8]))
+print("insert by CTA (slowest 8): " + " ".join(f"{c}@sm{smid[c]}:{ins[c]:.1f}" for c in order[-8:]))
+if os.environ.get("PERSM"):
+    persm = {}
+    for c in range(NC):
+        persm.setdefault(int(smid[c]), []).append(ins[c])
+    print("insert mean per SM (sm:us): " + " ".join(f"{m}:{np.mean(persm[m]):.0f}" for m in sorted(persm)))
+itend = st[:, 8:12] - st[:, 1:2]
+print("insert iteration ends (warp 0), median over CTAs:", np.round(np.median(itend, axis=0), 2), "max", np.round(itend.max(axis=0), 2))
+print("end", st[:, 6].max(), "dist", dist, "voxels", int(out.voxel_num[-1]), "kept", int((out.point2voxel >= 0).sum()))
