@@ -259,64 +259,137 @@ def cpu_baseline(name, clouds, raws, p, budget_s=12.0):
 
 
 # ------------------------------------------------------------------------------------------------
-def run_b200(args):
+def pgrad_pattern(n, rank, dev):
+    """flat perturber-gradient stand-in of rank r: r + 1 + i * 2^-10 -- exact in fp32, and so is every partial sum
+    over <= 8 ranks, so the all-reduced buffer can be compared with the closed form bit for bit"""
+    import torch
+    return (torch.arange(n, dtype=torch.float32, device=dev) * (1.0 / 1024.0) + float(rank + 1)).contiguous()
+
+
+def pgrad_expected(n, world, dev):
+    import torch
+    return torch.arange(n, dtype=torch.float32, device=dev) * (world / 1024.0) + float(world * (world + 1) // 2)
+
+
+class Collective:
+    """the step's only exchange: all-reduce of the perturber's flat parameter gradients (the reference gets
+    it from DDP, custom_hook.py:24-28), through this library's NVLink peer-memory kernel when every rank can map its
+    peers, else NCCL -- agreed by all ranks"""
+
+    def __init__(self, args, world, rank, dev):
+        import torch
+        import torch.distributed as dist
+        self.world, self.rank, self.dev, self.kind = world, rank, dev, args.allreduce
+        self.sync_par = None
+        self.sync_buf = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._pars = {}
+        self.peer = False
+        if world > 1 and args.allreduce in ("ll", "p2p"):
+            from robustpointclouds_b200 import PeerAllReduce
+            ok = 1.0
+            try:
+                self.sync_par = PeerAllReduce(4, dev)
+            except Exception as e:                      # no peer mapping on this box: every rank falls back together
+                print(f"[bench] rank {rank}: peer all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+                ok = 0.0
+            agree = torch.tensor([ok], device=dev)
+            dist.all_reduce(agree, op=dist.ReduceOp.MIN)
+            self.peer = agree.item() >= 1.0
+            if not self.peer:
+                self.sync_par = None
+
+    def for_size(self, n):
+        """PeerAllReduce for a buffer of n floats (None: NCCL / single GPU)"""
+        if not self.peer:
+            return None
+        if n not in self._pars:
+            from robustpointclouds_b200 import PeerAllReduce
+            self._pars[n] = PeerAllReduce(n, self.dev, mode="ll" if self.kind == "ll" else "oneshot")
+        return self._pars[n]
+
+    def rank_sync(self):
+        """device-side rendezvous of the ranks, OUTSIDE the per-step event pairs: every rank flushes its L2 at its
+        own pace, and without this the skew is paid inside the timed step by the all-reduce waiting for the peer"""
+        import torch.distributed as dist
+        if self.sync_par is not None:
+            self.sync_par.all_reduce(self.sync_buf)
+        elif self.world > 1:
+            dist.all_reduce(self.sync_buf)
+
+    def describe(self, n):
+        if self.world == 1:
+            return "none"
+        how = ("nccl all_reduce" if not self.peer else
+               "low-latency NVLink peer-memory all-reduce (rpc_allreduce_ll: value + call number pushed as one 8-byte store, in the step's graph)"
+               if self.kind == "ll" else "one-shot NVLink peer-memory all-reduce (rpc_allreduce_oneshot, in the step's graph)")
+        return how + " of %d fp32 perturber grads per step" % n
+
+    def timeouts(self):
+        t = 0
+        for q in list(self._pars.values()) + ([self.sync_par] if self.sync_par is not None else []):
+            t += int(q.state[2].item())
+        return t
+
+
+def measure(args, name, B_override, points, steps, warmup, coll, rank, world, dev, full):
+    """One workload on this rank's GPU: device-resident step time (CUDA-graph replay, cold L2), end-to-end time through
+    StepPipeline (pinned host buffers), per-kernel durations and the roofline figures.  `full`: the headline workload
+    (all legs); otherwise a shorter e2e leg and no lean / cpu legs."""
     import torch
     import torch.distributed as dist
 
-    from oracle import ref_path as orc           # bounds table + cpu_baseline leg only
-    from robustpointclouds_b200 import PerturbCfg, VoxelCfg, _lib, ops, synth
+    from robustpointclouds_b200 import PerturbCfg, StepPipeline, VoxelCfg, _lib, ops, synth
+    from robustpointclouds_b200.voxel_perturber import perturber_bounds
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    from robustpointclouds_b200.hostmem import bind_to_gpu_numa
-    numa_cpus = None if args.no_numa else bind_to_gpu_numa(local)      # pinned host buffers on the GPU's own NUMA node
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-
-    p, B, dynamic = workload(args.workload, args.batch)
+    global POINTS_OVERRIDE
+    saved = POINTS_OVERRIDE
+    POINTS_OVERRIDE = points
+    p, B, dynamic = workload(name, B_override)
+    POINTS_OVERRIDE = saved
     C, P, V = p["C"], p["max_num_points"], p["max_voxels"][0]
     F = C
     cfg = VoxelCfg.make(p["voxel_size"], p["point_cloud_range"], P, V, C, F)
-    clouds = synth.make_batch(args.workload.split("-")[0], B, N=p["N"], seed=1234 + rank * B)
+    clouds = synth.make_batch(name.split("-")[0], B, N=p["N"], seed=1234 + rank * B)
     raws = [synth.make_raw(c, 99 + rank * B + i) for i, c in enumerate(clouds)]
     n = [len(c) for c in clouds]
     N = sum(n)
-    eb, fb = orc.perturber_bounds(C, True)
-    bounds = PerturbCfg.make(eb, fb)
+    eb, fb = perturber_bounds(C, True)                      # the product's own table (no oracle in the GPU arm)
+    bounds = PerturbCfg.make(eb.tolist(), fb.tolist())
     h_pts = torch.from_numpy(np.concatenate(clouds)).pin_memory()
     h_raw = torch.from_numpy(np.concatenate(raws)).pin_memory()
     pts, raw = h_pts.to(dev), h_raw.to(dev)
+    # the graph-captured step owns its workspace (rpc_voxelize_hard keeps it clean between calls)
+    ws = torch.empty(((ops.dynamic_workspace_bytes if dynamic else ops.hard_workspace_bytes)(cfg, n) + 256,),
+                     dtype=torch.uint8, device=dev)
     if dynamic:
-        out = ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds)
+        out = ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds, workspace=ws)
         cap = N
     else:
-        out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True, want_slots=False)
+        out = ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, want_feats=True, want_maps=True, want_slots=False,
+                                workspace=ws)
         cap = out.capacity
     gfe = torch.randn((cap, F), device=dev, generator=torch.Generator(dev).manual_seed(5 + rank))
     graw = torch.empty((N, C), dtype=torch.float32, device=dev)
-    pgrad = torch.zeros(PERTURBER_PARAMS.get(C, 34641), dtype=torch.float32, device=dev)  # flat perturber grads
+    npar = PERTURBER_PARAMS.get(C, 34641)
+    pgrad = pgrad_pattern(npar, rank, dev)                  # this rank's flat perturber gradients (a fixed pattern)
+    psum = torch.zeros_like(pgrad)                          # their sum over the ranks
+    par = coll.for_size(npar)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
-    flush_rd = torch.zeros(L2_FLUSH_BYTES // 8, dtype=torch.int32, device=dev)        # 256 MiB, only ever read
+    flush_rd = torch.zeros(L2_FLUSH_BYTES // 8, dtype=torch.int32, device=dev) if args.flush == "write+read" else None
     flush_sink = torch.zeros(1, dtype=torch.int64, device=dev)
 
     def l2_flush():
-        """overwrite 512 MiB (evicts everything), then -- unless --flush write -- stream 256 MiB of clean data
+        """overwrite 512 MiB (evicts everything), then -- with --flush write+read -- stream 256 MiB of clean data
         through L2 so that the step does not also pay for writing back the flush's own dirty lines"""
         flush.zero_()
-        if args.flush == "write+read":
+        if flush_rd is not None:
             flush_sink.copy_(flush_rd.sum())
 
     def fwd():
         if dynamic:
-            ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+            ops.dynamic_scatter_mean(pts, n, cfg, raw=raw, bounds=bounds, out=out, workspace=ws)
         else:
-            ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out)
+            ops.hard_voxelize(pts, n, cfg, raw=raw, bounds=bounds, out=out, workspace=ws)
 
     def bwd():
         ops.step_bwd(gfe, out.num_points, out.point2voxel, cfg, raw=raw, bounds=bounds, out=graw)
@@ -325,38 +398,12 @@ def run_b200(args):
         fwd()
         bwd()
 
-    par = None
-    if world > 1 and args.allreduce in ("ll", "p2p"):
-        from robustpointclouds_b200 import PeerAllReduce
-        try:
-            par = PeerAllReduce(pgrad.numel(), dev, mode="ll" if args.allreduce == "ll" else "oneshot")
-        except Exception as e:                          # no peer mapping on this box: every rank falls back together
-            print(f"[bench] rank {rank}: peer all-reduce unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
-            par = None
-        agree = torch.tensor([1.0 if par is not None else 0.0], device=dev)
-        dist.all_reduce(agree, op=dist.ReduceOp.MIN)
-        if agree.item() < 1.0:
-            par = None
-
-    sync_buf = torch.zeros(4, dtype=torch.float32, device=dev)
-    sync_par = None
-    if par is not None:
-        from robustpointclouds_b200 import PeerAllReduce as _PAR
-        sync_par = _PAR(4, dev)                         # same mechanism as par, which every rank just built
-
-    def rank_sync():
-        """device-side rendezvous of the ranks, OUTSIDE the per-step event pairs: every rank flushes its L2 at its
-        own pace, and without this the skew is paid inside the timed step by the all-reduce waiting for the peer"""
-        if sync_par is not None:
-            sync_par.all_reduce(sync_buf)
-        elif world > 1:
-            dist.all_reduce(sync_buf)
-
-    def exchange():                                     # the step's only collective: perturber-gradient all-reduce
+    def exchange():                                     # perturber-gradient all-reduce: psum = sum over ranks of pgrad
         if par is not None:
-            par.all_reduce(pgrad)
+            par.all_reduce(pgrad, psum)
         elif world > 1:
-            dist.all_reduce(pgrad)
+            psum.copy_(pgrad)
+            dist.all_reduce(psum)
 
     graph = None
     if not args.no_graph:
@@ -383,17 +430,17 @@ def run_b200(args):
             path()
             exchange()
 
-    def timed(fn, steps, warmup):
-        for _ in range(warmup):
-            l2_flush(); rank_sync(); fn()
+    def timed(fn, k, w):
+        for _ in range(w):
+            l2_flush(); coll.rank_sync(); fn()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
         for a, b in ev:
             l2_flush()
-            rank_sync()
+            coll.rank_sync()
             a.record(); fn(); b.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -404,40 +451,48 @@ def run_b200(args):
             t = torch.tensor([tot], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             tot = float(t.item())
-        return tot                                   # ms for `steps` steps
+        return tot                                   # ms for `k` steps
 
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(dev.index)
     sampler.start()
-    tot_ms = timed(step, args.steps, args.warmup)
+    tot_ms = timed(step, steps, warmup)
     clocks = sampler.stop()
+    ms_per_step = tot_ms / steps
+
+    # the all-reduced buffer of the LAST timed step against the closed form, bit for bit (outside the timed region)
+    coll_check = "n/a"
+    if world > 1:
+        okv = torch.tensor([1.0 if torch.equal(psum, pgrad_expected(npar, world, dev)) else 0.0], device=dev)
+        dist.all_reduce(okv, op=dist.ReduceOp.MIN)
+        coll_check = "ok" if okv.item() >= 1.0 else "mismatch"
 
     vn = out.voxel_num.cpu().numpy()
     M = int(vn[-1])
     K = int((out.point2voxel >= 0).sum().item())
-    launches_per_step = 2 + (1 if par is not None else 0)   # k_hard_fwd | k_dyn_scatter (persistent, cooperative) + k_step_bwd [+ k_allreduce_oneshot]
+    launches_per_step = 2 + (1 if par is not None else 0)   # forward (persistent, cooperative) + k_step_bwd [+ all-reduce]
 
     # ---- e2e: pinned host buffers in, every API-visible output back to pinned host buffers, through the
     # package's public host front end (StepPipeline: H2D, kernels and D2H on three streams, double-buffered,
     # every step's copies inside the timed region); the perturber-gradient all-reduce follows each submit.
-    from robustpointclouds_b200 import StepPipeline
     pipe = StepPipeline(cfg, bounds, n, dev, depth=2, dynamic=dynamic, use_graph=not args.no_graph, pre_step=l2_flush)
     h_in_pts, h_in_raw = pipe.alloc_host_inputs()           # the caller's pinned staging buffer (one copy per step)
     h_in_pts.copy_(h_pts)
     h_in_raw.copy_(h_raw)
-    e2e_steps = max(3, min(args.steps, 100))
+    e2e_steps = max(3, min(steps, 100))
 
     def e2e_measure(pipe):
         def e2e_run(k):
             for _ in range(k):
                 pipe.submit(h_in_pts, h_in_raw, gfe)
                 if world > 1 and par is None:
-                    dist.all_reduce(pgrad)
+                    psum.copy_(pgrad)
+                    dist.all_reduce(psum)
                 elif par is not None:
                     with torch.cuda.stream(pipe.s_cmp):
-                        par.all_reduce(pgrad)
+                        par.all_reduce(pgrad, psum)
             pipe.drain()
 
-        e2e_run(max(3, min(args.warmup, 5)))
+        e2e_run(max(3, min(warmup, 5)))
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -458,36 +513,32 @@ def run_b200(args):
             ms = float(t.item())
         return ms
 
-    # two consecutive blocks of e2e_steps, the faster one is reported and both are listed: on this pool one block in
-    # a few comes out with the two PCIe directions not overlapping (0.99 instead of 0.52 ms on KITTI, same box, same
-    # process), which is the VM's copy-engine scheduling, not the pipeline
-    e2e_blocks = [e2e_measure(pipe), e2e_measure(pipe)]
-    e2e_ms = min(e2e_blocks)
+    # consecutive blocks of e2e_steps; the MEDIAN block is reported and all are listed (on this pool one block in a few
+    # comes out with the two PCIe directions not overlapping -- the VM's copy-engine scheduling, not the pipeline)
+    nblocks = 5 if full else 3
+    e2e_blocks = [e2e_measure(pipe) for _ in range(nblocks)]
+    e2e_ms = float(np.median(e2e_blocks))
+    h2d, d2h = pipe.h2d_bytes, pipe.d2h_bytes
+    del pipe
     # the same call with host_fields=LEAN_FIELDS: the zero-padded voxels tensor (an intermediate once the VFE mean is
-    # fused; the reference hands feats + coors on to the middle encoder) stays on the device.  Reported beside `e2e`,
-    # which keeps returning every API-visible output.
-    lean_ms = lean_d2h = None
-    if not dynamic:
+    # fused; the reference hands feats + coors on to the middle encoder) stays on the device.
+    lean = None
+    if full and not dynamic:
         lean_pipe = StepPipeline(cfg, bounds, n, dev, depth=2, dynamic=False, use_graph=not args.no_graph,
                                  pre_step=l2_flush, host_fields=StepPipeline.LEAN_FIELDS)
-        lean_ms = e2e_measure(lean_pipe)
-        lean_d2h = lean_pipe.d2h_bytes
+        lb = [e2e_measure(lean_pipe) for _ in range(3)]
+        lean = (float(np.median(lb)), lean_pipe.d2h_bytes, lb)
         del lean_pipe
-    h2d, d2h = pipe.h2d_bytes, pipe.d2h_bytes
-    # a peer that did not arrive within 2 s sets a status word instead of hanging the GPU: report it, do not hide it
-    ar_timeouts = (int(par.state[2].item()) + int(sync_par.state[2].item())) if par is not None else 0
-    if ar_timeouts:
-        print(f"[bench] rank {rank}: peer all-reduce saw a timeout", file=sys.stderr)
 
     # ---- per-kernel durations (CUDA events inside the library, same steps, cold L2, no graph)
     stages, phases = {}, {}
     _lib.profile_enable(True)
-    prof_steps = max(3, min(args.steps, 30))
+    prof_steps = max(3, min(steps, 30))
     for it in range(prof_steps + 2):
         l2_flush()
         fwd()
         t_fwd = _lib.profile_read()
-        ph = ops.dyn_phase_times_us(cfg, n, dev=dev) if dynamic else ops.phase_times_us(cfg, n, dev=dev)
+        ph = (ops.dyn_phase_times_us(cfg, n, workspace=ws) if dynamic else ops.phase_times_us(cfg, n, workspace=ws))
         bwd()
         t_bwd = _lib.profile_read()
         if it >= 2:
@@ -499,61 +550,113 @@ def run_b200(args):
     stage_us = {k2: round(1e3 * float(np.mean(v)), 3) for k2, v in stages.items()}
     peak, peak_src = measured_peak_gbs()
     balg = b_alg_dyn(N, C, M, F) if dynamic else b_alg_hard(N, C, P, M, K, F)
-    # per-kernel algorithmic bytes (DESIGN.md "kernels"): what that kernel alone must read and write
+    # this repo's own per-kernel byte model (DESIGN.md "kernels"): what that kernel alone must read and write
     kern_bytes = {
-        # forward: points + raw in; voxels, coors(4)+num_points, feats, point2voxel out
         "k_hard_fwd": 4 * (2 * N * C + M * P * C + 5 * M + M * F + N),
-        # dynamic forward: points + raw in; per-point coors (4) + map, voxel coors (4), counts, feats out
         "k_dyn_scatter": 4 * (2 * N * C + 5 * N + 5 * M + M * F),
-        # backward: point2voxel + raw + grad feats + counts in, grad_raw out
         "k_step_bwd": 4 * (N + N * C + M * F + M + N * C),
     }
     dom = max(stage_us, key=stage_us.get) if stage_us else None
-    ms_per_step = tot_ms / args.steps
+    step_ach = balg / (ms_per_step * 1e-3) / 1e9
+    # roofline.frac: algorithmic bytes of the WHOLE step / duration of the dominant kernel / measured peak;
+    # step_*: the same bytes over the whole graph-replayed step (what `value` is computed from)
     roof = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src, "traffic": None,
-            "stage_us": stage_us, "fwd_phase_us": {k2: round(float(np.mean(v)), 2) for k2, v in phases.items()},
-            "step": {"b_alg_bytes": balg, "achieved": round(balg / (ms_per_step * 1e-3) / 1e9, 2),
-                     "frac": round(balg / (ms_per_step * 1e-3) / 1e9 / peak, 4)}}
+            "b_alg_bytes": balg, "stage_us": stage_us,
+            "fwd_phase_us": {k2: round(float(np.mean(v)), 2) for k2, v in phases.items()},
+            "step_b_alg_bytes": balg, "step_achieved": round(step_ach, 2), "step_frac": round(step_ach / peak, 4),
+            "step": {"b_alg_bytes": balg, "achieved": round(step_ach, 2), "frac": round(step_ach / peak, 4)}}
     if dom is not None:
-        roof.update(ncu_traffic(args, dom))
-        kb = kern_bytes.get(dom, balg)
-        a = kb / (stage_us[dom] * 1e-6) / 1e9
-        roof.update({"achieved": round(a, 2), "frac": round(a / peak, 4), "b_alg_bytes": kb})
+        if name == args.workload:
+            roof.update(ncu_traffic(args, dom))
+        a = balg / (stage_us[dom] * 1e-6) / 1e9
+        roof.update({"achieved": round(a, 2), "frac": round(a / peak, 4),
+                     "kernel_bytes_model": {k2: kern_bytes[k2] for k2 in stage_us if k2 in kern_bytes}})
     else:
         roof.update({"achieved": None, "frac": None})
+    total_pts = N * world
+    res = {
+        "value": round(total_pts / (ms_per_step * 1e-3) / 1e6, 2), "ms_per_step": round(ms_per_step, 5),
+        "config": config_dict(name, p, B, l2="flushed between steps, outside the per-step CUDA-event pairs: 512 MiB overwrite" +
+                              (" then a 256 MiB read-only sweep (L2 left full of clean lines)"
+                               if args.flush == "write+read" else ""), cuda_graph=graph is not None, voxels=M, kept_points=K,
+                              collective=coll.describe(npar), collective_check=coll_check),
+        "clocks": clocks,
+        "e2e": {"value": round(total_pts / (e2e_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "ms_per_step": round(e2e_ms / e2e_steps, 5),
+                "blocks_ms_per_step": [round(b / e2e_steps, 5) for b in e2e_blocks], "block_stat": "median",
+                "how": "StepPipeline: pinned host in/out, ONE H2D and ONE D2H copy per step (packed buffers), H2D | kernels | D2H on three streams, depth 2"},
+        "gpu_launches": launches_per_step * steps,
+        "roofline": roof,
+    }
+    if lean is not None:
+        res["e2e_lean"] = {"value": round(total_pts / (lean[0] / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
+                           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": lean[1],
+                           "ms_per_step": round(lean[0] / e2e_steps, 5),
+                           "blocks_ms_per_step": [round(b / e2e_steps, 5) for b in lean[2]],
+                           "how": "as e2e, StepPipeline(host_fields=LEAN_FIELDS): feats, coors, num_points, voxel_num and grad_raw return to the host, the zero-padded voxels stay on the device"}
+    if full and world == 1 and not args.no_cpu:
+        res["cpu_baseline"] = cpu_baseline(name, clouds, raws, p)
+    return res
 
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    from robustpointclouds_b200.hostmem import bind_to_gpu_numa
+    numa_cpus = None if args.no_numa else bind_to_gpu_numa(local)      # pinned host buffers on the GPU's own NUMA node
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    coll = Collective(args, world, rank, dev)
+
+    head = measure(args, args.workload, args.batch, args.points, args.steps, args.warmup, coll, rank, world, dev, True)
+    # BASELINE.json configs[2], [3] and the top of the configs[4] sweep in the same invocation (shorter runs); at 8 GPUs
+    # the dynamic workload with ONE sweep per rank is configs[3] as written ("batch-sharded on 8 x B200")
+    also = {}
+    if not args.no_also and not args.batch and not args.points and args.workload == "kitti":
+        k = max(10, min(args.steps, 60))
+        extra = [("nuscenes", "nuscenes", 0, 0), ("nuscenes-dynamic", "nuscenes-dynamic", 0, 0)]
+        if world == 8:
+            extra.append(("nuscenes-dynamic-1-sweep-per-gpu", "nuscenes-dynamic", 1, 0))
+        if world == 1:
+            extra.append(("kitti-2x2M", "kitti", 2, 2_000_000))
+        for key, wl, b, pts_n in extra:
+            r = measure(args, wl, b, pts_n, k, max(3, min(args.warmup, 5)), coll, rank, world, dev, False)
+            also[key] = {"value": r["value"], "unit": "M points/s", "ms_per_step": r["ms_per_step"], "steps": k,
+                         "workload": r["config"]["workload"], "voxels": r["config"]["voxels"],
+                         "collective_check": r["config"]["collective_check"],
+                         "roofline": {q: r["roofline"][q] for q in ("kernel", "b_alg_bytes", "achieved", "frac", "stage_us",
+                                                                   "step_achieved", "step_frac")},
+                         "e2e": {q: r["e2e"][q] for q in ("value", "ms_per_step", "h2d_bytes_per_step",
+                                                          "d2h_bytes_per_step", "blocks_ms_per_step")}}
+    ar_timeouts = coll.timeouts()
+    if ar_timeouts:
+        print(f"[bench] rank {rank}: peer all-reduce saw a timeout", file=sys.stderr)
     if rank == 0:
-        total_pts = N * world
+        head["config"]["collective_timeouts"] = ar_timeouts
+        if numa_cpus:
+            head["e2e"]["how"] += "; process bound to the %d CPUs local to the GPU" % len(numa_cpus)
         line = {
-            "metric": "M points/s perturb+voxelize+VFE fwd/bwd", "value": round(total_pts / (ms_per_step * 1e-3) / 1e6, 2),
+            "metric": "M points/s perturb+voxelize+VFE fwd/bwd", "value": head["value"],
             "unit": "M points/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": round(ms_per_step, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": config_dict(args.workload, p, B, l2="flushed between steps, outside the per-step CUDA-event pairs: 512 MiB overwrite" +
-                                  (" then a 256 MiB read-only sweep (L2 left full of clean lines)"
-                                   if args.flush == "write+read" else ""), cuda_graph=graph is not None, voxels=M, kept_points=K,
-                                  collective=((("low-latency NVLink peer-memory all-reduce (rpc_allreduce_ll: value + call number pushed as one 8-byte store, in the step's graph)"
-                                                if args.allreduce == "ll" else
-                                                "one-shot NVLink peer-memory all-reduce (rpc_allreduce_oneshot, in the step's graph)")
-                                               if par is not None else "nccl all_reduce") +
-                                              " of %d fp32 perturber grads per step" % pgrad.numel())
-                                  if world > 1 else "none", collective_timeouts=ar_timeouts),
-            "clocks": clocks,
-            "e2e": {"value": round(total_pts / (e2e_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                    "ms_per_step": round(e2e_ms / e2e_steps, 5),
-                    "blocks_ms_per_step": [round(b / e2e_steps, 5) for b in e2e_blocks],
-                    "how": "StepPipeline: pinned host in/out, ONE H2D and ONE D2H copy per step (packed buffers), H2D | kernels | D2H on three streams, depth 2" +
-                           ("; process bound to the %d CPUs local to the GPU" % len(numa_cpus) if numa_cpus else "")},
-            "e2e_lean": (None if lean_ms is None else
-                         {"value": round(total_pts / (lean_ms / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
-                          "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": lean_d2h, "ms_per_step": round(lean_ms / e2e_steps, 5),
-                          "how": "as e2e, StepPipeline(host_fields=LEAN_FIELDS): feats, coors, num_points, voxel_num and grad_raw return to the host, the zero-padded voxels stay on the device"}),
-            "gpu_launches": launches_per_step * args.steps,
-            "roofline": roof,
+            "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": head["config"], "clocks": head["clocks"],
+            "e2e": head["e2e"], "e2e_lean": head.get("e2e_lean"), "gpu_launches": head["gpu_launches"],
+            "roofline": head["roofline"],
         }
-        if world == 1 and not args.no_cpu:
-            line["cpu_baseline"] = cpu_baseline(args.workload, clouds, raws, p)
+        if "cpu_baseline" in head:
+            line["cpu_baseline"] = head["cpu_baseline"]
+        if also:
+            line["also"] = also
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -577,6 +680,7 @@ def main():
     ap.add_argument("--flush", default="write", choices=["write", "write+read"],
                     help="L2 flush between steps: 512 MiB overwrite, optionally followed by a 256 MiB read sweep")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-also", action="store_true", help="headline workload only (no nuscenes / dynamic / 2 x 2M entries)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     global POINTS_OVERRIDE
