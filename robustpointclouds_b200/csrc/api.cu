@@ -224,7 +224,7 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     fp.ntiles = (int)pl.ntiles; fp.ng1 = (int)pl.ng1; fp.LS = pl.LS;
     {
         static int pf = -1;                                         // RPC_TABLE_PREFETCH=0|1|2 (kernel experiments)
-        if (pf < 0) { const char *e = getenv("RPC_TABLE_PREFETCH"); pf = e ? atoi(e) : 0; }
+        if (pf < 0) { const char *e = getenv("RPC_TABLE_PREFETCH"); pf = e ? atoi(e) : 1; }
         fp.pf_mode = pf;
     }
     fp.gd = gd; fp.bd = pl.bd; fp.pd = pd;

@@ -304,6 +304,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     }
     __syncthreads();
     const bool was_clean = s_flag != 0;
+    if (p.stamps && tid == 0) p.stamps[blockIdx.x * 16 + 15] = was_clean ? 1ull : 0ull;
     auto my_range = [&](int it, TileRange &tr) -> int {              // -> tile index or -1
         const int k = it * kSub + (tid >> 8);
         if (k < kTrCache) {
@@ -422,6 +423,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             if (p.p2s) p.p2s[idx] = -1;
         }
         if constexpr (kTma) __syncwarp();                            // the stage may be refilled from here on
+        if (p.stamps && it == 0) stamp(p, 12);                       // (warp 0: rows loaded, cells known)
         // claim / find the cell's entry: blind 16-byte CAS along the linear probe order (at LiDAR load factors ~0.3
         // the home entry is free or already the cell's own for most points: one L2 round trip)
         bool cand = false;                                           // first point of the cell so far
@@ -451,6 +453,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                 }
                 pos = pos + 1 == size ? 0u : pos + 1;
             }
+            if (p.stamps && it == 0) stamp(p, 13);                   // (warp 0: probes done)
             // A point that is not the first of its cell ARRIVES: it takes the next of the cell's P-1 arrival slots
             // (one atomicAdd on the entry's counter, one plain store) -- unordered; the first point sorts them when
             // it emits the voxel.  Only a cell with more than P points overflows: arrival P-1 and later compete for
@@ -487,6 +490,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                 }
             }
         }
+        if (p.stamps && it == 0) stamp(p, 14);                       // (warp 0: arrivals done)
         const uint32_t hs = cand ? h + 1u : 0u;
         if (it < kHsCache) s_hs[it * kPT + tid] = hs;
         else if (idx >= 0) p.hslot[idx] = hs;
