@@ -42,17 +42,28 @@ class _ScatterRows(torch.autograd.Function):
         return g_vox, g_rows, None, None
 
 
+LOSS_KEYS = ("l2_norm", "intensity_loss", "bias_loss", "imbalance_loss")
+
+
+def zero_loss_dict(device: torch.device) -> Dict[str, torch.Tensor]:
+    """The dict the reference's ``extract_feat`` falls back to when there is no valid row or the adversary fails
+    (adversarial_voxelnet.py:119-131): the four keys ``AdversarialVoxelNet.loss`` indexes, all zero.  (The reference
+    builds three of them on the CPU; here all four live on the voxels' device.)"""
+    return {k: torch.zeros((), dtype=torch.float32, device=device) for k in LOSS_KEYS}
+
+
 def perturb_voxels(voxels: torch.Tensor, num_points: torch.Tensor, adversary: Callable,
                    mask_mode: str = "rowsum"):
-    """-> (perturbed_voxels [M,P,C], loss_dict or None, valid_count).  ``mask_mode='rowsum'`` reproduces the
+    """-> (perturbed_voxels [M,P,C], loss_dict, valid_count).  ``mask_mode='rowsum'`` reproduces the
     reference's ``voxels_2d.sum(dim=1) != 0`` (which also skips real points whose features sum to zero);
     ``'count'`` uses ``slot < num_points``.  One host sync (the size of the valid set), where the
-    reference's boolean index has one too."""
+    reference's boolean index has one too.  No valid row: the clean voxels and the zero-valued loss dict
+    (adversarial_voxelnet.py:118-121)."""
     M, P, C = voxels.shape
     vr = ops.valid_rows(voxels, num_points, mask_mode)
     K = vr.k()
     if K == 0:
-        return voxels, None, 0
+        return voxels, zero_loss_dict(voxels.device), 0
     valid = vr.rows[:K]
     out = adversary(valid)
     perturbed_valid, loss_dict = out if isinstance(out, tuple) else (out, None)
@@ -65,18 +76,24 @@ def extract_voxel_features(voxel_dict: Dict[str, torch.Tensor], voxel_encoder: C
                            disabled: bool = False, mask_mode: str = "rowsum"):
     """The part of ``AdversarialVoxelNet.extract_feat`` in front of the middle encoder
     (adversarial_voxelnet.py:66-137): gate ``training and adversary and not disabled and epoch >= 3``
-    (:77-78), perturb the valid rows, fall back to the clean voxels when the adversary fails (:123-132),
-    then ``voxel_encoder(voxels, num_points, coors)``.  Returns (voxel_features, loss_dict or None)."""
+    (:77-78), perturb the valid rows, then ``voxel_encoder(voxels, num_points, coors)``.  Failure paths as the
+    reference has them (:118-132): no valid row, ANY exception raised by the adversary, or its NaN fall-back
+    (which returns ``(input, tensor(0.))`` -- indexing that tensor with ``'l2_norm'`` raises in the reference and
+    lands in the same ``except Exception``) all continue with the CLEAN voxels and the zero-valued four-key loss
+    dict that ``AdversarialVoxelNet.loss`` indexes.  Returns (voxel_features, loss_dict); loss_dict is None only
+    when the gate is closed (the reference leaves ``_current_loss_dict = None`` then)."""
     voxels, num_points, coors = voxel_dict["voxels"], voxel_dict["num_points"], voxel_dict["coors"]
     loss_dict = None
-    if training and adversary is not None and not disabled and epoch >= 3 and voxels.dim() == 3:
+    if training and adversary is not None and not disabled and epoch >= 3:
+        clean = voxels
         try:
             perturbed, loss_dict, _ = perturb_voxels(voxels, num_points, adversary, mask_mode)
-            if isinstance(loss_dict, torch.Tensor):      # the adversary's NaN fall-back returns tensor(0.)
-                loss_dict = None
+            loss_dict["l2_norm"]                         # a tensor / None here raises like the reference's lookup
             voxels = perturbed
-        except RuntimeError:
-            loss_dict = None
+        except Exception as e:                           # noqa: BLE001 -- the reference catches Exception (:123)
+            print(f"Warning: Adversary failed with error: {e}")
+            loss_dict = zero_loss_dict(clean.device)
+            voxels = clean
     feats = voxel_encoder(voxels, num_points, coors)
     return feats, loss_dict
 
@@ -87,9 +104,11 @@ class _AdversarialStep(torch.autograd.Function):
     def forward(ctx, points, raw, n_per_sample, cfg: VoxelCfg, bounds: PerturbCfg, out: Optional[ops.HardVoxels]):
         hv = ops.hard_voxelize(points, n_per_sample, cfg, raw=raw, bounds=bounds, want_feats=True,
                                want_maps=True, want_slots=False, out=out)
-        ctx.save_for_backward(raw, hv.num_points, hv.point2voxel)
+        # a caller-owned `out` is overwritten through raw pointers by the next forward: the backward keeps its own
+        # copies of the two small integer maps then (one backward per forward stays valid after `out` is reused)
+        num_points, p2v = (hv.num_points.clone(), hv.point2voxel.clone()) if out is not None else (hv.num_points, hv.point2voxel)
+        ctx.save_for_backward(raw, num_points, p2v)
         ctx.cfg, ctx.bounds = cfg, bounds
-        ctx.hv = hv
         ctx.mark_non_differentiable(hv.voxels, hv.coors, hv.num_points, hv.voxel_num)
         return hv.feats, hv.voxels, hv.coors, hv.num_points, hv.voxel_num
 
@@ -114,7 +133,8 @@ class _DynamicStep(torch.autograd.Function):
     @staticmethod
     def forward(ctx, points, raw, n_per_sample, cfg: VoxelCfg, bounds: PerturbCfg, out: Optional[ops.DynVoxels]):
         dv = ops.dynamic_scatter_mean(points, n_per_sample, cfg, raw=raw, bounds=bounds, out=out)
-        ctx.save_for_backward(raw, dv.num_points, dv.point2voxel)
+        num_points, p2v = (dv.num_points.clone(), dv.point2voxel.clone()) if out is not None else (dv.num_points, dv.point2voxel)
+        ctx.save_for_backward(raw, num_points, p2v)
         ctx.cfg, ctx.bounds = cfg, bounds
         ctx.mark_non_differentiable(dv.voxel_coors, dv.num_points, dv.voxel_num, dv.point2voxel)
         return dv.feats, dv.voxel_coors, dv.num_points, dv.voxel_num, dv.point2voxel

@@ -121,6 +121,29 @@ def test_extract_feat_matches_reference_lines(golden_dir, name, C):
         f2, ld2 = rpc.extract_voxel_features(dict(voxels=voxels, num_points=num, coors=coors), vfe, adversary=spy, **kw)
         assert ld2 is None
         assert np.array_equal(f2.cpu().numpy(), orc.vfe_mean_fwd(g["voxels"], g["num_points"], C))
+    # failure paths (adversarial_voxelnet.py:118-132): clean voxels + the zero-valued four-key dict that loss() indexes
+    clean_feats = orc.vfe_mean_fwd(g["voxels"], g["num_points"], C)
+
+    def check_fallback(f3, ld3):
+        assert set(ld3) == {"l2_norm", "intensity_loss", "bias_loss", "imbalance_loss"}
+        assert all(isinstance(v, torch.Tensor) and v.device.type == "cuda" and float(v) == 0.0 for v in ld3.values())
+        assert np.array_equal(f3.cpu().numpy(), clean_feats)
+
+    def raises(x):                                                    # any Exception, not only RuntimeError
+        raise ValueError("adversary exploded")
+
+    check_fallback(*rpc.extract_voxel_features(dict(voxels=voxels, num_points=num, coors=coors), vfe, adversary=raises,
+                                               training=True, epoch=3))
+    # the perturber's own NaN fall-back returns (input, tensor(0.)): the reference's loss_dict['l2_norm'] lookup raises
+    check_fallback(*rpc.extract_voxel_features(dict(voxels=voxels, num_points=num, coors=coors), vfe,
+                                               adversary=lambda x: (x, torch.tensor(0.0, device=x.device)),
+                                               training=True, epoch=3))
+    # empty valid set: every row sums to zero (:118-121)
+    zero_vox = torch.zeros_like(voxels)
+    f4, ld4 = rpc.extract_voxel_features(dict(voxels=zero_vox, num_points=num, coors=coors), vfe, adversary=raises,
+                                         training=True, epoch=3)
+    assert set(ld4) == {"l2_norm", "intensity_loss", "bias_loss", "imbalance_loss"} and all(float(v) == 0.0 for v in ld4.values())
+    assert not f4.cpu().numpy().any()
 
 
 def test_valid_rows_scatter_gather_vs_oracle():
