@@ -15,3 +15,14 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return os.path.join(ROOT, "tests", "golden")
+
+
+def assert_pgrad_matches_fp64(got, g, key, rel=1e-4):
+    """Parameter gradient `got` of parameter `key` against the fp64 run of the REFERENCE class stored in the fixture
+    (``pgrad64_*``: unclamped, tests/golden/make_golden.py), clamped to +-0.1 like the reference's gradient hook
+    (voxel_perturber.py:465-475).  The reference's own fp32 run agrees with its fp64 run to 1e-7, so the bound is
+    the stated bar: 1e-4 of the tensor's largest entry."""
+    import numpy as np
+    ref = np.clip(np.nan_to_num(np.asarray(g[f"pgrad64_{key}"], np.float64), nan=0.0), -0.1, 0.1)
+    scale = max(float(np.abs(ref).max()), 1e-6)
+    np.testing.assert_allclose(np.asarray(got, np.float64), ref, rtol=rel, atol=rel * scale, err_msg=key)

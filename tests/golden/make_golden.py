@@ -85,6 +85,11 @@ def perturber_case(builder, name, C, training, hidden, K, seed):
     state = {k: v.detach().clone().numpy() for k, v in adv.state_dict().items()}
 
     x = synth_points(K, C, seed + 2)
+    # fp64 shadow of the same module on the same input: arbitrates the tolerance of the parameter-gradient pin
+    # (rtol 1e-2 against the fp32 run was two orders looser than the stated bar)
+    import copy
+    adv64 = copy.deepcopy(adv).double()
+    adv64.train(training)
     captured = {}
     orig = adv._apply_physical_constraints
 
@@ -113,6 +118,30 @@ def perturber_case(builder, name, C, training, hidden, K, seed):
         out[f"state_{k}"] = v
     for k, q in adv.named_parameters():
         out[f"pgrad_{k}"] = q.grad.numpy()  # after the +-0.1 clamp hook (voxel_perturber.py:465-475)
+    # the fp64 run: same weights, same input, same loss; gradients after the same +-0.1 clamp hooks
+    cap64 = {}
+    orig64 = adv64._apply_physical_constraints
+
+    def spy64(p_, vf):
+        o = orig64(p_, vf)
+        cap64["p"] = o
+        return o
+
+    adv64._apply_physical_constraints = spy64
+    y64, ld64 = adv64(x.double())
+    p64 = cap64["p"]
+    p64.retain_grad()
+    total64 = ((y64 * w.double()).sum() + ld64["l2_norm"] + 2 * ld64["intensity_loss"] + 3 * ld64["bias_loss"]
+               + 4 * ld64["imbalance_loss"])
+    for q in adv64.parameters():
+        q.grad = None
+    total64.backward()
+    out["y64"] = y64.detach().numpy()
+    out["grad_p64"] = p64.grad.numpy()
+    for k, v in ld64.items():
+        out[f"loss64_{k}"] = v.detach().numpy()
+    for k, q in adv64.named_parameters():
+        out[f"pgrad64_{k}"] = q.grad.numpy()
     np.savez_compressed(os.path.join(HERE, f"perturber_{name}.npz"), **out)
     print(name, "K", K, "C", C, "l2", float(ld["l2_norm"]), "max|pgrad|",
           max(float(np.abs(q.grad.numpy()).max()) for q in adv.parameters()))
