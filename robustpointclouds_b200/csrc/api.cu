@@ -110,7 +110,7 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl, bool 
     pl->o_clean = o;
     pl->o_tab = o;    o += align_up(sizeof(Entry) * (size_t)tab);
     pl->o_l0 = o;     o += align_up(8 * (size_t)(tiles + 1));
-    pl->o_l1 = o;     o += align_up(4 * (size_t)(g1 + 1));
+    pl->o_l1 = o;     o += align_up(4 * (size_t)kL1Stride * (size_t)(g1 + 1));
     pl->o_lists = o;  o += align_up(4 * (size_t)pl->LS * (size_t)tab);   // sparse: rows of cells with > 2 points
     pl->o_ovf = o;    o += align_up(4 * (size_t)pl->LS * (size_t)pts);   // sparse: cells with > P points
     pl->front_end = o;
@@ -226,6 +226,9 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
         static int pf = -1;                                         // RPC_TABLE_PREFETCH=0|1|2 (kernel experiments)
         if (pf < 0) { const char *e = getenv("RPC_TABLE_PREFETCH"); pf = e ? atoi(e) : 1; }
         fp.pf_mode = pf;
+        static int dbg = -1;
+        if (dbg < 0) { const char *e = getenv("RPC_DBG"); dbg = e ? atoi(e) : 0; }
+        fp.dbg = dbg;
     }
     fp.gd = gd; fp.bd = pl.bd; fp.pd = pd;
     return raw ? launch_hard_t<C, true>(fp, smem, st) : launch_hard_t<C, false>(fp, smem, st);

@@ -52,6 +52,8 @@ constexpr int kSub = kPT / kTile;               // tiles a CTA works on per iter
 constexpr int kCtasPerSM = 2;                   // resident CTAs per SM (register cap 32 at 1024 threads)
 constexpr int kGrp = 32;                        // tiles per counter group (8192 points)
 constexpr int kMaxGroups = 8192;                // group counters are scanned in shared memory (32 KB)
+constexpr int kL1Stride = 64;                   // ints between two group counters: 256 bytes, so that the REDs of one
+                                                // iteration (256 per counter) spread over L2 slices instead of one line
 constexpr int kTrCache = 128;                   // tile ranges cached in shared memory per CTA (2 KB)
 constexpr int kHsCache = 8;                     // iterations whose per-point entry word stays in shared memory
 constexpr uint32_t kWBase = 0x40000000u;        // level value of point i: kWBase - i  (> 0, larger = earlier)
@@ -79,7 +81,7 @@ struct FwdParams {
     Entry *tab;                                 // [tab_total]
     uint32_t *hslot;                            // [ntotal]   1 + table entry of a candidate first point, else 0
     unsigned long long *l0;                     // [ntiles]   first points per warp of the tile, one byte each
-    int *l1;                                    // [ng1]      first points per group of kGrp tiles
+    int *l1;                                    // [ng1 * kL1Stride]  first points per group of kGrp tiles
     uint32_t *lists;                            // [tab_total * LS]  per entry: W of arrivals 1..P-2, then the id of its overflow list
     uint32_t *ovf;                              // [ntotal * LS]     overflow lists (cells with more than P points): P-1 levels
     float *voxels; int *coors; int *num_points; int *voxel_num; int *p2v; int *p2s; float *feats;
@@ -88,6 +90,7 @@ struct FwdParams {
     unsigned long long clean_lo, front_end, back_off, ws_bytes;
     int ntiles, ng1, LS;
     int pf_mode;                                // table prefetch: 0 none, 1 per line, 2 bulk (TMA)
+    int dbg;                                    // RPC_DBG bits (timing experiments only, results are wrong): 1 no arrivals, 2 no counters, 4 no map init, 8 no point prefetch, 16 count probes
     GridDesc gd;
     BatchDesc bd;
     PerturbDesc pd;
@@ -349,7 +352,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         __syncwarp();
     }
     // pull this CTA's point / perturbation tiles of the later iterations into L2 (one bulk prefetch per tile and array)
-    if ((tid & (kTile - 1)) == 0) {
+    if ((tid & (kTile - 1)) == 0 && !(p.dbg & 8)) {
         for (int it = 1; it < iters; ++it) {
             TileRange tr;
             const int tile = my_range(it, tr);
@@ -419,8 +422,10 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                 load_xyz<C, PERTURB>(p.pts, p.raw, p.pd, idx, x, y, z);
             }
             cell = point_cell(x, y, z, p.gd);
-            if (p.p2v) p.p2v[idx] = -1;
-            if (p.p2s) p.p2s[idx] = -1;
+            if (!(p.dbg & 4)) {
+                if (p.p2v) p.p2v[idx] = -1;
+                if (p.p2s) p.p2s[idx] = -1;
+            }
         }
         if constexpr (kTma) __syncwarp();                            // the stage may be refilled from here on
         if (p.stamps && it == 0) stamp(p, 12);                       // (warp 0: rows loaded, cells known)
@@ -438,7 +443,15 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             // entry always exists -- 1.5 entries per point)
             for (uint32_t probes = 0; probes < size; ++probes) {
                 Entry *e = p.tab + off + pos;
-                const uint4 o = cas_entry(e, mine);
+                if (p.dbg & 16) atomicAdd(&p.hdr->pad, 1u);
+                uint4 o;
+                if (p.dbg & 32) {                                    // experiment: 64-bit CAS on the key, counter read apart
+                    const unsigned long long q = atomicCAS(&e->key, 0ull, mine);
+                    o = make_uint4((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u);
+                    if (q != 0ull && o.y == ck) o.z = __ldcg(&e->cnt);
+                } else {
+                    o = cas_entry(e, mine);
+                }
                 if ((o.x | o.y) == 0u) { cand = true; h = off + pos; break; }
                 if (o.y == ck) {
                     h = off + pos;
@@ -461,7 +474,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             // loser moves on; levels only grow, so a late point whose W is below the LAST level is turned away by
             // one load -- LiDAR null returns all fall into the cell of the origin).  The voxel's P-1 later points
             // are the earliest of arrivals + overflow levels.
-            if (w != 0u && P > 1) {
+            if (w != 0u && P > 1 && !(p.dbg & 1)) {
                 Entry *e = p.tab + h;
                 const uint32_t D = (uint32_t)P - 1u;
                 uint32_t *row = p.lists + (size_t)h * LS;
@@ -496,15 +509,15 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         else if (idx >= 0) p.hslot[idx] = hs;
         // first points so far, per warp: one byte of the tile's word + the group's counter (no return value: RED)
         const uint32_t bal = __ballot_sync(0xFFFFFFFFu, cand);
-        if (wlane == 0 && bal != 0u) {
+        if (wlane == 0 && bal != 0u && !(p.dbg & 2)) {
             const int tl = tile - p.bd.tile_begin[tr.b];
             atomicAdd(p.l0 + tile, (unsigned long long)__popc(bal) << (8 * (wid & 7)));
-            atomicAdd(p.l1 + p.bd.g1_begin[tr.b] + tl / kGrp, __popc(bal));
+            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[tr.b] + tl / kGrp) * kL1Stride, __popc(bal));
         }
         if (disp >= 0) {                                             // the displaced point is not first after all
             const int jl = disp - p.bd.pt_begin[tr.b];
             atomicAdd(p.l0 + p.bd.tile_begin[tr.b] + jl / kTile, ~(1ull << (8 * ((jl >> 5) & 7))) + 1ull);
-            atomicAdd(p.l1 + p.bd.g1_begin[tr.b] + jl / (kTile * kGrp), -1);
+            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[tr.b] + jl / (kTile * kGrp)) * kL1Stride, -1);
         }
         if (p.stamps && it < 4) stamp(p, 8 + it);                    // (warp 0's pace through the iterations)
     }
@@ -520,10 +533,10 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         const int per = (p.ng1 + kPT - 1) / kPT;
         const int j0 = tid * per, j1 = min(j0 + per, p.ng1);
         int s = 0;
-        for (int j = j0; j < j1; ++j) s += __ldcg(p.l1 + j);
+        for (int j = j0; j < j1; ++j) s += __ldcg(p.l1 + (size_t)j * kL1Stride);
         int tot;
         int run = block_excl_scan<kPT>(s, sm, &tot);
-        for (int j = j0; j < j1; ++j) { s_E[j] = run; run += __ldcg(p.l1 + j); }
+        for (int j = j0; j < j1; ++j) { s_E[j] = run; run += __ldcg(p.l1 + (size_t)j * kL1Stride); }
         if (tid == kPT - 1) s_E[p.ng1] = tot;
         __syncthreads();
         if (tid == 0) {
@@ -678,7 +691,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     __syncthreads();
     if (s_flag) {
         for (int j = tid; j < p.ntiles; j += kPT) p.l0[j] = 0ull;
-        for (int j = tid; j < p.ng1; j += kPT) p.l1[j] = 0;
+        for (int j = tid; j < p.ng1; j += kPT) p.l1[(size_t)j * kL1Stride] = 0;
         if (tid == 0) {
             unsigned long long chi = p.front_end;
             if (was_clean) chi = __ldcg(&p.hdr->clean_hi);

@@ -64,5 +64,6 @@ itend = st[:, 8:12] - st[:, 1:2]
 print("insert iteration ends (warp 0), median over CTAs:", np.round(np.median(itend, axis=0), 2), "max", np.round(itend.max(axis=0), 2))
 sub = st[:, 12:15] - st[:, 1:2]
 print("iteration 0 of warp 0 (rows+cells / probes / arrivals done), median:", np.round(np.median(sub, axis=0), 2), "max", np.round(sub.max(axis=0), 2))
+print("probes counted (RPC_DBG=16), per call:", int(ws[28:32].view(torch.int32).item()) / 5.0, "points", sum(n))
 print("CTAs that found the workspace clean:", int(raw_st[:, 15].sum()), "of", NC)
 print("end", st[:, 6].max(), "dist", dist, "voxels", int(out.voxel_num[-1]), "kept", int((out.point2voxel >= 0).sum()))
