@@ -201,11 +201,10 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
                 size_t workspace_bytes, cudaStream_t st)
 {
     FwdParams fp;
-    // shared memory: entry words of the first kHsCache iterations, then the TMA row stages of phase A (C == 4),
-    // reused by the group prefix of phase B
+    // shared memory: the TMA row stages of phase A (C == 4), reused by the group prefix of phase B
     const size_t stage_bytes = C == 4 ? (size_t)2 * kSub * (raw ? 2 : 1) * kTile * 16 : 0;
     const size_t scan_bytes = 4 * (size_t)(pl.ng1 + 1);
-    const size_t smem = (size_t)kHsCache * kPT * 4 + (stage_bytes > scan_bytes ? stage_bytes : scan_bytes);
+    const size_t smem = stage_bytes > scan_bytes ? stage_bytes : scan_bytes;
     char *w = static_cast<char *>(workspace);
     const size_t back_off = (workspace_bytes - pl.back_bytes) & ~size_t(255);
     fp.pts = points; fp.raw = raw;
@@ -224,7 +223,7 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     fp.ntiles = (int)pl.ntiles; fp.ng1 = (int)pl.ng1; fp.LS = pl.LS;
     {
         static int pf = -1;                                         // RPC_TABLE_PREFETCH=0|1|2 (kernel experiments)
-        if (pf < 0) { const char *e = getenv("RPC_TABLE_PREFETCH"); pf = e ? atoi(e) : 1; }
+        if (pf < 0) { const char *e = getenv("RPC_TABLE_PREFETCH"); pf = e ? atoi(e) : 0; }
         fp.pf_mode = pf;
         static int dbg = -1;
         if (dbg < 0) { const char *e = getenv("RPC_DBG"); dbg = e ? atoi(e) : 0; }

@@ -54,8 +54,6 @@ constexpr int kGrp = 32;                        // tiles per counter group (8192
 constexpr int kMaxGroups = 8192;                // group counters are scanned in shared memory (32 KB)
 constexpr int kL1Stride = 64;                   // ints between two group counters: 256 bytes, so that the REDs of one
                                                 // iteration (256 per counter) spread over L2 slices instead of one line
-constexpr int kTrCache = 128;                   // tile ranges cached in shared memory per CTA (2 KB)
-constexpr int kHsCache = 8;                     // iterations whose per-point entry word stays in shared memory
 constexpr uint32_t kWBase = 0x40000000u;        // level value of point i: kWBase - i  (> 0, larger = earlier)
 constexpr unsigned long long kWsMagic = 0x325F4E4C43325052ull;   // "RP2CLN_2"
 constexpr size_t kWsHeaderBytes = 256;
@@ -72,7 +70,8 @@ struct WsHeader {
     unsigned long long clean_hi;                // byte offset: [clean_lo, clean_hi) is zero between calls
     unsigned long long ws_bytes;                // size the header was written for (the dirty tail sits at the end)
     unsigned int done;                          // CTAs that finished phase B (reset by the last one)
-    unsigned int pad;
+    unsigned int pad;                           // (probe counter of the RPC_DBG=16 experiment)
+    unsigned int next_a, next_b;                // tile counters of the two phases (reset by the last CTA)
 };
 
 struct FwdParams {
@@ -90,7 +89,7 @@ struct FwdParams {
     unsigned long long clean_lo, front_end, back_off, ws_bytes;
     int ntiles, ng1, LS;
     int pf_mode;                                // table prefetch: 0 none, 1 per line, 2 bulk (TMA)
-    int dbg;                                    // RPC_DBG bits (timing experiments only, results are wrong): 1 no arrivals, 2 no counters, 4 no map init, 8 no point prefetch, 16 count probes
+    int dbg;                                    // RPC_DBG bits (timing experiments; 1-4 give wrong results): 1 no arrivals, 2 no counters, 4 no map init, 8 no point prefetch, 16 count probes, 64 per-tile records, 256 plain (not evict_last) entry zeroing
     GridDesc gd;
     BatchDesc bd;
     PerturbDesc pd;
@@ -175,20 +174,6 @@ __device__ __forceinline__ uint32_t probe_start(uint32_t cell, uint32_t size)
     return __umulhi(h, size);
 }
 
-// Tiles are dealt round-robin: CTA c owns tiles c, c + G, c + 2G, ... (G = gridDim.x) and works on kSub of
-// them per iteration, one per group of 8 warps, thread order = point order inside the tile.  With 256-point
-// tiles every CTA gets the same number of tiles to within one.
-__device__ __forceinline__ int cta_iterations(int ntiles)
-{
-    const int mine = (int)blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
-    return (mine + kSub - 1) / kSub;
-}
-__device__ __forceinline__ int my_tile(int ntiles, int it)
-{
-    const int t = (int)blockIdx.x + (it * kSub + (int)(threadIdx.x >> 8)) * (int)gridDim.x;
-    return t < ntiles ? t : -1;
-}
-
 // sum of the 8 per-warp byte counts of a tile (each <= 32)
 __device__ __forceinline__ int tile_first_points(unsigned long long w8)
 {
@@ -242,6 +227,24 @@ __device__ __forceinline__ void bulk_prefetch_l2(const void *ptr, uint32_t bytes
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes) : "memory");
 }
 
+// The table lives in L2 ACROSS calls: the store that zeroes an entry at the end of a call carries an L2::evict_last
+// cache policy, so whatever runs between two calls (bench.py overwrites 512 MiB) evicts other lines first and the
+// next call's atomics hit L2 instead of fetching a 32-byte sector from DRAM each (tools/micro/atomics4.cu: 313 k
+// CASes 9.2 us warm, 14.4 us cold, 10.2 us after an overwrite when the zeroing stores carried the policy; ptxas
+// rejects the hint on atom itself).  17 MB (KITTI batch) / 29 MB (nuScenes) of the 126 MB L2.
+__device__ __forceinline__ void st_zero16_keep(void *ptr)
+{
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%1,%1,%1}, %2;" ::"l"(ptr), "r"(0u), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_zero4_keep(void *ptr)
+{
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(ptr), "r"(0u), "l"(pol) : "memory");
+}
+
 __device__ __forceinline__ uint4 ld_entry(const Entry *e)
 {
     uint4 v;
@@ -263,24 +266,42 @@ __device__ __forceinline__ void warp_zero_fill(float *out, int n, int lane)
     for (int q = head + (n4 << 2) + lane; q < n; q += 32) out[q] = 0.0f;
 }
 
+// (b, first point, end, tile) of a tile, or tile = -1 past the end
+__device__ __forceinline__ int4 pack_range(const FwdParams &p, int tile)
+{
+    if (tile < 0 || tile >= p.ntiles) return make_int4(0, 0, 0, -1);
+    const TileRange tr = tile_range(p, tile);
+    return make_int4(tr.b, tr.begin, tr.end, tile);
+}
+
+// barrier of one team (the 8 warps = 256 threads that work on one tile); ids 1..kSub, 0 is __syncthreads
+__device__ __forceinline__ void team_sync(int team)
+{
+    switch (team) {                                                  // immediate ids: only five barriers are reserved
+        case 0: asm volatile("bar.sync 1, 256;" ::: "memory"); break;
+        case 1: asm volatile("bar.sync 2, 256;" ::: "memory"); break;
+        case 2: asm volatile("bar.sync 3, 256;" ::: "memory"); break;
+        default: asm volatile("bar.sync 4, 256;" ::: "memory"); break;
+    }
+}
+
 template <int C, bool PERTURB>
 __global__ void __launch_bounds__(kPT, kCtasPerSM)
 k_hard_fwd(const __grid_constant__ FwdParams p)
 {
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ __align__(16) unsigned char dyn_sm[];     // [hs cache | A: TMA stages / B: group prefix]
+    extern __shared__ __align__(16) unsigned char dyn_sm[];     // A: TMA stages / B: group prefix
     __shared__ int sm[33];
     __shared__ int s_voff[RPC_MAX_BATCH + 1];                   // first voxel row of each sweep, then M
     __shared__ int s_base[RPC_MAX_BATCH];                       // first points in the groups before the sweep's first
     __shared__ __align__(8) unsigned long long s_bar[2 * (kPT / 32)];   // A (C == 4): one mbarrier per warp and stage
-    __shared__ int4 s_tr[kTrCache];
+    __shared__ int4 s_tile[2][kSub];                            // the tile every team takes next (published by its leader)
     __shared__ int s_flag;
     const int tid = threadIdx.x;
     const int P = p.gd.P, V = p.gd.V, LS = p.LS;
     const int nct = gridDim.x;
     const int wlane = tid & 31, wid = tid >> 5;
-    uint32_t *s_hs = reinterpret_cast<uint32_t *>(dyn_sm);                       // [kHsCache][kPT]
-    unsigned char *dyn2 = dyn_sm + (size_t)kHsCache * kPT * sizeof(uint32_t);
+    const int team = tid >> 8, tl = tid & (kTile - 1);           // a team = 8 warps = one tile at a time
 
     stamp(p, 0);
     if (p.stamps && threadIdx.x == 0) {
@@ -288,52 +309,32 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
         p.stamps[blockIdx.x * 16 + 7] = smid;
     }
-    const int iters = cta_iterations(p.ntiles);
     // is the workspace clean (all-zero table, rows, lists and counters, left so by the previous call)?
     if (tid == 0) {
         const unsigned long long *h = reinterpret_cast<const unsigned long long *>(p.hdr);
         const unsigned long long magic = __ldcg(h), chi = __ldcg(h + 1), wsb = __ldcg(h + 2);
         s_flag = (magic == kWsMagic && wsb == p.ws_bytes && chi >= p.front_end) ? 1 : 0;
     }
-    // the (sweep, first, end) of this CTA's tiles, looked up once: both phases walk the same tiles
-    if (tid < kTrCache && tid < iters * kSub) {
-        const int tile = (int)blockIdx.x + tid * nct;
-        int4 v = make_int4(0, 0, 0, -1);
-        if (tile < p.ntiles) {
-            const TileRange tr = tile_range(p, tile);
-            v = make_int4(tr.b, tr.begin, tr.end, tile);
-        }
-        s_tr[tid] = v;
-    }
+    // Tiles are handed out dynamically: a team's first two tiles are fixed (team t of CTA c starts with tiles
+    // c + t * G and c + (t + 4) * G), every further one comes from a global counter that the team's leader
+    // increments one iteration ahead.  Tiles differ by 6x in cost (an in-range tile waits for its atomics, an
+    // out-of-range one does not), so a static deal left most CTAs waiting at the barrier for the slowest.
+    int4 cur = pack_range(p, (int)blockIdx.x + team * nct);
     __syncthreads();
     const bool was_clean = s_flag != 0;
     if (p.stamps && tid == 0) p.stamps[blockIdx.x * 16 + 15] = was_clean ? 1ull : 0ull;
-    auto my_range = [&](int it, TileRange &tr) -> int {              // -> tile index or -1
-        const int k = it * kSub + (tid >> 8);
-        if (k < kTrCache) {
-            const int4 v = s_tr[k];
-            tr.b = v.x; tr.begin = v.y; tr.end = v.z;
-            return v.w;
-        }
-        const int tile = my_tile(p.ntiles, it);
-        if (tile >= 0) tr = tile_range(p, tile);
-        return tile;
-    };
-    // (the staging pipeline of phase A is set up here, and the rows of iteration 0 are requested first thing)
+    // (the staging pipeline of phase A is set up here, and the rows of the first tile are requested first thing)
     constexpr bool kTma = (C == 4);
     constexpr int kArr = PERTURB ? 2 : 1;                            // arrays staged per warp
     const uint32_t bar_sa = (uint32_t)__cvta_generic_to_shared(s_bar) + 8u * wid;          // + 8 * 32 * stage
-    const uint32_t stage_sa = (uint32_t)__cvta_generic_to_shared(dyn2) + (uint32_t)(wid * kArr * 512);   // + stage
+    const uint32_t stage_sa = (uint32_t)__cvta_generic_to_shared(dyn_sm) + (uint32_t)(wid * kArr * 512);   // + stage
     constexpr uint32_t kStageBytes = (kPT / 32) * kArr * 512;
-    auto issue_rows = [&](int it) {                                  // called by lane 0
-        const int st = it & 1;
-        TileRange tr;
-        const int tile = my_range(it, tr);
+    auto issue_rows = [&](const int4 &t, int st) {                   // called by lane 0 of every warp
         const uint32_t bar = bar_sa + 8u * (kPT / 32) * st;
         int r0 = 0, r1 = 0;
-        if (tile >= 0) {
-            r0 = tr.begin + (wid & 7) * 32;
-            r1 = min(r0 + 32, tr.end);
+        if (t.w >= 0) {
+            r0 = t.y + (wid & 7) * 32;
+            r1 = min(r0 + 32, t.z);
         }
         if (r1 <= r0) { mbar_arrive(bar); return; }
         const uint32_t bytes = (uint32_t)(r1 - r0) * 16u;
@@ -347,24 +348,13 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             mbar_init(bar_sa, 1);
             mbar_init(bar_sa + 8u * (kPT / 32), 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            if (iters > 0) issue_rows(0);
+            issue_rows(cur, 0);
         }
         __syncwarp();
     }
-    // pull this CTA's point / perturbation tiles of the later iterations into L2 (one bulk prefetch per tile and array)
-    if ((tid & (kTile - 1)) == 0 && !(p.dbg & 8)) {
-        for (int it = 1; it < iters; ++it) {
-            TileRange tr;
-            const int tile = my_range(it, tr);
-            if (tile < 0) continue;
-            const size_t b0 = ((size_t)tr.begin * C * 4) & ~size_t(15), b1 = ((size_t)tr.end * C * 4 + 15) & ~size_t(15);
-            bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
-            if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
-        }
-    }
     if (was_clean) {
-        // the table is all-zero but, after whatever ran since the last call, probably not in L2 (experiment knob:
-        // a streaming prefetch of the table did not pay in tools/micro/atomics2.cu, so the default is none)
+        // (experiment knob: stream the table into L2 while the first rows travel; off by default, the table stays
+        // L2-resident across calls through the evict_last policy of the stores that zero it)
         if (p.pf_mode == 1) {
             const char *t = reinterpret_cast<const char *>(p.tab);
             const long long nl = (p.tab_total * (long long)sizeof(Entry) + 127) >> 7;
@@ -383,32 +373,42 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         const long long n4 = (long long)((p.front_end - p.clean_lo) >> 4);
         for (long long i = (long long)blockIdx.x * kPT + tid; i < n4; i += (long long)nct * kPT)
             z[i] = make_uint4(0u, 0u, 0u, 0u);
-        if (blockIdx.x == 0 && tid == 0) p.hdr->done = 0;
+        if (blockIdx.x == 0 && tid == 0) { p.hdr->done = 0u; p.hdr->next_a = 0u; p.hdr->next_b = 0u; }
         grid.sync();
     }
     stamp(p, 1);
 
     // ------------------------------------------------------------------------------- A insert
-    for (int it = 0; it < iters; ++it) {
-        TileRange tr;
-        const int tile = my_range(it, tr);
-        int idx = -1, cell = -1;
-        uint32_t off = 0, size = 1;
-        if (tile >= 0) {
-            if (tr.begin + (tid & (kTile - 1)) < tr.end) {
-                idx = tr.begin + (tid & (kTile - 1));
-                off = p.bd.tab_off[tr.b]; size = p.bd.tab_size[tr.b];
+    unsigned int g_next = 0;                                         // (leader) the grab of the previous iteration
+    for (int it = 0;; ++it) {
+        // a team's first two tiles are fixed, the third and later come from the counter (grabbed one iteration ahead)
+        if (tl == 0)
+            s_tile[it & 1][team] = pack_range(p, it == 0 ? (int)blockIdx.x + (team + kSub) * nct : 2 * kSub * nct + (int)g_next);
+        team_sync(team);
+        if (cur.w < 0) break;                                        // (the same for the whole team)
+        const int4 nxt = s_tile[it & 1][team];
+        if (nxt.w >= 0) {
+            if (tl == 0) g_next = atomicAdd(&p.hdr->next_a, 1u);     // the tile after next: back before it is needed
+            if constexpr (kTma) {
+                // every lane of this warp is past its reads of the other stage (__syncwarp below): refill it
+                if (wlane == 0) issue_rows(nxt, (it + 1) & 1);
+            } else if (tl == 0 && !(p.dbg & 8)) {
+                const size_t b0 = ((size_t)nxt.y * C * 4) & ~size_t(15), b1 = ((size_t)nxt.z * C * 4 + 15) & ~size_t(15);
+                bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
+                if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
             }
         }
-        if constexpr (kTma) {
-            // every lane is past its reads of the other stage (__syncwarp at the end of the iteration): refill it
-            if (wlane == 0 && it + 1 < iters) issue_rows(it + 1);
-            mbar_wait(bar_sa + 8u * (kPT / 32) * (it & 1), (uint32_t)(it >> 1) & 1u);
-        }
+        const int tile = cur.w, sb = cur.x;
+        const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
+        int cell = -1;
+        const uint32_t off = p.bd.tab_off[sb], size = p.bd.tab_size[sb];
+        unsigned long long t_tile0 = 0;
+        if (p.stamps && (p.dbg & 64) && tl == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_tile0));
+        if constexpr (kTma) mbar_wait(bar_sa + 8u * (kPT / 32) * (it & 1), (uint32_t)(it >> 1) & 1u);
         if (idx >= 0) {
             float x, y, z;
             if constexpr (kTma) {
-                const float4 *sp = reinterpret_cast<const float4 *>(dyn2) +
+                const float4 *sp = reinterpret_cast<const float4 *>(dyn_sm) +
                                    ((it & 1) * (kPT / 32) + wid) * kArr * 32 + wlane;
                 const float4 v = sp[0];
                 x = v.x; y = v.y; z = v.z;
@@ -428,7 +428,6 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             }
         }
         if constexpr (kTma) __syncwarp();                            // the stage may be refilled from here on
-        if (p.stamps && it == 0) stamp(p, 12);                       // (warp 0: rows loaded, cells known)
         // claim / find the cell's entry: blind 16-byte CAS along the linear probe order (at LiDAR load factors ~0.3
         // the home entry is free or already the cell's own for most points: one L2 round trip)
         bool cand = false;                                           // first point of the cell so far
@@ -444,14 +443,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             for (uint32_t probes = 0; probes < size; ++probes) {
                 Entry *e = p.tab + off + pos;
                 if (p.dbg & 16) atomicAdd(&p.hdr->pad, 1u);
-                uint4 o;
-                if (p.dbg & 32) {                                    // experiment: 64-bit CAS on the key, counter read apart
-                    const unsigned long long q = atomicCAS(&e->key, 0ull, mine);
-                    o = make_uint4((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u);
-                    if (q != 0ull && o.y == ck) o.z = __ldcg(&e->cnt);
-                } else {
-                    o = cas_entry(e, mine);
-                }
+                const uint4 o = cas_entry(e, mine);
                 if ((o.x | o.y) == 0u) { cand = true; h = off + pos; break; }
                 if (o.y == ck) {
                     h = off + pos;
@@ -466,7 +458,6 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                 }
                 pos = pos + 1 == size ? 0u : pos + 1;
             }
-            if (p.stamps && it == 0) stamp(p, 13);                   // (warp 0: probes done)
             // A point that is not the first of its cell ARRIVES: it takes the next of the cell's P-1 arrival slots
             // (one atomicAdd on the entry's counter, one plain store) -- unordered; the first point sorts them when
             // it emits the voxel.  Only a cell with more than P points overflows: arrival P-1 and later compete for
@@ -503,23 +494,29 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                 }
             }
         }
-        if (p.stamps && it == 0) stamp(p, 14);                       // (warp 0: arrivals done)
-        const uint32_t hs = cand ? h + 1u : 0u;
-        if (it < kHsCache) s_hs[it * kPT + tid] = hs;
-        else if (idx >= 0) p.hslot[idx] = hs;
+        if (idx >= 0) p.hslot[idx] = cand ? h + 1u : 0u;
         // first points so far, per warp: one byte of the tile's word + the group's counter (no return value: RED)
         const uint32_t bal = __ballot_sync(0xFFFFFFFFu, cand);
         if (wlane == 0 && bal != 0u && !(p.dbg & 2)) {
-            const int tl = tile - p.bd.tile_begin[tr.b];
+            const int tt = tile - p.bd.tile_begin[sb];
             atomicAdd(p.l0 + tile, (unsigned long long)__popc(bal) << (8 * (wid & 7)));
-            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[tr.b] + tl / kGrp) * kL1Stride, __popc(bal));
+            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[sb] + tt / kGrp) * kL1Stride, __popc(bal));
         }
         if (disp >= 0) {                                             // the displaced point is not first after all
-            const int jl = disp - p.bd.pt_begin[tr.b];
-            atomicAdd(p.l0 + p.bd.tile_begin[tr.b] + jl / kTile, ~(1ull << (8 * ((jl >> 5) & 7))) + 1ull);
-            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[tr.b] + jl / (kTile * kGrp)) * kL1Stride, -1);
+            const int jl = disp - p.bd.pt_begin[sb];
+            atomicAdd(p.l0 + p.bd.tile_begin[sb] + jl / kTile, ~(1ull << (8 * ((jl >> 5) & 7))) + 1ull);
+            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[sb] + jl / (kTile * kGrp)) * kL1Stride, -1);
         }
-        if (p.stamps && it < 4) stamp(p, 8 + it);                    // (warp 0's pace through the iterations)
+        if (p.stamps && (p.dbg & 64)) {                              // per-tile record: start, end (warp 0 of the team), in-range points of warp 0
+            const uint32_t inr = __ballot_sync(0xFFFFFFFFu, cell >= 0);
+            if (tl == 0 && tile < 5000) {
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+                unsigned long long *rec = p.stamps + 16 * 296 + 3 * (size_t)tile;
+                rec[0] = t_tile0; rec[1] = t1; rec[2] = ((unsigned long long)blockIdx.x << 32) | (unsigned)__popc(inr);
+            }
+        }
+        cur = nxt;
     }
     if (p.stamps) __syncthreads();
     stamp(p, 2);
@@ -528,7 +525,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
 
     // ------------------------------------------------------------------------------- B emit
     // exclusive scan of the group counters (first points in the groups before g), every CTA for itself
-    int *s_E = reinterpret_cast<int *>(dyn2);
+    int *s_E = reinterpret_cast<int *>(dyn_sm);
     {
         const int per = (p.ng1 + kPT - 1) / kPT;
         const int j0 = tid * per, j1 = min(j0 + per, p.ng1);
@@ -557,129 +554,139 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 4);
     const int F = p.gd.F;
     const int PC = P * C;
-    for (int it = 0; it < iters; ++it) {
-        TileRange tr;
-        const int tile = my_range(it, tr);
-        int idx = -1;
-        uint32_t hs = 0;
-        if (tile >= 0 && tr.begin + (tid & (kTile - 1)) < tr.end) {
-            idx = tr.begin + (tid & (kTile - 1));
-            hs = it < kHsCache ? s_hs[it * kPT + tid] : __ldcg(p.hslot + idx);
-        }
+    cur = pack_range(p, (int)blockIdx.x + team * nct);
+    uint32_t hs = (cur.w >= 0 && cur.y + tl < cur.z) ? __ldcg(p.hslot + cur.y + tl) : 0u;
+    for (int it = 0;; ++it) {
+        if (tl == 0)
+            s_tile[it & 1][team] = pack_range(p, it == 0 ? (int)blockIdx.x + (team + kSub) * nct : 2 * kSub * nct + (int)g_next);
+        team_sync(team);
+        if (cur.w < 0) break;
+        const int4 nxt = s_tile[it & 1][team];
+        if (nxt.w >= 0 && tl == 0) g_next = atomicAdd(&p.hdr->next_b, 1u);
+        // the next tile's entry words travel while this one is emitted
+        const uint32_t hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
+        const int tile = cur.w, sb = cur.x;
+        const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
         const uint32_t wc = __ballot_sync(0xFFFFFFFFu, hs != 0u);
-        if (tile < 0 || wc == 0u) continue;                          // warp-uniform: no candidate, no first point
-        // every load of the iteration is issued before the first one is waited for: the candidate's entry, its own
-        // row, the tile's counter word and those of the earlier tiles of the group -- ONE round trip
-        const int tl = tile - p.bd.tile_begin[tr.b];
-        const int tg = tl & (kGrp - 1);
-        uint4 ev = make_uint4(0u, 0u, 0u, 0u);
-        Entry *e = p.tab + (hs - 1u);
-        if (hs != 0u) ev = ld_entry(e);
-        const unsigned long long w8 = __ldcg(p.l0 + tile);
-        const unsigned long long g8 = wlane < tg ? __ldcg(p.l0 + tile - tg + wlane) : 0ull;
-        float x[C];
-        if (hs != 0u) load_row<C, PERTURB>(p, idx, x);
-        // candidates look at their entry again: still theirs -> first point of the cell, and the entry is zeroed
-        // for the next call right away (a displaced candidate that reads the zero is not first either way)
-        const bool f = hs != 0u && (ev.x | ev.y) != 0u && ev.x == (uint32_t)idx;
-        if (f) __stcg(reinterpret_cast<uint4 *>(e), make_uint4(0u, 0u, 0u, 0u));
-        const uint32_t wf = __ballot_sync(0xFFFFFFFFu, f);
-        if (wf == 0u) continue;                                      // warp-uniform
-        // voxel index of the warp's first first point inside the sweep = first points of: earlier groups (shared
-        // memory), earlier tiles of this group (one 8-byte load per lane), earlier warps of this tile (its word)
-        int pre_w;
-        {
-            int s = tile_first_points(g8);
+        if (wc != 0u) {                                              // warp-uniform: a candidate in this warp
+            // every load of the iteration is issued before the first one is waited for: the candidate's entry, its
+            // own row, the tile's counter word and those of the earlier tiles of the group -- ONE round trip
+            const int tt = tile - p.bd.tile_begin[sb];
+            const int tg = tt & (kGrp - 1);
+            uint4 ev = make_uint4(0u, 0u, 0u, 0u);
+            Entry *e = p.tab + (hs - 1u);
+            if (hs != 0u) ev = ld_entry(e);
+            const unsigned long long w8 = __ldcg(p.l0 + tile);
+            const unsigned long long g8 = wlane < tg ? __ldcg(p.l0 + tile - tg + wlane) : 0ull;
+            float x[C];
+            if (hs != 0u) load_row<C, PERTURB>(p, idx, x);
+            // candidates look at their entry again: still theirs -> first point of the cell, and the entry is zeroed
+            // for the next call right away (a displaced candidate that reads the zero is not first either way)
+            const bool f = hs != 0u && (ev.x | ev.y) != 0u && ev.x == (uint32_t)idx;
+            if (f) { if (p.dbg & 256) __stcg(reinterpret_cast<uint4 *>(e), make_uint4(0u, 0u, 0u, 0u)); else st_zero16_keep(e); }
+            const uint32_t wf = __ballot_sync(0xFFFFFFFFu, f);
+            if (wf != 0u) {                                          // warp-uniform: a first point in this warp
+                // voxel index of the warp's first first point inside the sweep = first points of: earlier groups
+                // (shared memory), earlier tiles of this group (one 8-byte load per lane), earlier warps of this
+                // tile (its word)
+                int pre_w;
+                {
+                    int s = tile_first_points(g8);
 #pragma unroll
-            for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, d);
-            pre_w = s_E[p.bd.g1_begin[tr.b] + tl / kGrp] - s_base[tr.b] + s +
-                    tile_first_points(w8 & ((1ull << (8 * (wid & 7))) - 1ull));
-        }
-        const int pre = pre_w + __popc(wf & ((1u << wlane) - 1u));
-        const bool kept = f && pre < V;                              // cells first seen after V voxels are refused
-        const int voff = s_voff[tr.b];
-        const uint32_t wk = __ballot_sync(0xFFFFFFFFu, kept);
-        // the cell's later points: min(cnt, P-1) arrivals (slot0 in the entry, the rest in its row) and, for a cell
-        // with more than P points, the levels of its overflow list
-        const uint32_t D = (uint32_t)P - 1u;
-        const uint32_t m = f ? (ev.z < D ? ev.z : D) : 0u;
-        uint32_t *row = p.lists + (size_t)(hs - 1u) * LS;            // (only dereferenced by first points)
-        uint32_t *L = nullptr;
-        if (f && P > 1 && ev.z >= D) {
-            const uint32_t lp = __ldcg(row + D - 1u);
-            if (lp != 0u) { L = p.ovf + (size_t)(lp - 1u) * LS; __stcg(row + D - 1u, 0u); }
-        }
-        if (wk != 0u) {
-            // the warp's kept voxels are the rows [voff + pre_w, + popc(wk)): zero them with coalesced stores, then
-            // (after __syncwarp, which orders the stores of the participating lanes) every first point fills its row
-            warp_zero_fill(p.voxels + (size_t)(voff + pre_w) * PC, __popc(wk) * PC, wlane);
-            __syncwarp();
-        }
-        if (kept) {
-            const long long v = voff + pre;
-            float *vrow = p.voxels + v * PC;
-            float sum[C];
-            if constexpr (C == 4) {
-                reinterpret_cast<float4 *>(vrow)[0] = make_float4(x[0], x[1], x[2], x[3]);
-            } else {
-#pragma unroll
-                for (int c = 0; c < C; ++c) vrow[c] = x[c];
-            }
-#pragma unroll
-            for (int c = 0; c < C; ++c) sum[c] = x[c];               // 0 + x == x: the oracle's sum starts at 0.0f
-            const int cx = axis_cell(x[0], p.gd, 0), cy = axis_cell(x[1], p.gd, 1), cz = axis_cell(x[2], p.gd, 2);
-            if (p.p2v) p.p2v[idx] = (int)v;
-            if (p.p2s) p.p2s[idx] = 0;
-            int n = 1;
-            uint32_t prev = 0xFFFFFFFFu;                             // slot q takes the largest W below slot q-1's
-            for (int q = 1; q < P; ++q) {
-                uint32_t best = 0u;
-                if (m >= 1u && ev.w < prev) best = ev.w;
-                for (uint32_t j = 0; j + 1u < m; ++j) {
-                    const uint32_t t = __ldcg(row + j);
-                    if (t < prev && t > best) best = t;
+                    for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, d);
+                    pre_w = s_E[p.bd.g1_begin[sb] + tt / kGrp] - s_base[sb] + s +
+                            tile_first_points(w8 & ((1ull << (8 * (wid & 7))) - 1ull));
                 }
-                if (L) {
-                    for (uint32_t j = 0; j < D; ++j) {               // (sorted: the first one below prev is the largest)
-                        const uint32_t t = __ldcg(L + j);
-                        if (t < prev) { if (t > best) best = t; break; }
+                const int pre = pre_w + __popc(wf & ((1u << wlane) - 1u));
+                const bool kept = f && pre < V;                      // cells first seen after V voxels are refused
+                const int voff = s_voff[sb];
+                const uint32_t wk = __ballot_sync(0xFFFFFFFFu, kept);
+                // the cell's later points: min(cnt, P-1) arrivals (slot0 in the entry, the rest in its row) and, for
+                // a cell with more than P points, the levels of its overflow list
+                const uint32_t D = (uint32_t)P - 1u;
+                const uint32_t m = f ? (ev.z < D ? ev.z : D) : 0u;
+                uint32_t *row = p.lists + (size_t)(hs - 1u) * LS;    // (only dereferenced by first points)
+                uint32_t *L = nullptr;
+                if (f && P > 1 && ev.z >= D) {
+                    const uint32_t lp = __ldcg(row + D - 1u);
+                    if (lp != 0u) { L = p.ovf + (size_t)(lp - 1u) * LS; __stcg(row + D - 1u, 0u); }
+                }
+                if (wk != 0u) {
+                    // the warp's kept voxels are the rows [voff + pre_w, + popc(wk)): zero them with coalesced stores,
+                    // then (after __syncwarp, which orders the stores of the participating lanes) every first point
+                    // fills its row
+                    warp_zero_fill(p.voxels + (size_t)(voff + pre_w) * PC, __popc(wk) * PC, wlane);
+                    __syncwarp();
+                }
+                if (kept) {
+                    const long long v = voff + pre;
+                    float *vrow = p.voxels + v * PC;
+                    float sum[C];
+                    if constexpr (C == 4) {
+                        reinterpret_cast<float4 *>(vrow)[0] = make_float4(x[0], x[1], x[2], x[3]);
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) vrow[c] = x[c];
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; ++c) sum[c] = x[c];       // 0 + x == x: the oracle's sum starts at 0.0f
+                    const int cx = axis_cell(x[0], p.gd, 0), cy = axis_cell(x[1], p.gd, 1), cz = axis_cell(x[2], p.gd, 2);
+                    if (p.p2v) p.p2v[idx] = (int)v;
+                    if (p.p2s) p.p2s[idx] = 0;
+                    int n = 1;
+                    uint32_t prev = 0xFFFFFFFFu;                     // slot q takes the largest W below slot q-1's
+                    for (int q = 1; q < P; ++q) {
+                        uint32_t best = 0u;
+                        if (m >= 1u && ev.w < prev) best = ev.w;
+                        for (uint32_t j = 0; j + 1u < m; ++j) {
+                            const uint32_t t = __ldcg(row + j);
+                            if (t < prev && t > best) best = t;
+                        }
+                        if (L) {
+                            for (uint32_t j = 0; j < D; ++j) {       // (sorted: the first one below prev is the largest)
+                                const uint32_t t = __ldcg(L + j);
+                                if (t < prev) { if (t > best) best = t; break; }
+                            }
+                        }
+                        if (best == 0u) break;
+                        prev = best;
+                        const int i2 = (int)(kWBase - best);
+                        load_row<C, PERTURB>(p, i2, x);
+                        if constexpr (C == 4) {
+                            reinterpret_cast<float4 *>(vrow)[q] = make_float4(x[0], x[1], x[2], x[3]);
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < C; ++c) vrow[q * C + c] = x[c];
+                        }
+#pragma unroll
+                        for (int c = 0; c < C; ++c) sum[c] = __fadd_rn(sum[c], x[c]);
+                        if (p.p2v) p.p2v[i2] = (int)v;
+                        if (p.p2s) p.p2s[i2] = q;
+                        n = q + 1;
+                    }
+                    p.num_points[v] = n;
+                    reinterpret_cast<int4 *>(p.coors)[v] = make_int4(sb, cz, cy, cx);
+                    if (p.feats) {
+                        const float fn = (float)n;
+#pragma unroll
+                        for (int c = 0; c < C; ++c)
+                            if (c < F) p.feats[v * F + c] = __fdiv_rn(sum[c], fn);
                     }
                 }
-                if (best == 0u) break;
-                prev = best;
-                const int i2 = (int)(kWBase - best);
-                load_row<C, PERTURB>(p, i2, x);
-                if constexpr (C == 4) {
-                    reinterpret_cast<float4 *>(vrow)[q] = make_float4(x[0], x[1], x[2], x[3]);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < C; ++c) vrow[q * C + c] = x[c];
-                }
-#pragma unroll
-                for (int c = 0; c < C; ++c) sum[c] = __fadd_rn(sum[c], x[c]);
-                if (p.p2v) p.p2v[i2] = (int)v;
-                if (p.p2s) p.p2s[i2] = q;
-                n = q + 1;
-            }
-            p.num_points[v] = n;
-            reinterpret_cast<int4 *>(p.coors)[v] = make_int4(tr.b, cz, cy, cx);
-            if (p.feats) {
-                const float fn = (float)n;
-#pragma unroll
-                for (int c = 0; c < C; ++c)
-                    if (c < F) p.feats[v * F + c] = __fdiv_rn(sum[c], fn);
-            }
-        }
-        // kept or refused, the cell's first point leaves the row and the overflow list zero for the next call
-        if (f) {
-            for (uint32_t j = 0; j + 1u < m; ++j) __stcg(row + j, 0u);
-            if (L) {
-                for (uint32_t j = 0; j < D; ++j) {
-                    if (__ldcg(L + j) == 0u) break;
-                    __stcg(L + j, 0u);
+                // kept or refused, the cell's first point leaves the row and the overflow list zero for the next call
+                if (f) {
+                    for (uint32_t j = 0; j + 1u < m; ++j) st_zero4_keep(row + j);
+                    if (L) {
+                        for (uint32_t j = 0; j < D; ++j) {
+                            if (__ldcg(L + j) == 0u) break;
+                            __stcg(L + j, 0u);
+                        }
+                    }
                 }
             }
         }
+        cur = nxt;
+        hs = hs_nxt;
     }
     if (p.stamps) __syncthreads();
     stamp(p, 5);
@@ -698,6 +705,8 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             p.hdr->clean_hi = chi < p.back_off ? chi : p.back_off;
             p.hdr->ws_bytes = p.ws_bytes;
             p.hdr->done = 0u;
+            p.hdr->next_a = 0u;
+            p.hdr->next_b = 0u;
             p.hdr->magic = kWsMagic;
         }
     }

@@ -60,10 +60,24 @@ if os.environ.get("PERSM"):
     for c in range(NC):
         persm.setdefault(int(smid[c]), []).append(ins[c])
     print("insert mean per SM (sm:us): " + " ".join(f"{m}:{np.mean(persm[m]):.0f}" for m in sorted(persm)))
-itend = st[:, 8:12] - st[:, 1:2]
-print("insert iteration ends (warp 0), median over CTAs:", np.round(np.median(itend, axis=0), 2), "max", np.round(itend.max(axis=0), 2))
-sub = st[:, 12:15] - st[:, 1:2]
-print("iteration 0 of warp 0 (rows+cells / probes / arrivals done), median:", np.round(np.median(sub, axis=0), 2), "max", np.round(sub.max(axis=0), 2))
+if int(os.environ.get("RPC_DBG", "0")) & 64:
+    nt = sum((x + 255) // 256 for x in n)
+    rec = ws[off + 8 * 16 * 296: off + 8 * 16 * 296 + 24 * nt].view(torch.int64).cpu().numpy().reshape(nt, 3)
+    t_s = (rec[:, 0] - t0) / 1e3; t_e = (rec[:, 1] - t0) / 1e3; cta = rec[:, 2] >> 32; inr = rec[:, 2] & 0xFFFFFFFF
+    dur = t_e - t_s
+    for lo, hi in ((0, 0), (1, 15), (16, 31), (32, 32)):
+        sel = (inr >= lo) & (inr <= hi)
+        if sel.any():
+            print(f"tiles with {lo}-{hi} in-range points in warp 0: n={sel.sum():5d} dur med {np.median(dur[sel]):6.2f} p90 {np.percentile(dur[sel], 90):6.2f} max {dur[sel].max():6.2f}")
+    order_t = np.argsort(t_s)
+    for a in range(0, nt, max(nt // 12, 1)):
+        sl = order_t[a:a + max(nt // 12, 1)]
+        print(f"  tiles started {t_s[sl].min():6.1f}..{t_s[sl].max():6.1f} us: dur med {np.median(dur[sl]):6.2f} max {dur[sl].max():6.2f}; in-range share {np.mean(inr[sl] > 0):.2f}")
+    persm = {}
+    for i in range(nt):
+        persm.setdefault(int(smid[cta[i]]), []).append(dur[i] if inr[i] > 0 else np.nan)
+    v = np.array([np.nanmedian(persm[k]) if np.isfinite(persm[k]).any() else np.nan for k in sorted(persm)])
+    print("median duration of in-range tiles per SM: min", np.nanmin(v), "med", np.nanmedian(v), "max", np.nanmax(v))
 print("probes counted (RPC_DBG=16), per call:", int(ws[28:32].view(torch.int32).item()) / 5.0, "points", sum(n))
 print("CTAs that found the workspace clean:", int(raw_st[:, 15].sum()), "of", NC)
 print("end", st[:, 6].max(), "dist", dist, "voxels", int(out.voxel_num[-1]), "kept", int((out.point2voxel >= 0).sum()))
