@@ -203,8 +203,13 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     FwdParams fp;
     // shared memory: the TMA row stages of phase A (C == 4), reused by the group prefix of phase B
     const size_t stage_bytes = C == 4 ? (size_t)2 * kSub * (raw ? 2 : 1) * kTile * 16 : 0;
-    const size_t scan_bytes = 4 * (size_t)(pl.ng1 + 1);
-    const size_t smem = stage_bytes > scan_bytes ? stage_bytes : scan_bytes;
+    const size_t scan_words = ((size_t)pl.ng1 + 1 + 3) & ~size_t(3);
+    const int D = gd.P - 1;
+    fp.DS = (D >= 1 && D <= kFastD) ? (D | 1) : 0;                   // odd stride: conflict-free rows of sort scratch
+    fp.scan_words = (int)scan_words;
+    const size_t b_bytes = 4 * (scan_words + (size_t)kPT * fp.DS);
+    const size_t smem = stage_bytes > b_bytes ? stage_bytes : b_bytes;
+    if (smem > 100 * 1024) return RPC_ERR_TOO_LARGE;
     char *w = static_cast<char *>(workspace);
     const size_t back_off = (workspace_bytes - pl.back_bytes) & ~size_t(255);
     fp.pts = points; fp.raw = raw;

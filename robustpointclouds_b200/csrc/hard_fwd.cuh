@@ -54,6 +54,7 @@ constexpr int kGrp = 32;                        // tiles per counter group (8192
 constexpr int kMaxGroups = 8192;                // group counters are scanned in shared memory (32 KB)
 constexpr int kL1Stride = 64;                   // ints between two group counters: 256 bytes, so that the REDs of one
                                                 // iteration (256 per counter) spread over L2 slices instead of one line
+constexpr int kFastD = 15;                      // P-1 up to which a voxel's arrivals are sorted in shared memory
 constexpr uint32_t kWBase = 0x40000000u;        // level value of point i: kWBase - i  (> 0, larger = earlier)
 constexpr unsigned long long kWsMagic = 0x325F4E4C43325052ull;   // "RP2CLN_2"
 constexpr size_t kWsHeaderBytes = 256;
@@ -88,6 +89,8 @@ struct FwdParams {
     long long tab_total;
     unsigned long long clean_lo, front_end, back_off, ws_bytes;
     int ntiles, ng1, LS;
+    int DS;                                     // words of shared-memory sort scratch per thread in phase B (odd, >= P-1), 0: none
+    int scan_words;                             // ints of shared memory in front of the scratch (group prefix)
     int pf_mode;                                // table prefetch: 0 none, 1 per line, 2 bulk (TMA)
     int dbg;                                    // RPC_DBG bits (timing experiments; 1-4 give wrong results): 1 no arrivals, 2 no counters, 4 no map init, 8 no point prefetch, 16 count probes, 64 per-tile records, 256 plain (not evict_last) entry zeroing
     GridDesc gd;
@@ -526,6 +529,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // ------------------------------------------------------------------------------- B emit
     // exclusive scan of the group counters (first points in the groups before g), every CTA for itself
     int *s_E = reinterpret_cast<int *>(dyn_sm);
+    uint32_t *s_sc = reinterpret_cast<uint32_t *>(dyn_sm) + p.scan_words;       // [kPT][DS] per-thread sort scratch
     {
         const int per = (p.ng1 + kPT - 1) / kPT;
         const int j0 = tid * per, j1 = min(j0 + per, p.ng1);
@@ -634,35 +638,71 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                     if (p.p2v) p.p2v[idx] = (int)v;
                     if (p.p2s) p.p2s[idx] = 0;
                     int n = 1;
-                    uint32_t prev = 0xFFFFFFFFu;                     // slot q takes the largest W below slot q-1's
-                    for (int q = 1; q < P; ++q) {
-                        uint32_t best = 0u;
-                        if (m >= 1u && ev.w < prev) best = ev.w;
-                        for (uint32_t j = 0; j + 1u < m; ++j) {
-                            const uint32_t t = __ldcg(row + j);
-                            if (t < prev && t > best) best = t;
+                    if (m > 0u && L == nullptr && D <= (uint32_t)kFastD) {
+                        // the usual cell (at most P points): its arrivals -- slot0 from the entry, the others with
+                        // independent loads from its row -- are sorted by point order in shared memory, then gathered
+                        // with the next point's row in flight while the current one is stored
+                        uint32_t *sc = s_sc + tid * p.DS;
+                        sc[0] = ev.w;
+                        for (uint32_t j = 0; j + 1u < m; ++j) sc[j + 1u] = __ldcg(row + j);
+                        for (uint32_t a = 1; a < m; ++a) {           // insertion sort, largest W (earliest point) first
+                            const uint32_t t = sc[a];
+                            uint32_t b = a;
+                            while (b > 0u && sc[b - 1u] < t) { sc[b] = sc[b - 1u]; --b; }
+                            sc[b] = t;
                         }
-                        if (L) {
-                            for (uint32_t j = 0; j < D; ++j) {       // (sorted: the first one below prev is the largest)
-                                const uint32_t t = __ldcg(L + j);
-                                if (t < prev) { if (t > best) best = t; break; }
+                        float xn[C];
+                        load_row<C, PERTURB>(p, (int)(kWBase - sc[0]), xn);
+                        for (uint32_t q = 1; q <= m; ++q) {
+                            const int i2 = (int)(kWBase - sc[q - 1u]);
+#pragma unroll
+                            for (int c = 0; c < C; ++c) x[c] = xn[c];
+                            if (q < m) load_row<C, PERTURB>(p, (int)(kWBase - sc[q]), xn);
+                            if constexpr (C == 4) {
+                                reinterpret_cast<float4 *>(vrow)[q] = make_float4(x[0], x[1], x[2], x[3]);
+                            } else {
+#pragma unroll
+                                for (int c = 0; c < C; ++c) vrow[q * C + c] = x[c];
                             }
-                        }
-                        if (best == 0u) break;
-                        prev = best;
-                        const int i2 = (int)(kWBase - best);
-                        load_row<C, PERTURB>(p, i2, x);
-                        if constexpr (C == 4) {
-                            reinterpret_cast<float4 *>(vrow)[q] = make_float4(x[0], x[1], x[2], x[3]);
-                        } else {
 #pragma unroll
-                            for (int c = 0; c < C; ++c) vrow[q * C + c] = x[c];
+                            for (int c = 0; c < C; ++c) sum[c] = __fadd_rn(sum[c], x[c]);
+                            if (p.p2v) p.p2v[i2] = (int)v;
+                            if (p.p2s) p.p2s[i2] = (int)q;
                         }
+                        n = 1 + (int)m;
+                    } else if (m > 0u) {
+                        // crowded cell (overflow list) or a very large P: selection straight from global memory --
+                        // slot q takes the largest W below slot q-1's among arrivals and overflow levels
+                        uint32_t prev = 0xFFFFFFFFu;
+                        for (int q = 1; q < P; ++q) {
+                            uint32_t best = 0u;
+                            if (ev.w < prev) best = ev.w;
+                            for (uint32_t j = 0; j + 1u < m; ++j) {
+                                const uint32_t t = __ldcg(row + j);
+                                if (t < prev && t > best) best = t;
+                            }
+                            if (L) {
+                                for (uint32_t j = 0; j < D; ++j) {   // (sorted: the first one below prev is the largest)
+                                    const uint32_t t = __ldcg(L + j);
+                                    if (t < prev) { if (t > best) best = t; break; }
+                                }
+                            }
+                            if (best == 0u) break;
+                            prev = best;
+                            const int i2 = (int)(kWBase - best);
+                            load_row<C, PERTURB>(p, i2, x);
+                            if constexpr (C == 4) {
+                                reinterpret_cast<float4 *>(vrow)[q] = make_float4(x[0], x[1], x[2], x[3]);
+                            } else {
 #pragma unroll
-                        for (int c = 0; c < C; ++c) sum[c] = __fadd_rn(sum[c], x[c]);
-                        if (p.p2v) p.p2v[i2] = (int)v;
-                        if (p.p2s) p.p2s[i2] = q;
-                        n = q + 1;
+                                for (int c = 0; c < C; ++c) vrow[q * C + c] = x[c];
+                            }
+#pragma unroll
+                            for (int c = 0; c < C; ++c) sum[c] = __fadd_rn(sum[c], x[c]);
+                            if (p.p2v) p.p2v[i2] = (int)v;
+                            if (p.p2s) p.p2s[i2] = q;
+                            n = q + 1;
+                        }
                     }
                     p.num_points[v] = n;
                     reinterpret_cast<int4 *>(p.coors)[v] = make_int4(sb, cz, cy, cx);
