@@ -54,11 +54,12 @@ constexpr int kGrp = 32;                        // tiles per counter group (8192
 constexpr int kMaxGroups = 8192;                // group counters are scanned in shared memory (32 KB)
 constexpr int kL1Stride = 64;                   // ints between two group counters: 256 bytes, so that the REDs of one
                                                 // iteration (256 per counter) spread over L2 slices instead of one line
+constexpr int kQCap = 512;                      // queue of in-range points per team: < one round left + one tile pushed
 constexpr int kFastD = 15;                      // P-1 up to which a voxel's arrivals are sorted in shared memory
 constexpr uint32_t kWBase = 0x40000000u;        // level value of point i: kWBase - i  (> 0, larger = earlier)
 constexpr unsigned long long kWsMagic = 0x325F4E4C43325052ull;   // "RP2CLN_2"
 constexpr size_t kWsHeaderBytes = 256;
-constexpr size_t kWsStampBytes = 8 * 16 * 1024;
+constexpr size_t kWsStampBytes = 8 * 16 * 4096;     // per-CTA stamps + per-tile records of the RPC_DBG=64 experiment
 
 struct __align__(16) Entry {
     unsigned long long key;                     // 0 = empty; ((cell + 1) << 32) | index of the first point so far
@@ -277,6 +278,33 @@ __device__ __forceinline__ int4 pack_range(const FwdParams &p, int tile)
     return make_int4(tr.b, tr.begin, tr.end, tile);
 }
 
+// Order in which phase B takes the tiles: round-robin over the sweeps (k-th tile of sweep 0, of sweep 1, ...), so that
+// the tiles at the START of every sweep -- where the cells are first seen, i.e. where the voxels are emitted -- are
+// handed out first and evenly: longest jobs first.  j = 0, 1, 2, ... -> tile (a bijection; ragged sweeps are skipped
+// once they run out).
+__device__ __forceinline__ int emit_order(const FwdParams &p, int j)
+{
+    if (j < 0 || j >= p.ntiles) return -1;
+    const int B = p.bd.B;
+    if (B == 1) return j;
+    // sweeps sorted by tile count would give a closed form; B <= 32, so walk the "layers": layer k holds one tile of
+    // every sweep with more than k tiles.  tmin = smallest sweep: the first tmin layers are full.
+    int tmin = 0x7FFFFFFF;
+    for (int b = 0; b < B; ++b) tmin = min(tmin, p.bd.tile_begin[b + 1] - p.bd.tile_begin[b]);
+    if (j < tmin * B) return p.bd.tile_begin[j % B] + j / B;
+    int left = j - tmin * B;
+    for (int k = tmin;; ++k) {                                       // (ragged tail: rarely more than a few layers)
+        int alive = 0;
+        for (int b = 0; b < B; ++b) alive += (p.bd.tile_begin[b + 1] - p.bd.tile_begin[b]) > k;
+        if (left < alive) {
+            for (int b = 0; b < B; ++b)
+                if ((p.bd.tile_begin[b + 1] - p.bd.tile_begin[b]) > k && left-- == 0) return p.bd.tile_begin[b] + k;
+        }
+        left -= alive;
+        if (alive == 0) return -1;
+    }
+}
+
 // barrier of one team (the 8 warps = 256 threads that work on one tile); ids 1..kSub, 0 is __syncthreads
 __device__ __forceinline__ void team_sync(int team)
 {
@@ -299,6 +327,9 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     __shared__ int s_base[RPC_MAX_BATCH];                       // first points in the groups before the sweep's first
     __shared__ __align__(8) unsigned long long s_bar[2 * (kPT / 32)];   // A (C == 4): one mbarrier per warp and stage
     __shared__ int4 s_tile[2][kSub];                            // the tile every team takes next (published by its leader)
+    __shared__ int s_qcell[kSub][kQCap], s_qidx[kSub][kQCap];   // per team: queue of in-range points (cell, index, sweep)
+    __shared__ unsigned char s_qsb[kSub][kQCap];
+    __shared__ uint32_t s_qtail[kSub];                          // points pushed so far (a ring: position = count mod kQCap)
     __shared__ int s_flag;
     const int tid = threadIdx.x;
     const int P = p.gd.P, V = p.gd.V, LS = p.LS;
@@ -307,6 +338,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     const int team = tid >> 8, tl = tid & (kTile - 1);           // a team = 8 warps = one tile at a time
 
     stamp(p, 0);
+    if (p.stamps && threadIdx.x == 0) { p.stamps[blockIdx.x * 16 + 8] = 0ull; p.stamps[blockIdx.x * 16 + 9] = 0ull; }
     if (p.stamps && threadIdx.x == 0) {
         unsigned int smid;
         asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
@@ -318,9 +350,8 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         const unsigned long long magic = __ldcg(h), chi = __ldcg(h + 1), wsb = __ldcg(h + 2);
         s_flag = (magic == kWsMagic && wsb == p.ws_bytes && chi >= p.front_end) ? 1 : 0;
     }
-    // Tiles are handed out dynamically: a team's first two tiles are fixed (team t of CTA c starts with tiles
-    // c + t * G and c + (t + 4) * G), every further one comes from a global counter that the team's leader
-    // increments one iteration ahead.  Tiles differ by 6x in cost (an in-range tile waits for its atomics, an
+    // Tiles are handed out dynamically: a team's first tile is fixed (team t of CTA c starts with tile c + t * G),
+    // every further one comes from a global counter that the team's leader increments one iteration ahead.  Tiles differ by 6x in cost (an in-range tile waits for its atomics, an
     // out-of-range one does not), so a static deal left most CTAs waiting at the barrier for the slowest.
     int4 cur = pack_range(p, (int)blockIdx.x + team * nct);
     __syncthreads();
@@ -382,143 +413,177 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 1);
 
     // ------------------------------------------------------------------------------- A insert
-    unsigned int g_next = 0;                                         // (leader) the grab of the previous iteration
+    // Two stages per team.  Stage 1, tile by tile: rows -> [perturb] -> cell; the points that are in range are pushed
+    // into the team's queue in shared memory (the others are done).  Stage 2, whenever the queue holds a full round
+    // of 256 points (and once more at the end): every thread takes one queued point through the table.  An
+    // out-of-range tile costs ~0.8 us, a round of atomics ~4 us whatever the number of its points, so rounds are
+    // only ever run full, and a team that runs rounds simply grabs fewer tiles: the SMs stay evenly loaded although
+    // a LiDAR sweep's in-range points come in long runs (KITTI: 56 % of the tiles are entirely out of range).
+    // only a team's FIRST tile is fixed; every further one comes from the counter, grabbed one iteration ahead (the
+    // first grab travels while the first tile's rows do)
+    unsigned int g_next = 0;                                         // (leader) the latest grab
+    if (tl == 0) g_next = atomicAdd(&p.hdr->next_a, 1u);
+    uint32_t qhead = 0;                                              // (team-uniform) first queued point not yet taken
+    if (tl == 0) s_qtail[team] = 0u;
     for (int it = 0;; ++it) {
-        // a team's first two tiles are fixed, the third and later come from the counter (grabbed one iteration ahead)
-        if (tl == 0)
-            s_tile[it & 1][team] = pack_range(p, it == 0 ? (int)blockIdx.x + (team + kSub) * nct : 2 * kSub * nct + (int)g_next);
+        if (tl == 0) s_tile[it & 1][team] = pack_range(p, kSub * nct + (int)g_next);
         team_sync(team);
-        if (cur.w < 0) break;                                        // (the same for the whole team)
-        const int4 nxt = s_tile[it & 1][team];
-        if (nxt.w >= 0) {
-            if (tl == 0) g_next = atomicAdd(&p.hdr->next_a, 1u);     // the tile after next: back before it is needed
-            if constexpr (kTma) {
-                // every lane of this warp is past its reads of the other stage (__syncwarp below): refill it
-                if (wlane == 0) issue_rows(nxt, (it + 1) & 1);
-            } else if (tl == 0 && !(p.dbg & 8)) {
-                const size_t b0 = ((size_t)nxt.y * C * 4) & ~size_t(15), b1 = ((size_t)nxt.z * C * 4 + 15) & ~size_t(15);
-                bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
-                if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
-            }
-        }
-        const int tile = cur.w, sb = cur.x;
-        const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
-        int cell = -1;
-        const uint32_t off = p.bd.tab_off[sb], size = p.bd.tab_size[sb];
-        unsigned long long t_tile0 = 0;
-        if (p.stamps && (p.dbg & 64) && tl == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_tile0));
-        if constexpr (kTma) mbar_wait(bar_sa + 8u * (kPT / 32) * (it & 1), (uint32_t)(it >> 1) & 1u);
-        if (idx >= 0) {
-            float x, y, z;
-            if constexpr (kTma) {
-                const float4 *sp = reinterpret_cast<const float4 *>(dyn_sm) +
-                                   ((it & 1) * (kPT / 32) + wid) * kArr * 32 + wlane;
-                const float4 v = sp[0];
-                x = v.x; y = v.y; z = v.z;
-                if constexpr (PERTURB) {
-                    const float4 r = sp[32];
-                    x = __fadd_rn(x, perturb_delta(r.x, p.pd.eb[0], p.pd.fb[0]));
-                    y = __fadd_rn(y, perturb_delta(r.y, p.pd.eb[1], p.pd.fb[1]));
-                    z = __fadd_rn(z, perturb_delta(r.z, p.pd.eb[2], p.pd.fb[2]));
+        const bool last = cur.w < 0;                                 // (the same for the whole team) no tile left: drain
+        const int4 nxt = last ? cur : s_tile[it & 1][team];
+        if (!last) {
+            if (nxt.w >= 0) {
+                if (tl == 0) g_next = atomicAdd(&p.hdr->next_a, 1u); // the tile after next: back before it is needed
+                if constexpr (kTma) {
+                    // every lane of this warp is past its reads of the other stage (__syncwarp below): refill it
+                    if (wlane == 0) issue_rows(nxt, (it + 1) & 1);
+                } else if (tl == 0 && !(p.dbg & 8)) {
+                    const size_t b0 = ((size_t)nxt.y * C * 4) & ~size_t(15), b1 = ((size_t)nxt.z * C * 4 + 15) & ~size_t(15);
+                    bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
+                    if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
                 }
-            } else {
-                load_xyz<C, PERTURB>(p.pts, p.raw, p.pd, idx, x, y, z);
             }
-            cell = point_cell(x, y, z, p.gd);
-            if (!(p.dbg & 4)) {
+            // ---- stage 1: this tile's cells
+            const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
+            int cell = -1;
+            if constexpr (kTma) mbar_wait(bar_sa + 8u * (kPT / 32) * (it & 1), (uint32_t)(it >> 1) & 1u);
+            if (idx >= 0) {
+                float x, y, z;
+                if constexpr (kTma) {
+                    const float4 *sp = reinterpret_cast<const float4 *>(dyn_sm) +
+                                       ((it & 1) * (kPT / 32) + wid) * kArr * 32 + wlane;
+                    const float4 v = sp[0];
+                    x = v.x; y = v.y; z = v.z;
+                    if constexpr (PERTURB) {
+                        const float4 r = sp[32];
+                        x = __fadd_rn(x, perturb_delta(r.x, p.pd.eb[0], p.pd.fb[0]));
+                        y = __fadd_rn(y, perturb_delta(r.y, p.pd.eb[1], p.pd.fb[1]));
+                        z = __fadd_rn(z, perturb_delta(r.z, p.pd.eb[2], p.pd.fb[2]));
+                    }
+                } else {
+                    load_xyz<C, PERTURB>(p.pts, p.raw, p.pd, idx, x, y, z);
+                }
+                cell = point_cell(x, y, z, p.gd);
                 if (p.p2v) p.p2v[idx] = -1;
                 if (p.p2s) p.p2s[idx] = -1;
+                if (cell < 0) p.hslot[idx] = 0u;                     // (in-range points get their word in stage 2)
             }
+            if constexpr (kTma) __syncwarp();                        // the stage may be refilled from here on
+            const uint32_t inr = __ballot_sync(0xFFFFFFFFu, cell >= 0);
+            if (inr != 0u) {
+                uint32_t base = 0;
+                if (wlane == 0) base = atomicAdd(&s_qtail[team], (uint32_t)__popc(inr));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                if (cell >= 0) {
+                    const uint32_t q = (base + (uint32_t)__popc(inr & ((1u << wlane) - 1u))) & (kQCap - 1);
+                    s_qcell[team][q] = cell;
+                    s_qidx[team][q] = idx;
+                    s_qsb[team][q] = (unsigned char)cur.x;
+                }
+            }
+            team_sync(team);                                         // the pushes of all 8 warps are in
         }
-        if constexpr (kTma) __syncwarp();                            // the stage may be refilled from here on
-        // claim / find the cell's entry: blind 16-byte CAS along the linear probe order (at LiDAR load factors ~0.3
-        // the home entry is free or already the cell's own for most points: one L2 round trip)
-        bool cand = false;                                           // first point of the cell so far
-        uint32_t h = 0;
-        int disp = -1;                                               // displaced "first so far"
-        if (cell >= 0) {
-            const uint32_t ck = (uint32_t)cell + 1u;
-            const unsigned long long mine = ((unsigned long long)ck << 32) | (uint32_t)idx;
-            uint32_t pos = probe_start((uint32_t)cell, size);
-            uint32_t w = 0u, cnt = 0u;                               // level value of whoever arrives; snapshot of the counter
-            // (bounded: a table that someone else scribbled into must not hang the GPU; with a clean table a free
-            // entry always exists -- 1.5 entries per point)
-            for (uint32_t probes = 0; probes < size; ++probes) {
-                Entry *e = p.tab + off + pos;
-                if (p.dbg & 16) atomicAdd(&p.hdr->pad, 1u);
-                const uint4 o = cas_entry(e, mine);
-                if ((o.x | o.y) == 0u) { cand = true; h = off + pos; break; }
-                if (o.y == ck) {
-                    h = off + pos;
-                    int carry = idx;
-                    cnt = o.z;
-                    if (o.x > (uint32_t)idx) {
-                        const unsigned long long old = atomicMin(&e->key, mine);
-                        if ((uint32_t)old > (uint32_t)idx) { cand = true; disp = (int)(uint32_t)old; carry = disp; }
-                    }
-                    w = kWBase - (uint32_t)carry;
-                    break;
-                }
-                pos = pos + 1 == size ? 0u : pos + 1;
+        const uint32_t qn = s_qtail[team] - qhead;
+        // ---- stage 2: one round, when it is full or when nothing more will come
+        if (qn >= (uint32_t)kTile || (last && qn > 0u)) {
+            const uint32_t take = qn < (uint32_t)kTile ? qn : (uint32_t)kTile;
+            if (p.stamps && tl == 0) {                               // (experiments) rounds and points of this CTA, time in rounds
+                atomicAdd(p.stamps + blockIdx.x * 16 + 8, 1ull);
+                atomicAdd(p.stamps + blockIdx.x * 16 + 9, (unsigned long long)take);
             }
-            // A point that is not the first of its cell ARRIVES: it takes the next of the cell's P-1 arrival slots
-            // (one atomicAdd on the entry's counter, one plain store) -- unordered; the first point sorts them when
-            // it emits the voxel.  Only a cell with more than P points overflows: arrival P-1 and later compete for
-            // the P-1 levels of an overflow list (every level keeps the largest W = earliest point it has seen, the
-            // loser moves on; levels only grow, so a late point whose W is below the LAST level is turned away by
-            // one load -- LiDAR null returns all fall into the cell of the origin).  The voxel's P-1 later points
-            // are the earliest of arrivals + overflow levels.
-            if (w != 0u && P > 1 && !(p.dbg & 1)) {
-                Entry *e = p.tab + h;
-                const uint32_t D = (uint32_t)P - 1u;
-                uint32_t *row = p.lists + (size_t)h * LS;
-                bool over = cnt > D;                                 // (snapshot) someone overflowed already
-                if (!over) {
-                    const uint32_t r = atomicAdd(&e->cnt, 1u);
-                    if (r == 0u) __stcg(&e->slot0, w);
-                    else if (r < D) __stcg(row + r - 1u, w);
-                    else over = true;
-                }
-                if (over) {
-                    bool fresh = false;
-                    uint32_t lp = __ldcg(row + D - 1u);
-                    if (lp == 0u) {
-                        lp = atomicCAS(row + D - 1u, 0u, (uint32_t)idx + 1u);
-                        if (lp == 0u) { lp = (uint32_t)idx + 1u; fresh = true; }
+            int idx = -1, cell = -1, sb = 0;
+            if ((uint32_t)tl < take) {
+                const uint32_t q = (qhead + (uint32_t)tl) & (kQCap - 1);
+                cell = s_qcell[team][q]; idx = s_qidx[team][q]; sb = s_qsb[team][q];
+            }
+            qhead += take;
+            const uint32_t off = p.bd.tab_off[sb], size = p.bd.tab_size[sb];
+            // claim / find the cell's entry: blind 16-byte CAS along the linear probe order (at LiDAR load factors
+            // ~0.3 the home entry is free or already the cell's own for most points: one L2 round trip)
+            bool cand = false;                                       // first point of the cell so far
+            uint32_t h = 0;
+            int disp = -1;                                           // displaced "first so far"
+            if (cell >= 0) {
+                const uint32_t ck = (uint32_t)cell + 1u;
+                const unsigned long long mine = ((unsigned long long)ck << 32) | (uint32_t)idx;
+                uint32_t pos = probe_start((uint32_t)cell, size);
+                uint32_t w = 0u, cnt = 0u;                           // level value of whoever arrives; snapshot of the counter
+                // (bounded: a table that someone else scribbled into must not hang the GPU; with a clean table a
+                // free entry always exists -- 1.5 entries per point)
+                for (uint32_t probes = 0; probes < size; ++probes) {
+                    Entry *e = p.tab + off + pos;
+                    if (p.dbg & 16) atomicAdd(&p.hdr->pad, 1u);
+                    const uint4 o = cas_entry(e, mine);
+                    if ((o.x | o.y) == 0u) { cand = true; h = off + pos; break; }
+                    if (o.y == ck) {
+                        h = off + pos;
+                        int carry = idx;
+                        cnt = o.z;
+                        if (o.x > (uint32_t)idx) {
+                            const unsigned long long old = atomicMin(&e->key, mine);
+                            if ((uint32_t)old > (uint32_t)idx) { cand = true; disp = (int)(uint32_t)old; carry = disp; }
+                        }
+                        w = kWBase - (uint32_t)carry;
+                        break;
                     }
-                    uint32_t *L = p.ovf + (size_t)(lp - 1u) * LS;
-                    if (fresh || D == 1u || __ldcg(L + D - 1u) < w) {
-                        for (uint32_t q = 0; q < D; ++q) {
-                            const uint32_t old = atomicMax(L + q, w);
-                            if (old == 0u) break;
-                            w = old < w ? old : w;
+                    pos = pos + 1 == size ? 0u : pos + 1;
+                }
+                // A point that is not the first of its cell ARRIVES: it takes the next of the cell's P-1 arrival slots
+                // (one atomicAdd on the entry's counter, one plain store) -- unordered; the first point sorts them
+                // when it emits the voxel.  Only a cell with more than P points overflows: arrival P-1 and later
+                // compete for the P-1 levels of an overflow list (every level keeps the largest W = earliest point it
+                // has seen, the loser moves on; levels only grow, so a late point whose W is below the LAST level is
+                // turned away by one load -- LiDAR null returns all fall into the cell of the origin).  The voxel's
+                // P-1 later points are the earliest of arrivals + overflow levels.
+                if (w != 0u && P > 1 && !(p.dbg & 1)) {
+                    Entry *e = p.tab + h;
+                    const uint32_t D = (uint32_t)P - 1u;
+                    uint32_t *row = p.lists + (size_t)h * LS;
+                    bool over = cnt > D;                             // (snapshot) someone overflowed already
+                    if (!over) {
+                        const uint32_t r = atomicAdd(&e->cnt, 1u);
+                        if (r == 0u) __stcg(&e->slot0, w);
+                        else if (r < D) __stcg(row + r - 1u, w);
+                        else over = true;
+                    }
+                    if (over) {
+                        bool fresh = false;
+                        uint32_t lp = __ldcg(row + D - 1u);
+                        if (lp == 0u) {
+                            lp = atomicCAS(row + D - 1u, 0u, (uint32_t)idx + 1u);
+                            if (lp == 0u) { lp = (uint32_t)idx + 1u; fresh = true; }
+                        }
+                        uint32_t *L = p.ovf + (size_t)(lp - 1u) * LS;
+                        if (fresh || D == 1u || __ldcg(L + D - 1u) < w) {
+                            for (uint32_t q = 0; q < D; ++q) {
+                                const uint32_t old = atomicMax(L + q, w);
+                                if (old == 0u) break;
+                                w = old < w ? old : w;
+                            }
                         }
                     }
                 }
+                p.hslot[idx] = cand ? h + 1u : 0u;
+            }
+            // first points so far: +1 in the byte of the point's warp in its tile's word and in the group's counter
+            // (REDs, aggregated over the lanes that share the word / the counter: queued points keep their order, so
+            // a warp of the round mostly covers one or two warps of one tile)
+            const uint32_t cm = __ballot_sync(0xFFFFFFFFu, cand);
+            if (cand && !(p.dbg & 2)) {
+                const int jl = idx - p.bd.pt_begin[sb];
+                const uint32_t g0 = __match_any_sync(cm, (uint32_t)(jl >> 5) | ((uint32_t)sb << 26));
+                if ((g0 & ((1u << wlane) - 1u)) == 0u)
+                    atomicAdd(p.l0 + p.bd.tile_begin[sb] + jl / kTile, (unsigned long long)__popc(g0) << (8 * ((jl >> 5) & 7)));
+                const uint32_t g1 = __match_any_sync(cm, (uint32_t)(jl / (kTile * kGrp)) | ((uint32_t)sb << 26));
+                if ((g1 & ((1u << wlane) - 1u)) == 0u)
+                    atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[sb] + jl / (kTile * kGrp)) * kL1Stride, __popc(g1));
+            }
+            if (disp >= 0) {                                         // the displaced point is not first after all
+                const int jl = disp - p.bd.pt_begin[sb];
+                atomicAdd(p.l0 + p.bd.tile_begin[sb] + jl / kTile, ~(1ull << (8 * ((jl >> 5) & 7))) + 1ull);
+                atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[sb] + jl / (kTile * kGrp)) * kL1Stride, -1);
             }
         }
-        if (idx >= 0) p.hslot[idx] = cand ? h + 1u : 0u;
-        // first points so far, per warp: one byte of the tile's word + the group's counter (no return value: RED)
-        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, cand);
-        if (wlane == 0 && bal != 0u && !(p.dbg & 2)) {
-            const int tt = tile - p.bd.tile_begin[sb];
-            atomicAdd(p.l0 + tile, (unsigned long long)__popc(bal) << (8 * (wid & 7)));
-            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[sb] + tt / kGrp) * kL1Stride, __popc(bal));
-        }
-        if (disp >= 0) {                                             // the displaced point is not first after all
-            const int jl = disp - p.bd.pt_begin[sb];
-            atomicAdd(p.l0 + p.bd.tile_begin[sb] + jl / kTile, ~(1ull << (8 * ((jl >> 5) & 7))) + 1ull);
-            atomicAdd(p.l1 + (size_t)(p.bd.g1_begin[sb] + jl / (kTile * kGrp)) * kL1Stride, -1);
-        }
-        if (p.stamps && (p.dbg & 64)) {                              // per-tile record: start, end (warp 0 of the team), in-range points of warp 0
-            const uint32_t inr = __ballot_sync(0xFFFFFFFFu, cell >= 0);
-            if (tl == 0 && tile < 5000) {
-                unsigned long long t1;
-                asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-                unsigned long long *rec = p.stamps + 16 * 296 + 3 * (size_t)tile;
-                rec[0] = t_tile0; rec[1] = t1; rec[2] = ((unsigned long long)blockIdx.x << 32) | (unsigned)__popc(inr);
-            }
-        }
+        if (last) break;
         cur = nxt;
     }
     if (p.stamps) __syncthreads();
@@ -558,11 +623,11 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 4);
     const int F = p.gd.F;
     const int PC = P * C;
-    cur = pack_range(p, (int)blockIdx.x + team * nct);
+    cur = pack_range(p, emit_order(p, (int)blockIdx.x + team * nct));
+    if (tl == 0) g_next = atomicAdd(&p.hdr->next_b, 1u);
     uint32_t hs = (cur.w >= 0 && cur.y + tl < cur.z) ? __ldcg(p.hslot + cur.y + tl) : 0u;
     for (int it = 0;; ++it) {
-        if (tl == 0)
-            s_tile[it & 1][team] = pack_range(p, it == 0 ? (int)blockIdx.x + (team + kSub) * nct : 2 * kSub * nct + (int)g_next);
+        if (tl == 0) s_tile[it & 1][team] = pack_range(p, emit_order(p, kSub * nct + (int)g_next));
         team_sync(team);
         if (cur.w < 0) break;
         const int4 nxt = s_tile[it & 1][team];
@@ -571,6 +636,8 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         const uint32_t hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
         const int tile = cur.w, sb = cur.x;
         const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
+        unsigned long long t_tile0 = 0;
+        if (p.stamps && (p.dbg & 64) && tl == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_tile0));
         const uint32_t wc = __ballot_sync(0xFFFFFFFFu, hs != 0u);
         if (wc != 0u) {                                              // warp-uniform: a candidate in this warp
             // every load of the iteration is issued before the first one is waited for: the candidate's entry, its
@@ -724,6 +791,12 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                     }
                 }
             }
+        }
+        if (p.stamps && (p.dbg & 64) && tl == 0 && tile < 5000) {    // per-tile record of phase B (warp 0 of the team)
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+            unsigned long long *rec = p.stamps + 16 * 296 + 3 * (size_t)(5000 + tile);
+            rec[0] = t_tile0; rec[1] = t1; rec[2] = ((unsigned long long)blockIdx.x << 32) | (unsigned)__popc(wc);
         }
         cur = nxt;
         hs = hs_nxt;

@@ -73,11 +73,28 @@ if int(os.environ.get("RPC_DBG", "0")) & 64:
     for a in range(0, nt, max(nt // 12, 1)):
         sl = order_t[a:a + max(nt // 12, 1)]
         print(f"  tiles started {t_s[sl].min():6.1f}..{t_s[sl].max():6.1f} us: dur med {np.median(dur[sl]):6.2f} max {dur[sl].max():6.2f}; in-range share {np.mean(inr[sl] > 0):.2f}")
+    recb = ws[off + 8 * 16 * 296 + 24 * 5000: off + 8 * 16 * 296 + 24 * (5000 + nt)].view(torch.int64).cpu().numpy().reshape(nt, 3)
+    tb_s = (recb[:, 0] - t0) / 1e3; tb_e = (recb[:, 1] - t0) / 1e3; candb = recb[:, 2] & 0xFFFFFFFF
+    durb = tb_e - tb_s
+    print("emit tiles: candidates in warp 0 == 0: n=%d dur med %.2f max %.2f | > 0: n=%d dur med %.2f p90 %.2f max %.2f" % (
+        (candb == 0).sum(), np.median(durb[candb == 0]), durb[candb == 0].max(), (candb > 0).sum(),
+        np.median(durb[candb > 0]), np.percentile(durb[candb > 0], 90), durb[candb > 0].max()))
+    ob = np.argsort(tb_s)
+    for a in range(0, nt, max(nt // 8, 1)):
+        sl = ob[a:a + max(nt // 8, 1)]
+        print(f"  emit tiles started {tb_s[sl].min():6.1f}..{tb_s[sl].max():6.1f} us: dur med {np.median(durb[sl]):6.2f} max {durb[sl].max():6.2f}; tile ids {sl.min()}..{sl.max()}")
+    heavy = np.argsort(-durb)[:10]
+    print("  slowest emit tiles (tile:dur@start):", " ".join(f"{t}:{durb[t]:.1f}@{tb_s[t]:.0f}" for t in heavy))
     persm = {}
     for i in range(nt):
         persm.setdefault(int(smid[cta[i]]), []).append(dur[i] if inr[i] > 0 else np.nan)
     v = np.array([np.nanmedian(persm[k]) if np.isfinite(persm[k]).any() else np.nan for k in sorted(persm)])
     print("median duration of in-range tiles per SM: min", np.nanmin(v), "med", np.nanmedian(v), "max", np.nanmax(v))
 print("probes counted (RPC_DBG=16), per call:", int(ws[28:32].view(torch.int32).item()) / 5.0, "points", sum(n))
+rounds, rpts = raw_st[:, 8], raw_st[:, 9]
+print("rounds per CTA: min %d med %d max %d; points per CTA: min %d med %d max %d; corr(insert time, rounds) %.2f, corr(insert time, points) %.2f" % (
+    rounds.min(), np.median(rounds), rounds.max(), rpts.min(), np.median(rpts), rpts.max(),
+    np.corrcoef(ins, rounds)[0, 1], np.corrcoef(ins, rpts)[0, 1]))
+print("slowest CTAs: " + " ".join(f"{c}:{ins[c]:.1f}us/{rounds[c]}r/{rpts[c]}p" for c in order[-8:]) + " | fastest: " + " ".join(f"{c}:{ins[c]:.1f}us/{rounds[c]}r/{rpts[c]}p" for c in order[:6]))
 print("CTAs that found the workspace clean:", int(raw_st[:, 15].sum()), "of", NC)
 print("end", st[:, 6].max(), "dist", dist, "voxels", int(out.voxel_num[-1]), "kept", int((out.point2voxel >= 0).sum()))
