@@ -84,7 +84,9 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl, bool 
         pl->bd.pt_begin[b] = (int)pts;
         pl->bd.tile_begin[b] = (int)tiles;
         pl->bd.g1_begin[b] = (int)g1;
-        int64_t sz = ((int64_t)n[b] * 3 + 1) / 2;
+        static int tab_x2 = -1;                                     // RPC_TABLE_X2: entries per point, times two (default 3 = 1.5 per point)
+        if (tab_x2 < 0) { const char *e = getenv("RPC_TABLE_X2"); tab_x2 = e ? atoi(e) : 3; if (tab_x2 < 3) tab_x2 = 3; }
+        int64_t sz = ((int64_t)n[b] * tab_x2 + 1) / 2;
         if (sz < 64) sz = 64;
         sz = (sz + 3) & ~int64_t(3);
         pl->bd.tab_off[b] = (uint32_t)tab;

@@ -386,6 +386,16 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         __syncwarp();
     }
+    // pull the team's later tiles into L2 now (static deal: tiles first + k * 4 G): their TMA loads then hit L2 instead
+    // of paying the HBM latency once per iteration
+    if (tl == 0 && !(p.dbg & 8)) {
+        for (int t = (int)blockIdx.x + (team + kSub) * nct; t < p.ntiles; t += kSub * nct) {
+            const int4 r = pack_range(p, t);
+            const size_t b0 = ((size_t)r.y * C * 4) & ~size_t(15), b1 = ((size_t)r.z * C * 4 + 15) & ~size_t(15);
+            bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
+            if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
+        }
+    }
     if (was_clean) {
         // (experiment knob: stream the table into L2 while the first rows travel; off by default, the table stays
         // L2-resident across calls through the evict_last policy of the stores that zero it)
@@ -422,24 +432,21 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // only a team's FIRST tile is fixed; every further one comes from the counter, grabbed one iteration ahead (the
     // first grab travels while the first tile's rows do)
     unsigned int g_next = 0;                                         // (leader) the latest grab
-    if (tl == 0) g_next = atomicAdd(&p.hdr->next_a, 1u);
+    const bool stat = (p.dbg & 512) == 0;                            // static strided tiles (RPC_DBG=512: dynamic, from a global counter)
+    if (tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_a, 1u);
     uint32_t qhead = 0;                                              // (team-uniform) first queued point not yet taken
     if (tl == 0) s_qtail[team] = 0u;
     for (int it = 0;; ++it) {
-        if (tl == 0) s_tile[it & 1][team] = pack_range(p, kSub * nct + (int)g_next);
+        if (tl == 0) s_tile[it & 1][team] = pack_range(p, stat ? (int)blockIdx.x + (team + kSub * (it + 1)) * nct : kSub * nct + (int)g_next);
         team_sync(team);
         const bool last = cur.w < 0;                                 // (the same for the whole team) no tile left: drain
         const int4 nxt = last ? cur : s_tile[it & 1][team];
         if (!last) {
             if (nxt.w >= 0) {
-                if (tl == 0) g_next = atomicAdd(&p.hdr->next_a, 1u); // the tile after next: back before it is needed
+                if (tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_a, 1u); // the tile after next: back before it is needed
                 if constexpr (kTma) {
                     // every lane of this warp is past its reads of the other stage (__syncwarp below): refill it
                     if (wlane == 0) issue_rows(nxt, (it + 1) & 1);
-                } else if (tl == 0 && !(p.dbg & 8)) {
-                    const size_t b0 = ((size_t)nxt.y * C * 4) & ~size_t(15), b1 = ((size_t)nxt.z * C * 4 + 15) & ~size_t(15);
-                    bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
-                    if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
                 }
             }
             // ---- stage 1: this tile's cells
@@ -484,7 +491,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         const uint32_t qn = s_qtail[team] - qhead;
         // ---- stage 2: one round, when it is full or when nothing more will come
-        if (qn >= (uint32_t)kTile || (last && qn > 0u)) {
+        if ((qn >= (uint32_t)kTile || (last && qn > 0u)) && !(p.dbg & 1024)) {
             const uint32_t take = qn < (uint32_t)kTile ? qn : (uint32_t)kTile;
             if (p.stamps && tl == 0) {                               // (experiments) rounds and points of this CTA, time in rounds
                 atomicAdd(p.stamps + blockIdx.x * 16 + 8, 1ull);
@@ -624,20 +631,21 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     const int F = p.gd.F;
     const int PC = P * C;
     cur = pack_range(p, emit_order(p, (int)blockIdx.x + team * nct));
-    if (tl == 0) g_next = atomicAdd(&p.hdr->next_b, 1u);
+    if (tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_b, 1u);
     uint32_t hs = (cur.w >= 0 && cur.y + tl < cur.z) ? __ldcg(p.hslot + cur.y + tl) : 0u;
     for (int it = 0;; ++it) {
-        if (tl == 0) s_tile[it & 1][team] = pack_range(p, emit_order(p, kSub * nct + (int)g_next));
+        if (tl == 0) s_tile[it & 1][team] = pack_range(p, emit_order(p, stat ? (int)blockIdx.x + (team + kSub * (it + 1)) * nct : kSub * nct + (int)g_next));
         team_sync(team);
         if (cur.w < 0) break;
         const int4 nxt = s_tile[it & 1][team];
-        if (nxt.w >= 0 && tl == 0) g_next = atomicAdd(&p.hdr->next_b, 1u);
+        if (nxt.w >= 0 && tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_b, 1u);
         // the next tile's entry words travel while this one is emitted
         const uint32_t hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
         const int tile = cur.w, sb = cur.x;
         const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
         unsigned long long t_tile0 = 0;
         if (p.stamps && (p.dbg & 64) && tl == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_tile0));
+        if (p.dbg & 16384) hs = 0u;                                  // (experiment: loop skeleton only)
         const uint32_t wc = __ballot_sync(0xFFFFFFFFu, hs != 0u);
         if (wc != 0u) {                                              // warp-uniform: a candidate in this warp
             // every load of the iteration is issued before the first one is waited for: the candidate's entry, its
@@ -650,11 +658,11 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             const unsigned long long w8 = __ldcg(p.l0 + tile);
             const unsigned long long g8 = wlane < tg ? __ldcg(p.l0 + tile - tg + wlane) : 0ull;
             float x[C];
-            if (hs != 0u) load_row<C, PERTURB>(p, idx, x);
+            if (hs != 0u && !(p.dbg & 8192)) load_row<C, PERTURB>(p, idx, x);
             // candidates look at their entry again: still theirs -> first point of the cell, and the entry is zeroed
             // for the next call right away (a displaced candidate that reads the zero is not first either way)
             const bool f = hs != 0u && (ev.x | ev.y) != 0u && ev.x == (uint32_t)idx;
-            if (f) { if (p.dbg & 256) __stcg(reinterpret_cast<uint4 *>(e), make_uint4(0u, 0u, 0u, 0u)); else st_zero16_keep(e); }
+            if (f && !(p.dbg & 4096)) { if (p.dbg & 256) __stcg(reinterpret_cast<uint4 *>(e), make_uint4(0u, 0u, 0u, 0u)); else st_zero16_keep(e); }
             const uint32_t wf = __ballot_sync(0xFFFFFFFFu, f);
             if (wf != 0u) {                                          // warp-uniform: a first point in this warp
                 // voxel index of the warp's first first point inside the sweep = first points of: earlier groups
@@ -669,7 +677,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
                             tile_first_points(w8 & ((1ull << (8 * (wid & 7))) - 1ull));
                 }
                 const int pre = pre_w + __popc(wf & ((1u << wlane) - 1u));
-                const bool kept = f && pre < V;                      // cells first seen after V voxels are refused
+                const bool kept = f && pre < V && !(p.dbg & 2048);   // cells first seen after V voxels are refused
                 const int voff = s_voff[sb];
                 const uint32_t wk = __ballot_sync(0xFFFFFFFFu, kept);
                 // the cell's later points: min(cnt, P-1) arrivals (slot0 in the entry, the rest in its row) and, for
