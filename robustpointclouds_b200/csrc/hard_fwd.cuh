@@ -46,7 +46,7 @@ namespace cg = cooperative_groups;
 
 namespace rpc {
 
-constexpr int kPT = 1024;                       // threads per CTA of the persistent kernel
+constexpr int kPT = 768;                        // threads per CTA of the persistent kernel
 constexpr int kTile = 256;                      // points per tile: the unit that is dealt to the CTAs
 constexpr int kSub = kPT / kTile;               // tiles a CTA works on per iteration (8 warps each)
 constexpr int kCtasPerSM = 2;                   // resident CTAs per SM (register cap 32 at 1024 threads)
@@ -54,7 +54,8 @@ constexpr int kGrp = 32;                        // tiles per counter group (8192
 constexpr int kMaxGroups = 8192;                // group counters are scanned in shared memory (32 KB)
 constexpr int kL1Stride = 64;                   // ints between two group counters: 256 bytes, so that the REDs of one
                                                 // iteration (256 per counter) spread over L2 slices instead of one line
-constexpr int kQCap = 512;                      // queue of in-range points per team: < one round left + one tile pushed
+constexpr int kTr = 32;                         // tiles per team and phase whose (sweep, range) is looked up once, at kernel start
+constexpr int kQCap = 1024;                     // queue of in-range points per team: a round being read (256) + < 256 left + one tile pushed
 constexpr int kFastD = 15;                      // P-1 up to which a voxel's arrivals are sorted in shared memory
 constexpr uint32_t kWBase = 0x40000000u;        // level value of point i: kWBase - i  (> 0, larger = earlier)
 constexpr unsigned long long kWsMagic = 0x325F4E4C43325052ull;   // "RP2CLN_2"
@@ -270,30 +271,57 @@ __device__ __forceinline__ void warp_zero_fill(float *out, int n, int lane)
     for (int q = head + (n4 << 2) + lane; q < n; q += 32) out[q] = 0.0f;
 }
 
-// (b, first point, end, tile) of a tile, or tile = -1 past the end
-__device__ __forceinline__ int4 pack_range(const FwdParams &p, int tile)
+// (b, first point, end, tile) of a tile, or tile = -1 past the end.  Called by all 32 lanes of a warp: lane b tests
+// one sweep boundary, so the sweep of a tile costs one parameter load per lane and a ballot (a serial search by one
+// thread per team was ~1 us per tile and phase).
+__device__ __forceinline__ int4 warp_range(const FwdParams &p, int tile, int lane)
+{
+    const bool ge = lane + 1 < p.bd.B && tile >= p.bd.tile_begin[lane + 1 < RPC_MAX_BATCH ? lane + 1 : RPC_MAX_BATCH];
+    const int b = __popc(__ballot_sync(0xFFFFFFFFu, ge));
+    if (tile < 0 || tile >= p.ntiles) return make_int4(0, 0, 0, -1);
+    const int begin = p.bd.pt_begin[b] + (tile - p.bd.tile_begin[b]) * kTile;
+    return make_int4(b, begin, min(begin + kTile, p.bd.pt_begin[b + 1]), tile);
+}
+
+// Order in which phase B takes the tiles: round-robin over the sweeps (k-th tile of sweep 0, of sweep 1, ...), so that
+// the tiles at the START of every sweep -- where the cells are first seen, i.e. where the voxels are emitted -- come
+// first and spread evenly over the teams: longest jobs first.  j = 0, 1, 2, ... -> tile (a bijection; ragged sweeps are
+// skipped once they run out).  Warp-parallel: lane b holds the tile count of sweep b.
+__device__ __forceinline__ int emit_order(const FwdParams &p, int j, int lane)
+{
+    const int B = p.bd.B;
+    const int nt = lane < B ? p.bd.tile_begin[lane + 1] - p.bd.tile_begin[lane] : 0x7FFFFFFF;
+    int tmin = nt;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) tmin = min(tmin, __shfl_xor_sync(0xFFFFFFFFu, tmin, d));
+    if (j < 0 || j >= p.ntiles) return -1;
+    if (j < tmin * B) return p.bd.tile_begin[j % B] + j / B;
+    int left = j - tmin * B;
+    for (int k = tmin;; ++k) {                                       // (ragged tail: layer k holds one tile of every sweep longer than k)
+        const uint32_t alive = __ballot_sync(0xFFFFFFFFu, lane < B && nt > k);
+        const int na = __popc(alive);
+        if (left < na) return p.bd.tile_begin[__fns(alive, 0, left + 1)] + k;
+        left -= na;
+        if (na == 0) return -1;
+    }
+}
+
+// serial versions (one thread), used once per tile at kernel start to fill the per-team tile tables
+__device__ __forceinline__ int4 serial_range(const FwdParams &p, int tile)
 {
     if (tile < 0 || tile >= p.ntiles) return make_int4(0, 0, 0, -1);
     const TileRange tr = tile_range(p, tile);
     return make_int4(tr.b, tr.begin, tr.end, tile);
 }
-
-// Order in which phase B takes the tiles: round-robin over the sweeps (k-th tile of sweep 0, of sweep 1, ...), so that
-// the tiles at the START of every sweep -- where the cells are first seen, i.e. where the voxels are emitted -- are
-// handed out first and evenly: longest jobs first.  j = 0, 1, 2, ... -> tile (a bijection; ragged sweeps are skipped
-// once they run out).
-__device__ __forceinline__ int emit_order(const FwdParams &p, int j)
+__device__ __forceinline__ int serial_emit_order(const FwdParams &p, int j)
 {
     if (j < 0 || j >= p.ntiles) return -1;
     const int B = p.bd.B;
-    if (B == 1) return j;
-    // sweeps sorted by tile count would give a closed form; B <= 32, so walk the "layers": layer k holds one tile of
-    // every sweep with more than k tiles.  tmin = smallest sweep: the first tmin layers are full.
     int tmin = 0x7FFFFFFF;
     for (int b = 0; b < B; ++b) tmin = min(tmin, p.bd.tile_begin[b + 1] - p.bd.tile_begin[b]);
     if (j < tmin * B) return p.bd.tile_begin[j % B] + j / B;
     int left = j - tmin * B;
-    for (int k = tmin;; ++k) {                                       // (ragged tail: rarely more than a few layers)
+    for (int k = tmin;; ++k) {
         int alive = 0;
         for (int b = 0; b < B; ++b) alive += (p.bd.tile_begin[b + 1] - p.bd.tile_begin[b]) > k;
         if (left < alive) {
@@ -326,11 +354,11 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     __shared__ int s_voff[RPC_MAX_BATCH + 1];                   // first voxel row of each sweep, then M
     __shared__ int s_base[RPC_MAX_BATCH];                       // first points in the groups before the sweep's first
     __shared__ __align__(8) unsigned long long s_bar[2 * (kPT / 32)];   // A (C == 4): one mbarrier per warp and stage
-    __shared__ int4 s_tile[2][kSub];                            // the tile every team takes next (published by its leader)
     __shared__ int s_qcell[kSub][kQCap], s_qidx[kSub][kQCap];   // per team: queue of in-range points (cell, index, sweep)
     __shared__ unsigned char s_qsb[kSub][kQCap];
-    __shared__ uint32_t s_qtail[kSub];                          // points pushed so far (a ring: position = count mod kQCap)
+    __shared__ uint32_t s_qpush[kSub][3];                       // points pushed in iteration it (slot it % 3; reset two iterations later)
     __shared__ int s_flag;
+    __shared__ int4 s_tr[2][kSub][kTr];                         // [phase][team][k]: the team's k-th tile (sweep, first, end, tile)
     const int tid = threadIdx.x;
     const int P = p.gd.P, V = p.gd.V, LS = p.LS;
     const int nct = gridDim.x;
@@ -353,8 +381,18 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // Tiles are handed out dynamically: a team's first tile is fixed (team t of CTA c starts with tile c + t * G),
     // every further one comes from a global counter that the team's leader increments one iteration ahead.  Tiles differ by 6x in cost (an in-range tile waits for its atomics, an
     // out-of-range one does not), so a static deal left most CTAs waiting at the barrier for the slowest.
-    int4 cur = pack_range(p, (int)blockIdx.x + team * nct);
+    const int first = (int)blockIdx.x + team * nct, stride = kSub * nct;   // this team's tiles: first + k * stride
+    // the (sweep, range) of every tile this CTA will touch, looked up once: doing it per iteration in every warp
+    // (index arithmetic, searches over the sweep boundaries in parameter space) cost 3 us per iteration and phase
+    if (tid < 2 * kSub * kTr) {
+        const int ph = tid / (kSub * kTr), t = (tid / kTr) % kSub, k = tid % kTr;
+        const int j = (int)blockIdx.x + t * nct + k * stride;
+        s_tr[ph][t][k] = serial_range(p, ph ? serial_emit_order(p, j) : j);
+    }
     __syncthreads();
+    auto tile_a = [&](int k) -> int4 { return k < kTr ? s_tr[0][team][k] : warp_range(p, first + k * stride, wlane); };
+    auto tile_b = [&](int k) -> int4 { return k < kTr ? s_tr[1][team][k] : warp_range(p, emit_order(p, first + k * stride, wlane), wlane); };
+    int4 cur = tile_a(0);
     const bool was_clean = s_flag != 0;
     if (p.stamps && tid == 0) p.stamps[blockIdx.x * 16 + 15] = was_clean ? 1ull : 0ull;
     // (the staging pipeline of phase A is set up here, and the rows of the first tile are requested first thing)
@@ -388,9 +426,10 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     }
     // pull the team's later tiles into L2 now (static deal: tiles first + k * 4 G): their TMA loads then hit L2 instead
     // of paying the HBM latency once per iteration
-    if (tl == 0 && !(p.dbg & 8)) {
-        for (int t = (int)blockIdx.x + (team + kSub) * nct; t < p.ntiles; t += kSub * nct) {
-            const int4 r = pack_range(p, t);
+    if (tl < 32 && !(p.dbg & 8)) {
+        for (int t = first + stride; t < p.ntiles; t += stride) {
+            const int4 r = tile_a((t - first) / stride);
+            if (wlane != 0) continue;
             const size_t b0 = ((size_t)r.y * C * 4) & ~size_t(15), b1 = ((size_t)r.z * C * 4 + 15) & ~size_t(15);
             bulk_prefetch_l2(reinterpret_cast<const char *>(p.pts) + b0, (uint32_t)(b1 - b0));
             if constexpr (PERTURB) bulk_prefetch_l2(reinterpret_cast<const char *>(p.raw) + b0, (uint32_t)(b1 - b0));
@@ -429,25 +468,17 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // out-of-range tile costs ~0.8 us, a round of atomics ~4 us whatever the number of its points, so rounds are
     // only ever run full, and a team that runs rounds simply grabs fewer tiles: the SMs stay evenly loaded although
     // a LiDAR sweep's in-range points come in long runs (KITTI: 56 % of the tiles are entirely out of range).
-    // only a team's FIRST tile is fixed; every further one comes from the counter, grabbed one iteration ahead (the
-    // first grab travels while the first tile's rows do)
-    unsigned int g_next = 0;                                         // (leader) the latest grab
-    const bool stat = (p.dbg & 512) == 0;                            // static strided tiles (RPC_DBG=512: dynamic, from a global counter)
-    if (tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_a, 1u);
-    uint32_t qhead = 0;                                              // (team-uniform) first queued point not yet taken
-    if (tl == 0) s_qtail[team] = 0u;
+    uint32_t qhead = 0, qtail = 0;                                   // (team-uniform) the queue holds positions [qhead, qtail) mod kQCap
+    if (tl < 3) s_qpush[team][tl] = 0u;
+    team_sync(team);
     for (int it = 0;; ++it) {
-        if (tl == 0) s_tile[it & 1][team] = pack_range(p, stat ? (int)blockIdx.x + (team + kSub * (it + 1)) * nct : kSub * nct + (int)g_next);
-        team_sync(team);
         const bool last = cur.w < 0;                                 // (the same for the whole team) no tile left: drain
-        const int4 nxt = last ? cur : s_tile[it & 1][team];
+        int4 nxt = cur;
         if (!last) {
-            if (nxt.w >= 0) {
-                if (tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_a, 1u); // the tile after next: back before it is needed
-                if constexpr (kTma) {
-                    // every lane of this warp is past its reads of the other stage (__syncwarp below): refill it
-                    if (wlane == 0) issue_rows(nxt, (it + 1) & 1);
-                }
+            nxt = tile_a(it + 1);
+            if constexpr (kTma) {
+                // every lane of this warp is past its reads of the other stage (__syncwarp below): refill it
+                if (nxt.w >= 0 && wlane == 0) issue_rows(nxt, (it + 1) & 1);
             }
             // ---- stage 1: this tile's cells
             const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
@@ -478,18 +509,20 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             const uint32_t inr = __ballot_sync(0xFFFFFFFFu, cell >= 0);
             if (inr != 0u) {
                 uint32_t base = 0;
-                if (wlane == 0) base = atomicAdd(&s_qtail[team], (uint32_t)__popc(inr));
+                if (wlane == 0) base = atomicAdd(&s_qpush[team][it % 3], (uint32_t)__popc(inr));
                 base = __shfl_sync(0xFFFFFFFFu, base, 0);
                 if (cell >= 0) {
-                    const uint32_t q = (base + (uint32_t)__popc(inr & ((1u << wlane) - 1u))) & (kQCap - 1);
+                    const uint32_t q = (qtail + base + (uint32_t)__popc(inr & ((1u << wlane) - 1u))) & (kQCap - 1);
                     s_qcell[team][q] = cell;
                     s_qidx[team][q] = idx;
                     s_qsb[team][q] = (unsigned char)cur.x;
                 }
             }
             team_sync(team);                                         // the pushes of all 8 warps are in
+            qtail += s_qpush[team][it % 3];
+            if (tl == 0) s_qpush[team][(it + 2) % 3] = 0u;           // (slot of iteration it - 1: read by all, next used at it + 2)
         }
-        const uint32_t qn = s_qtail[team] - qhead;
+        const uint32_t qn = qtail - qhead;
         // ---- stage 2: one round, when it is full or when nothing more will come
         if ((qn >= (uint32_t)kTile || (last && qn > 0u)) && !(p.dbg & 1024)) {
             const uint32_t take = qn < (uint32_t)kTile ? qn : (uint32_t)kTile;
@@ -630,17 +663,14 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     stamp(p, 4);
     const int F = p.gd.F;
     const int PC = P * C;
-    cur = pack_range(p, emit_order(p, (int)blockIdx.x + team * nct));
-    if (tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_b, 1u);
-    uint32_t hs = (cur.w >= 0 && cur.y + tl < cur.z) ? __ldcg(p.hslot + cur.y + tl) : 0u;
+    // (no team barrier in this phase: every warp walks the team's tiles on its own, 32 consecutive points of each)
+    cur = tile_b(0);
+    uint32_t hs = (cur.w >= 0 && cur.y + tl < cur.z && !(p.dbg & 32768)) ? __ldcg(p.hslot + cur.y + tl) : 0u;
     for (int it = 0;; ++it) {
-        if (tl == 0) s_tile[it & 1][team] = pack_range(p, emit_order(p, stat ? (int)blockIdx.x + (team + kSub * (it + 1)) * nct : kSub * nct + (int)g_next));
-        team_sync(team);
         if (cur.w < 0) break;
-        const int4 nxt = s_tile[it & 1][team];
-        if (nxt.w >= 0 && tl == 0 && !stat) g_next = atomicAdd(&p.hdr->next_b, 1u);
+        const int4 nxt = tile_b(it + 1);
         // the next tile's entry words travel while this one is emitted
-        const uint32_t hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
+        const uint32_t hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z && !(p.dbg & 32768)) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
         const int tile = cur.w, sb = cur.x;
         const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
         unsigned long long t_tile0 = 0;
@@ -808,6 +838,11 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         }
         cur = nxt;
         hs = hs_nxt;
+    }
+    if (p.stamps && (p.dbg & 65536) && wlane == 0 && blockIdx.x < 64) {   // (experiment) when every warp leaves the emit loop
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+        p.stamps[16 * 296 + 3 * 10000 + blockIdx.x * 32 + wid] = t1;
     }
     if (p.stamps) __syncthreads();
     stamp(p, 5);

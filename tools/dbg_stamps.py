@@ -91,6 +91,12 @@ if int(os.environ.get("RPC_DBG", "0")) & 64:
     v = np.array([np.nanmedian(persm[k]) if np.isfinite(persm[k]).any() else np.nan for k in sorted(persm)])
     print("median duration of in-range tiles per SM: min", np.nanmin(v), "med", np.nanmedian(v), "max", np.nanmax(v))
 print("probes counted (RPC_DBG=16), per call:", int(ws[28:32].view(torch.int32).item()) / 5.0, "points", sum(n))
+if int(os.environ.get("RPC_DBG", "0")) & 65536:
+    wx = ws[off + 8 * (16 * 296 + 30000): off + 8 * (16 * 296 + 30000 + 64 * 32)].view(torch.int64).cpu().numpy().reshape(64, 32)
+    wx = (wx - t0) / 1e3 - st[:64, 4:5]
+    print("warp exit from the emit loop, relative to the CTA's emit start (us): per-CTA min med max over warps, first 6 CTAs:")
+    for c in range(6):
+        print("   CTA", c, np.round(np.sort(wx[c]), 2))
 rounds, rpts = raw_st[:, 8], raw_st[:, 9]
 print("rounds per CTA: min %d med %d max %d; points per CTA: min %d med %d max %d; corr(insert time, rounds) %.2f, corr(insert time, points) %.2f" % (
     rounds.min(), np.median(rounds), rounds.max(), rpts.min(), np.median(rpts), rpts.max(),
