@@ -664,15 +664,28 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     const int F = p.gd.F;
     const int PC = P * C;
     // (no team barrier in this phase: every warp walks the team's tiles on its own, 32 consecutive points of each)
-    cur = tile_b(0);
-    uint32_t hs = (cur.w >= 0 && cur.y + tl < cur.z && !(p.dbg & 32768)) ? __ldcg(p.hslot + cur.y + tl) : 0u;
+    // (the tile descriptors are re-read from shared memory every iteration rather than carried in registers: this
+    // phase is the register-hungry one, and a spilled register is an L2 round trip here)
+    uint32_t hs;
+    {
+        const int4 c0 = tile_b(0);
+        hs = (c0.w >= 0 && c0.y + tl < c0.z && !(p.dbg & 32768)) ? __ldcg(p.hslot + c0.y + tl) : 0u;
+    }
+#pragma unroll 1
     for (int it = 0;; ++it) {
-        if (cur.w < 0) break;
-        const int4 nxt = tile_b(it + 1);
+        int tile, sb, idx;
+        {
+            const int4 c = tile_b(it);
+            if (c.w < 0) break;
+            tile = c.w; sb = c.x;
+            idx = c.y + tl < c.z ? c.y + tl : -1;
+        }
         // the next tile's entry words travel while this one is emitted
-        const uint32_t hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z && !(p.dbg & 32768)) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
-        const int tile = cur.w, sb = cur.x;
-        const int idx = cur.y + tl < cur.z ? cur.y + tl : -1;
+        uint32_t hs_nxt;
+        {
+            const int4 nxt = tile_b(it + 1);
+            hs_nxt = (nxt.w >= 0 && nxt.y + tl < nxt.z && !(p.dbg & 32768)) ? __ldcg(p.hslot + nxt.y + tl) : 0u;
+        }
         unsigned long long t_tile0 = 0;
         if (p.stamps && (p.dbg & 64) && tl == 0) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_tile0));
         if (p.dbg & 16384) hs = 0u;                                  // (experiment: loop skeleton only)
@@ -836,7 +849,6 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
             unsigned long long *rec = p.stamps + 16 * 296 + 3 * (size_t)(5000 + tile);
             rec[0] = t_tile0; rec[1] = t1; rec[2] = ((unsigned long long)blockIdx.x << 32) | (unsigned)__popc(wc);
         }
-        cur = nxt;
         hs = hs_nxt;
     }
     if (p.stamps && (p.dbg & 65536) && wlane == 0 && blockIdx.x < 64) {   // (experiment) when every warp leaves the emit loop
