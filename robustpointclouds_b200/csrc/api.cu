@@ -61,63 +61,46 @@ int make_grid(const rpc_voxel_cfg *cfg, GridDesc *gd)
 
 struct Plan {                                     // host-side layout of one batched call
     BatchDesc bd;
-    int64_t ntotal, ntiles, tab_total, cap, ng1;
-    int LS;                                       // ints per entry row / overflow list: P-1, rounded up to 4 (16-byte rows)
-    // workspace: [header | stamps | clean region: table, tile words, group counters, rows, overflow lists | ... | dirty tail: hslot]
-    size_t o_stamps, o_clean, o_tab, o_l0, o_l1, o_lists, o_ovf, front_end, back_bytes, bytes;
+    int64_t ntotal, ntiles, tab_total, cap;
+    size_t o_tab, o_hslot, o_tiles, o_slots, o_stamps, bytes;
 };
 
-constexpr int kMaxTiles = 24576;                  // rpc_valid_rows scans its tile counts in shared memory (96 KB)
-
 // Tiles are kTile consecutive points of one sweep; tables hold 1.5 entries per point (worst-case load
-// 0.67 when every point is its own cell; ~0.3 on LiDAR sweeps).  `hard`: also lay out the workspace of
-// rpc_voxelize_hard (the dynamic path only uses the batch description).
-int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl, bool hard = true)
+// 0.67 when every point is its own cell; ~0.3 on LiDAR sweeps).
+int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
 {
     if (!n) return RPC_ERR_NULL;
     if (B < 1 || B > RPC_MAX_BATCH) return RPC_ERR_BATCH;
     memset(pl, 0, sizeof(*pl));
     pl->bd.B = B;
-    int64_t pts = 0, tiles = 0, tab = 0, cap = 0, g1 = 0;
+    int64_t pts = 0, tiles = 0, tab = 0, cap = 0;
     for (int b = 0; b < B; ++b) {
         if (n[b] < 0) return RPC_ERR_BATCH;
         pl->bd.pt_begin[b] = (int)pts;
         pl->bd.tile_begin[b] = (int)tiles;
-        pl->bd.g1_begin[b] = (int)g1;
-        static int tab_x2 = -1;                                     // RPC_TABLE_X2: entries per point, times two (default 3 = 1.5 per point)
-        if (tab_x2 < 0) { const char *e = getenv("RPC_TABLE_X2"); tab_x2 = e ? atoi(e) : 3; if (tab_x2 < 3) tab_x2 = 3; }
-        int64_t sz = ((int64_t)n[b] * tab_x2 + 1) / 2;
+        int64_t sz = ((int64_t)n[b] * 3 + 1) / 2;
         if (sz < 64) sz = 64;
-        sz = (sz + 3) & ~int64_t(3);
+        sz = (sz + 3) & ~int64_t(3);                            // buckets of 4 entries (32 bytes)
         pl->bd.tab_off[b] = (uint32_t)tab;
         pl->bd.tab_size[b] = (uint32_t)sz;
         tab += sz;
         pts += n[b];
-        const int64_t t = (n[b] + kTile - 1) / kTile;
-        tiles += t;
-        g1 += (t + kGrp - 1) / kGrp;
+        tiles += (n[b] + kTile - 1) / kTile;
         cap += n[b] < cfg->max_voxels ? n[b] : cfg->max_voxels;
-        if (pts > 0x3FFFFFF0LL || tab > 0x3FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // level values are 2^30 - index
+        if (pts > 0x3FFFFFF0LL || tab > 0x3FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // bits 30, 31 of hslot are flags
     }
+    if (tiles > kMaxTiles) return RPC_ERR_TOO_LARGE;
     pl->bd.pt_begin[B] = (int)pts;
     pl->bd.tile_begin[B] = (int)tiles;
-    pl->bd.g1_begin[B] = (int)g1;
-    pl->ntotal = pts; pl->ntiles = tiles; pl->tab_total = tab; pl->cap = cap; pl->ng1 = g1;
-    if (!hard) return RPC_OK;
-    if (g1 > kMaxGroups) return RPC_ERR_TOO_LARGE;                  // 67 M points
+    pl->ntotal = pts; pl->ntiles = tiles; pl->tab_total = tab; pl->cap = cap;
     if (cap * (int64_t)cfg->max_points > 0x7FFFFFF0LL) return RPC_ERR_TOO_LARGE;
-    pl->LS = cfg->max_points > 1 ? (cfg->max_points - 1 + 3) & ~3 : 0;
-    size_t o = kWsHeaderBytes;
-    pl->o_stamps = o; o += kWsStampBytes;
-    pl->o_clean = o;
-    pl->o_tab = o;    o += align_up(sizeof(Entry) * (size_t)tab);
-    pl->o_l0 = o;     o += align_up(8 * (size_t)(tiles + 1));
-    pl->o_l1 = o;     o += align_up(4 * (size_t)kL1Stride * (size_t)(g1 + 1));
-    pl->o_lists = o;  o += align_up(4 * (size_t)pl->LS * (size_t)tab);   // sparse: rows of cells with > 2 points
-    pl->o_ovf = o;    o += align_up(4 * (size_t)pl->LS * (size_t)pts);   // sparse: cells with > P points
-    pl->front_end = o;
-    pl->back_bytes = align_up(4 * (size_t)pts);                     // hslot: rewritten by every call, never assumed clean
-    pl->bytes = o + pl->back_bytes;
+    size_t o = 0;
+    pl->o_tab = o;   o += align_up(8 * (size_t)tab);
+    pl->o_hslot = o; o += align_up(4 * (size_t)pts);
+    pl->o_tiles = o; o += align_up(8 * (size_t)(tiles + 1));       // 8 per-warp byte counts per tile
+    pl->o_slots = o; o += align_up(4 * (size_t)cap * cfg->max_points);
+    pl->o_stamps = o; o += align_up(8 * 16 * 1024);
+    pl->bytes = o;
     return RPC_OK;
 }
 
@@ -177,7 +160,7 @@ int launch_hard_t(FwdParams &fp, size_t smem, cudaStream_t st)
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) != cudaSuccess)
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess)
             return RPC_ERR_CUDA;
         attr_done[dev] = true;
     }
@@ -200,42 +183,31 @@ template <int C>
 int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const float *points,
                 const float *raw, float *voxels, int32_t *coors, int32_t *num_points,
                 int32_t *voxel_num, int32_t *p2v, int32_t *p2s, float *feats, void *workspace,
-                size_t workspace_bytes, cudaStream_t st)
+                cudaStream_t st)
 {
     FwdParams fp;
-    // shared memory: the TMA row stages of phase A (C == 4), reused by the group prefix of phase B
-    const size_t stage_bytes = C == 4 ? (size_t)2 * kSub * (raw ? 2 : 1) * kTile * 16 : 0;
-    const size_t scan_words = ((size_t)pl.ng1 + 1 + 3) & ~size_t(3);
-    const int D = gd.P - 1;
-    fp.DS = (D >= 1 && D <= kFastD) ? (D | 1) : 0;                   // odd stride: conflict-free rows of sort scratch
-    fp.scan_words = (int)scan_words;
-    const size_t b_bytes = 4 * (scan_words + (size_t)kPT * fp.DS);
-    const size_t smem = stage_bytes > b_bytes ? stage_bytes : b_bytes;
-    if (smem > 100 * 1024) return RPC_ERR_TOO_LARGE;
+    size_t smem = 0;
+    // P5: slot lists of VT voxels per warp in shared memory; VT = 32 unless max_points is large
+    fp.VT = 32;
+    while (fp.VT > 4 && (size_t)(kPT / 32) * fp.VT * gd.P * sizeof(int) > 200 * 1024 / kCtasPerSM) fp.VT >>= 1;
+    fp.gather_stride = fp.VT * gd.P;
+    smem = (size_t)(kPT / 32) * fp.gather_stride * sizeof(int);
+    if (smem > 200 * 1024 / kCtasPerSM) return RPC_ERR_CONFIG;         // max_points > 195
+    const size_t scan_bytes = 4 * (size_t)(pl.ntiles + 1);          // P3's prefix array shares the buffer
+    if (smem < scan_bytes) smem = scan_bytes;
+    const size_t stage_bytes = C == 4 ? (size_t)2 * kSub * (raw ? 2 : 1) * kTile * 16 : 0;   // P1's TMA tile stages
+    smem = smem > stage_bytes ? smem : stage_bytes;
     char *w = static_cast<char *>(workspace);
-    const size_t back_off = (workspace_bytes - pl.back_bytes) & ~size_t(255);
     fp.pts = points; fp.raw = raw;
-    fp.hdr = reinterpret_cast<WsHeader *>(w);
-    fp.tab = reinterpret_cast<Entry *>(w + pl.o_tab);
-    fp.l0 = reinterpret_cast<unsigned long long *>(w + pl.o_l0);
-    fp.l1 = reinterpret_cast<int *>(w + pl.o_l1);
-    fp.lists = reinterpret_cast<uint32_t *>(w + pl.o_lists);
-    fp.ovf = reinterpret_cast<uint32_t *>(w + pl.o_ovf);
-    fp.hslot = reinterpret_cast<uint32_t *>(w + back_off);
+    fp.tab = reinterpret_cast<unsigned long long *>(w + pl.o_tab);
+    fp.hslot = reinterpret_cast<uint32_t *>(w + pl.o_hslot);
+    fp.wcnt = reinterpret_cast<unsigned long long *>(w + pl.o_tiles);
+    fp.slots = reinterpret_cast<int *>(w + pl.o_slots);
     fp.stamps = g_prof.on ? reinterpret_cast<unsigned long long *>(w + pl.o_stamps) : nullptr;
     fp.voxels = voxels; fp.coors = coors; fp.num_points = num_points; fp.voxel_num = voxel_num;
     fp.p2v = p2v; fp.p2s = p2s; fp.feats = feats;
     fp.tab_total = pl.tab_total;
-    fp.clean_lo = pl.o_clean; fp.front_end = pl.front_end; fp.back_off = back_off; fp.ws_bytes = workspace_bytes;
-    fp.ntiles = (int)pl.ntiles; fp.ng1 = (int)pl.ng1; fp.LS = pl.LS;
-    {
-        static int pf = -1;                                         // RPC_TABLE_PREFETCH=0|1|2 (kernel experiments)
-        if (pf < 0) { const char *e = getenv("RPC_TABLE_PREFETCH"); pf = e ? atoi(e) : 0; }
-        fp.pf_mode = pf;
-        static int dbg = -1;
-        if (dbg < 0) { const char *e = getenv("RPC_DBG"); dbg = e ? atoi(e) : 0; }
-        fp.dbg = dbg;
-    }
+    fp.ntiles = (int)pl.ntiles;
     fp.gd = gd; fp.bd = pl.bd; fp.pd = pd;
     return raw ? launch_hard_t<C, true>(fp, smem, st) : launch_hard_t<C, false>(fp, smem, st);
 }
@@ -330,17 +302,15 @@ RPC_API int rpc_voxelize_hard(const rpc_voxel_cfg *cfg, const float *points,
     if (raw && !pc) return RPC_ERR_NULL;
     if (workspace_bytes < pl.bytes) return RPC_ERR_WORKSPACE;
     if (misaligned(points) || misaligned(raw) || misaligned(voxels) || misaligned(coors) ||
-        (reinterpret_cast<uintptr_t>(workspace) & 255u) != 0 || misaligned(feats))
+        (reinterpret_cast<uintptr_t>(workspace) & 31u) != 0 || misaligned(feats))      // buckets are read as 32 bytes
         return RPC_ERR_ALIGN;
     PerturbDesc pd;
     fill_perturb(cfg, pc, &pd);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (pl.ntotal == 0)                                             // nothing to voxelize: B + 1 zero counts
-        return cudaMemsetAsync(voxel_num, 0, sizeof(int32_t) * (size_t)(B + 1), s) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
     switch (cfg->C) {
 #define RPC_CASE(CC)                                                                              \
     case CC: return launch_hard<CC>(gd, pl, pd, points, raw, voxels, coors, num_points, voxel_num, \
-                                    point2voxel, point2slot, feats, workspace, workspace_bytes, s);
+                                    point2voxel, point2slot, feats, workspace, s);
         RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
 #undef RPC_CASE
     }
@@ -426,7 +396,7 @@ RPC_API int rpc_voxelize_dynamic(const rpc_voxel_cfg *cfg, const float *points,
     rpc_voxel_cfg c2 = *cfg;
     c2.max_points = 1; c2.max_voxels = 1;
     Plan pl;
-    if ((st = make_plan(&c2, B, n_per_sample, &pl, false))) return st;
+    if ((st = make_plan(&c2, B, n_per_sample, &pl))) return st;
     if (pl.ntotal == 0) return RPC_OK;
     if (!points || !coors) return RPC_ERR_NULL;
     if (raw && !pc) return RPC_ERR_NULL;
@@ -471,7 +441,7 @@ int make_dyn_plan(const rpc_voxel_cfg *cfg, const GridDesc &gd, int B, const int
 {
     rpc_voxel_cfg c2 = *cfg;
     c2.max_points = 1; c2.max_voxels = 1;
-    int st = make_plan(&c2, B, n, &dp->pl, false);
+    int st = make_plan(&c2, B, n, &dp->pl);
     if (st) return st;
     const long long G = (long long)gd.g[0] * gd.g[1] * gd.g[2];
     dp->Gp = (G + kCoarseCells - 1) / kCoarseCells * kCoarseCells;

@@ -34,7 +34,6 @@ struct BatchDesc {
     int tile_begin[RPC_MAX_BATCH + 1];
     uint32_t tab_off[RPC_MAX_BATCH];   // first entry of the sweep's hash sub-table
     uint32_t tab_size[RPC_MAX_BATCH];  // its entries (even, >= 1.5 x points of the sweep)
-    int g1_begin[RPC_MAX_BATCH + 1];   // first counter group (32 tiles) of the sweep; groups never straddle sweeps
 };
 
 struct PerturbDesc {

@@ -284,7 +284,7 @@ def vfe_mean_bwd(grad_out: torch.Tensor, num_points: torch.Tensor, P: int, C: in
     return g
 
 
-PHASES = ("setup", "insert", "barrier", "scan", "emit", "tail")
+PHASES = ("clear", "insert", "flag", "assign", "rank", "gather")
 
 
 def phase_times_us(cfg: VoxelCfg, n_per_sample: Sequence[int], workspace: Optional[torch.Tensor] = None,

@@ -40,13 +40,14 @@ import sys, json
 d = json.loads(sys.stdin.read().strip().splitlines()[-1]); r = d['roofline']
 print('kitti 2 x $n', 'us/step', round(d['ms_per_step'] * 1e3, 2), r['stage_us'], r['fwd_phase_us'])"
   done ;;
-ab)
+ab|abr)
+  fl=write; [ $what = abr ] && fl=write+read
   for wl in kitti nuscenes; do for rep in 1 2; do for lib in default build_ab/librpc_r01.so; do
     if [ $lib = default ]; then unset RPC_B200_LIB; else export RPC_B200_LIB=/root/repo/$lib; fi
-    timeout 300 python bench.py --workload $wl --steps 200 --warmup 20 --no-cpu --no-also 2>/dev/null | python -c "
+    timeout 300 python bench.py --workload $wl --steps 200 --warmup 20 --no-cpu --no-also --flush $fl 2>/dev/null | python -c "
 import sys, json
 d = json.loads(sys.stdin.read().strip().splitlines()[-1]); r = d['roofline']
-print('$wl', '$lib', 'us/step', round(d['ms_per_step'] * 1e3, 2), r['stage_us'])"
+print('$wl', '$fl', '$lib', 'us/step', round(d['ms_per_step'] * 1e3, 2), r['stage_us'])"
   done; done; done 2>&1 | tee gpurun_out/ab.log ;;
 esac
 done
