@@ -89,7 +89,7 @@ int make_plan(const rpc_voxel_cfg *cfg, int B, const int32_t *n, Plan *pl)
         cap += n[b] < cfg->max_voxels ? n[b] : cfg->max_voxels;
         if (pts > 0x3FFFFFF0LL || tab > 0x3FFFFFF0LL) return RPC_ERR_TOO_LARGE;   // bits 30, 31 of hslot are flags
     }
-    if (tiles > kMaxTiles) return RPC_ERR_TOO_LARGE;
+    if (tiles > (int64_t)kMaxTiles * 32) return RPC_ERR_TOO_LARGE;   // (the scan takes groups of up to 32 tiles)
     pl->bd.pt_begin[B] = (int)pts;
     pl->bd.tile_begin[B] = (int)tiles;
     pl->ntotal = pts; pl->ntiles = tiles; pl->tab_total = tab; pl->cap = cap;
@@ -193,7 +193,10 @@ int launch_hard(const GridDesc &gd, const Plan &pl, const PerturbDesc &pd, const
     fp.gather_stride = fp.VT * gd.P;
     smem = (size_t)(kPT / 32) * fp.gather_stride * sizeof(int);
     if (smem > 200 * 1024 / kCtasPerSM) return RPC_ERR_CONFIG;         // max_points > 195
-    const size_t scan_bytes = 4 * (size_t)(pl.ntiles + 1);          // P3's prefix array shares the buffer
+    int gs = 0;                                                     // P3 scans groups of 2^gs tiles (0 up to kMaxTiles tiles)
+    while (((pl.ntiles + (1 << gs) - 1) >> gs) > kMaxTiles) ++gs;
+    fp.gs = gs;
+    const size_t scan_bytes = 4 * (size_t)(((pl.ntiles + (1 << gs) - 1) >> gs) + 1);   // P3's prefix array shares the buffer
     if (smem < scan_bytes) smem = scan_bytes;
     const size_t stage_bytes = C == 4 ? (size_t)2 * kSub * (raw ? 2 : 1) * kTile * 16 : 0;   // P1's TMA tile stages
     smem = smem > stage_bytes ? smem : stage_bytes;

@@ -64,7 +64,7 @@ struct FwdParams {
     float *voxels; int *coors; int *num_points; int *voxel_num; int *p2v; int *p2s; float *feats;
     unsigned long long *stamps;                 // [gridDim][16] %globaltimer per CTA and phase, or NULL
     long long tab_total;
-    int ntiles, VT, gather_stride;               // VT: voxel rows per gather task (one warp); floats of smem per warp
+    int ntiles, gs, VT, gather_stride;               // VT: voxel rows per gather task (one warp); floats of smem per warp
     GridDesc gd;
     BatchDesc bd;
     PerturbDesc pd;
@@ -194,6 +194,38 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
     } while (!ok);
 }
 
+// ---- batches of more than kMaxTiles tiles (P3): exclusive scan over groups of 2^gs tiles; a tile's prefix is its
+// group's plus the first points of the group's earlier tiles
+__device__ __noinline__ void big_scan(const unsigned long long *wcnt, int ntiles, int gs, int *prefix, int *sm)
+{
+    const int tid = threadIdx.x;
+    const int ngr = (ntiles + (1 << gs) - 1) >> gs;
+    const int per = (ngr + kPT - 1) / kPT;
+    const int j0 = tid * per, j1 = min(j0 + per, ngr);
+    auto group = [&](int j) {
+        int s = 0;
+        for (int t = j << gs; t < min((j + 1) << gs, ntiles); ++t) s += tile_first_points(__ldcg(wcnt + t));
+        return s;
+    };
+    int s = 0;
+    for (int j = j0; j < j1; ++j) s += group(j);
+    int tot;
+    int run = block_excl_scan<kPT>(s, sm, &tot);
+    for (int j = j0; j < j1; ++j) { prefix[j] = run; run += group(j); }
+    if (tid == kPT - 1) prefix[ngr] = tot;
+    __syncthreads();
+}
+// (warp-uniform t in [0, ntiles]; the whole warp calls)
+__device__ __noinline__ int big_prefix_at(const unsigned long long *wcnt, const int *prefix, int t, int gs)
+{
+    const int lane = threadIdx.x & 31;
+    const int g0 = (t >> gs) << gs;
+    int s = g0 + lane < t ? tile_first_points(__ldcg(wcnt + g0 + lane)) : 0;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, d);
+    return prefix[t >> gs] + s;
+}
+
 template <int C, bool PERTURB>
 __global__ void __launch_bounds__(kPT, kCtasPerSM)
 k_hard_fwd(const __grid_constant__ FwdParams p)
@@ -202,6 +234,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     extern __shared__ __align__(16) unsigned char dyn_sm[];     // P3: int prefix[ntiles]; P5: gather tile
     __shared__ int sm[33];
     __shared__ int s_voff[RPC_MAX_BATCH + 1];                   // first voxel row of each sweep, then M
+    __shared__ int s_pb[RPC_MAX_BATCH + 1];                     // first points before each sweep
     __shared__ __align__(8) unsigned long long s_bar[2 * (kPT / 32)];   // P1 (C == 4): one mbarrier per warp and stage
     const int tid = threadIdx.x;
     const int P = p.gd.P, V = p.gd.V;
@@ -435,7 +468,10 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
     // every CTA scans all tile counts into shared memory (ntiles <= kMaxTiles): prefix[j] = first points
     // in tiles < j; a sweep's voxel index base is prefix[its first tile]
     int *prefix = reinterpret_cast<int *>(dyn_sm);
-    {
+    // (batches of more than kMaxTiles tiles: the scan runs over GROUPS of 2^gs <= 32 tiles -- big_* helpers, kept out
+    // of line so that the usual path pays no registers for them)
+    const int gs = p.gs;
+    if (gs == 0) {
         const int per = (p.ntiles + kPT - 1) / kPT;
         const int j0 = tid * per, j1 = min(j0 + per, p.ntiles);
         constexpr int kKeep = 6;                                     // counts kept in registers between the two passes
@@ -454,19 +490,28 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         for (int j = j0 + kKeep; j < j1; ++j) { prefix[j] = run; run += tile_first_points(__ldcg(p.wcnt + j)); }
         if (tid == kPT - 1) prefix[p.ntiles] = tot;
         __syncthreads();
-        if (tid == 0) {
-            int acc = 0;
-            for (int b = 0; b < p.bd.B; ++b) {
-                const int m = min(prefix[p.bd.tile_begin[b + 1]] - prefix[p.bd.tile_begin[b]], V);
-                s_voff[b] = acc;
-                if (blockIdx.x == 0) p.voxel_num[b] = m;
-                acc += m;
+        if (tid <= p.bd.B) s_pb[tid] = prefix[p.bd.tile_begin[tid]];
+    } else {
+        big_scan(p.wcnt, p.ntiles, gs, prefix, sm);
+        if (wid == 0)
+            for (int b = 0; b <= p.bd.B; ++b) {
+                const int v = big_prefix_at(p.wcnt, prefix, p.bd.tile_begin[b], gs);
+                if (wlane == 0) s_pb[b] = v;
             }
-            s_voff[p.bd.B] = acc;
-            if (blockIdx.x == 0) p.voxel_num[p.bd.B] = acc;
-        }
-        __syncthreads();
     }
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0;
+        for (int b = 0; b < p.bd.B; ++b) {
+            const int m = min(s_pb[b + 1] - s_pb[b], V);
+            s_voff[b] = acc;
+            if (blockIdx.x == 0) p.voxel_num[b] = m;
+            acc += m;
+        }
+        s_voff[p.bd.B] = acc;
+        if (blockIdx.x == 0) p.voxel_num[p.bd.B] = acc;
+    }
+    __syncthreads();
     const int lvl_step = kTile % P;
     for (int it = 0; it < iters; ++it) {
         TileRange tr;
@@ -474,7 +519,7 @@ k_hard_fwd(const __grid_constant__ FwdParams p)
         uint32_t hs = kDropped;
         int idx = -1, base = 0, voff = 0;
         if (tile >= 0) {
-            base = prefix[tile] - prefix[p.bd.tile_begin[tr.b]];
+            base = (gs == 0 ? prefix[tile] : big_prefix_at(p.wcnt, prefix, tile, gs)) - s_pb[tr.b];
             voff = s_voff[tr.b];
             if (tr.begin + (tid & (kTile - 1)) < tr.end) { idx = tr.begin + (tid & (kTile - 1)); hs = __ldcg(p.hslot + idx); }
         }

@@ -207,3 +207,39 @@ def test_hard_voxelize_max_batch():
     clouds = [synth.make_cloud("kitti", 300 + 37 * i, "lidar" if i % 2 else "clustered", 900 + i) for i in range(32)]
     M, exact = _run_case(clouds, "kitti", 150, True)
     assert M > 0 and exact
+
+
+def test_hard_voxelize_large_batch_matches_per_sweep_calls():
+    """6 x 2M points (46 878 tiles > kMaxTiles: the assign phase scans GROUPS of tiles): the batched call returns,
+    sweep by sweep, exactly what six single-sweep calls return (those take the ungrouped scan the oracle tests pin)"""
+    cfgd = synth.PRESETS["kitti"]
+    C, P, V = cfgd["C"], cfgd["max_num_points"], 40000
+    dev = torch.device("cuda:0")
+    cfg = VoxelCfg.make(cfgd["voxel_size"], cfgd["point_cloud_range"], P, V, C, C)
+    N = 2_000_000
+    g = torch.Generator(device="cpu").manual_seed(11)
+    lo = torch.tensor(cfgd["point_cloud_range"][:3]) - 2.0
+    hi = torch.tensor(cfgd["point_cloud_range"][3:]) + 2.0
+    sweeps = []
+    for b in range(6):
+        x = torch.rand(N, C, generator=g)
+        x[:, :3] = lo + x[:, :3] * (hi - lo)
+        x[: N // 2, :3] = x[N // 2:, :3] + 0.01 * torch.rand(N - N // 2, 3, generator=g)   # crowded cells too
+        sweeps.append(x)
+    pts = torch.cat(sweeps).to(dev)
+    out = ops.hard_voxelize(pts, [N] * 6, cfg, want_feats=True, want_maps=True)
+    vn = out.voxel_num.cpu().tolist()
+    assert vn[-1] == sum(vn[:-1]) and all(v == V for v in vn[:-1])
+    row = 0
+    for b in range(6):
+        one = ops.hard_voxelize(pts[b * N:(b + 1) * N], [N], cfg, want_feats=True, want_maps=True)
+        m = int(one.voxel_num[0])
+        assert m == vn[b]
+        assert torch.equal(one.voxels[:m], out.voxels[row:row + m])
+        assert torch.equal(one.coors[:m, 1:], out.coors[row:row + m, 1:]) and bool((out.coors[row:row + m, 0] == b).all())
+        assert torch.equal(one.num_points[:m], out.num_points[row:row + m])
+        assert torch.equal(one.feats[:m], out.feats[row:row + m])
+        p2v = out.point2voxel[b * N:(b + 1) * N]
+        assert torch.equal(torch.where(one.point2voxel >= 0, one.point2voxel + row, one.point2voxel), p2v)
+        assert torch.equal(one.point2slot, out.point2slot[b * N:(b + 1) * N])
+        row += m
