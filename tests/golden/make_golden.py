@@ -128,7 +128,19 @@ def perturber_case(builder, name, C, training, hidden, K, seed):
         return o
 
     adv64._apply_physical_constraints = spy64
+    # smallest |ReLU input| of the fp64 run: a pre-activation within fp32 rounding of zero lets two correct fp32
+    # implementations (CPU / GPU operation order) take different sides of the kink, which moves the parameter gradients
+    # by O(1/K).  The first kitti_eval fixture (seed 200) had one at 6e-9 and failed on the B200 at 1e-4.
+    margins = []
+    hooks = [m.register_forward_hook(lambda m_, i_, o_: margins.append(float(o_.detach().abs().min())))
+             for m in adv64.modules() if isinstance(m, torch.nn.BatchNorm1d)]
+    hooks += [adv64.attention[0].register_forward_hook(lambda m_, i_, o_: margins.append(float(o_.detach().abs().min())))]
     y64, ld64 = adv64(x.double())
+    for h_ in hooks:
+        h_.remove()
+    out["relu_margin"] = np.array(min(margins))
+    print(name, "relu margin %.3g" % min(margins))
+    assert min(margins) > 1e-5, "pick another seed: a ReLU input within fp32 rounding of zero"
     p64 = cap64["p"]
     p64.retain_grad()
     total64 = ((y64 * w.double()).sum() + ld64["l2_norm"] + 2 * ld64["intensity_loss"] + 3 * ld64["bias_loss"]
@@ -236,7 +248,7 @@ def hand_cases():
 if __name__ == "__main__":
     builder, _ = _load_reference_perturber()
     perturber_case(builder, "kitti_train", 4, True, [64, 128, 64], 311, 100)
-    perturber_case(builder, "kitti_eval", 4, False, [64, 128, 64], 311, 200)
+    perturber_case(builder, "kitti_eval", 4, False, [16, 32, 64], 127, 203)  # seed chosen for the ReLU margin
     perturber_case(builder, "nus_train", 5, True, [16, 32, 64], 293, 300)
     extract_feat_case(builder, "kitti", 4, 400)
     extract_feat_case(builder, "nus", 5, 500)
