@@ -51,7 +51,8 @@ enum {
     RPC_ERR_WORKSPACE = -4,   /* workspace smaller than rpc_workspace_bytes() */
     RPC_ERR_CUDA = -5,        /* a CUDA launch failed (cudaGetLastError) */
     RPC_ERR_TOO_LARGE = -6,   /* point count or grid does not fit 31-bit indices */
-    RPC_ERR_ALIGN = -7        /* a pointer is not 16-byte aligned */
+    RPC_ERR_ALIGN = -7,       /* a pointer is not 16-byte aligned */
+    RPC_ERR_STATIC_LIMIT = -8 /* input beyond the fixed capacity of a *_static entry point */
 };
 
 /* mirrors mmcv Voxelization(voxel_size, point_cloud_range, max_num_points, max_voxels) */
@@ -270,6 +271,22 @@ int rpc_perturb_losses_bwd(const float *p, const float *consts, const float *gra
  * ------------------------------------------------------------------------------------------------- */
 int rpc_points_range_filter(const float *points, int64_t N, int C, const float *range6 /*[host]*/, float *out_points,
                             int32_t *out_index, int32_t *count, void *workspace, size_t workspace_bytes, void *stream);
+
+/*
+ * Allocation-free variant of rpc_points_range_filter.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it) and therefore cannot provide a workspace.  Same inputs, outputs and
+ * results as rpc_points_range_filter; the per-tile count scratch lives in a `static __device__` array inside the
+ * library (16 640 bytes, held by every GPU that loads the library until the process exits), so
+ *   - N is limited to RPC_STATIC_FILTER_MAX_POINTS rows; a larger N returns RPC_ERR_STATIC_LIMIT and launches nothing;
+ *   - the call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine);
+ *   - every call on a device shares the array: calls that overlap on the GPU (different streams, or graphs
+ *     replayed concurrently) race on it; stream-ordered calls are safe.  The kernel writes every count before it
+ *     reads it, so stale contents of the previous call are harmless.
+ */
+#define RPC_STATIC_FILTER_MAX_POINTS 4194304   /* 4096 tiles of 1024 rows */
+int rpc_points_range_filter_static(const float *points, int64_t N, int C, const float *range6 /*[host]*/,
+                                   float *out_points, int32_t *out_index, int32_t *count, void *stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Post-VFE perturbation variant: the elementwise part of

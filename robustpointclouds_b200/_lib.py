@@ -24,7 +24,7 @@ SYMBOLS = (
     "rpc_valid_rows_workspace_bytes", "rpc_valid_rows", "rpc_scatter_rows", "rpc_gather_rows",
     "rpc_perturb_apply_fwd", "rpc_perturb_apply_bwd",
     "rpc_dynamic_workspace_bytes", "rpc_dynamic_scatter_mean_fwd", "rpc_dynamic_stamps_offset", "rpc_allreduce_flag_bytes", "rpc_allreduce_oneshot", "rpc_allreduce_ll_bytes", "rpc_allreduce_ll",
-    "rpc_voxel_centers", "rpc_points_range_filter", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
+    "rpc_voxel_centers", "rpc_points_range_filter", "rpc_points_range_filter_static", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
     "rpc_attention_scratch_bytes", "rpc_attention_gate_fwd", "rpc_attention_gate_bwd", "rpc_linear_wgrad",
     "rpc_bn_scratch_bytes", "rpc_bn_relu_fwd", "rpc_bn_relu_bwd",
 )
@@ -117,6 +117,7 @@ def lib() -> ctypes.CDLL:
     L.rpc_momentum_apply_fwd.argtypes = [vp, vp, vp, i32, ctypes.c_float, ctypes.c_float, i64, vp, vp, vp, vp, vp]
     L.rpc_momentum_apply_bwd.argtypes = [vp, vp, vp, vp, i32, ctypes.c_float, i64, vp, vp, vp]
     L.rpc_points_range_filter.argtypes = [vp, i64, i32, ctypes.POINTER(ctypes.c_float), vp, vp, vp, vp, sz, vp]
+    L.rpc_points_range_filter_static.argtypes = [vp, i64, i32, ctypes.POINTER(ctypes.c_float), vp, vp, vp, vp]
     L.rpc_moments_bytes.restype = sz
     L.rpc_normalize_fwd.argtypes = [vp, i64, vp, i32, vp, vp, vp]
     L.rpc_perturb_losses_fwd.argtypes = [vp, i64, vp, i32, vp, vp, vp, vp]

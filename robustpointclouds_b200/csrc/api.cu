@@ -235,6 +235,7 @@ RPC_API const char *rpc_strerror(int status)
         case RPC_ERR_CUDA: return "CUDA launch failed";
         case RPC_ERR_TOO_LARGE: return "point count, table or grid exceeds 31-bit indexing";
         case RPC_ERR_ALIGN: return "pointer not 16-byte aligned";
+        case RPC_ERR_STATIC_LIMIT: return "input larger than the static-scratch entry point allows (RPC_STATIC_FILTER_MAX_POINTS rows)";
         default: return "unknown status";
     }
 }
@@ -1002,6 +1003,62 @@ RPC_API int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_me
                                                               grad_y, grad_gamma, grad_beta);
     }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ allocation-free variant (static device scratch)
+// rpc_points_range_filter_static: rpc_points_range_filter with its per-tile count scratch in a file-scope device
+// array, for callers that cannot provide a workspace (CUDA-graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (kStaticFilterInts ints = 16 640 bytes) until exit.
+// All calls on a device share it: the kernel writes every count it later reads, so nothing has to start at zero,
+// but two calls that overlap on the GPU (different streams) race on it.
+namespace {
+constexpr int kStaticFilterTiles = (int)(RPC_STATIC_FILTER_MAX_POINTS / kRowTile);
+static_assert((int64_t)kStaticFilterTiles * kRowTile == RPC_STATIC_FILTER_MAX_POINTS, "limit is a whole number of tiles");
+static_assert(kStaticFilterTiles <= kMaxTiles, "static scratch must fit the compaction kernel's scan");
+constexpr int kStaticFilterInts = (kStaticFilterTiles + 1 + 63) / 64 * 64;      // what rpc_valid_rows_workspace_bytes rounds to
+static __device__ __align__(256) int g_static_filter_cnt[kStaticFilterInts];
+
+// In host code `g_static_filter_cnt` is only a stand-in for the symbol: its device address is looked up once per
+// device, with that device current, and handed to the kernel as an ordinary pointer.
+int static_filter_scratch(int **out)
+{
+    static int *cache[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return RPC_ERR_CUDA;
+    if (!cache[dev]) {
+        void *ptr = nullptr;
+        if (cudaGetSymbolAddress(&ptr, g_static_filter_cnt) != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            return RPC_ERR_CUDA;
+        }
+        cache[dev] = static_cast<int *>(ptr);
+    }
+    *out = cache[dev];
+    return RPC_OK;
+}
+}  // namespace
+
+extern "C" {
+
+RPC_API int rpc_points_range_filter_static(const float *points, int64_t N, int C, const float *range6,
+                                           float *out_points, int32_t *out_index, int32_t *count, void *stream)
+{
+    if (C < 3 || N < 0) return RPC_ERR_CONFIG;
+    if (N > RPC_STATIC_FILTER_MAX_POINTS) return RPC_ERR_STATIC_LIMIT;
+    if (!count || !range6) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (N == 0) return cudaMemsetAsync(count, 0, 4, st) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    if (!points || !out_index) return RPC_ERR_NULL;
+    int *scratch = nullptr;
+    const int rc = static_filter_scratch(&scratch);
+    if (rc != RPC_OK) return rc;
+    RangeDesc rd;
+    for (int d = 0; d < 3; ++d) { rd.lo[d] = range6[d]; rd.hi[d] = range6[3 + d]; }
+    return launch_valid_rows(points, nullptr, N, 1, C, 2, nullptr, out_index, nullptr, out_points, count, scratch,
+                             sizeof(int) * (size_t)kStaticFilterInts, rd, st);
 }
 
 }  // extern "C"
