@@ -348,6 +348,31 @@ int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, cons
                     const float *gamma, const float *beta, int64_t K, int H, double *scratch, float *grad_y,
                     float *grad_gamma, float *grad_beta, void *stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * The Linear layers of the perturber's MLP trunk on the tensor cores (fourth slice of SURVEY 8f row 2): the forward
+ * products of `self.model` (models/adversarial/voxel_perturber.py:82-103, run at :176) and the input-gradient products
+ * autograd's addmm backward derives from them -- what the reference gets from cuBLAS.
+ *   y[K, NO] = f(x)[K, NI] * B^T (+ bias) (-> tanh),  NI, NO <= 128
+ *   w_layout 0: B = w [NO, NI] (forward, the nn.Linear weight as it lies); 1: B^T = w [NI, NO] (input gradient: x = dL/dy
+ *   of the layer, w = the same weight tensor)
+ *   in_mean / in_invstd / in_gamma / in_beta [NI] (all or none): f = the previous layer's training-mode BatchNorm +
+ *   ReLU applied while x is loaded, so the normalised activation is never written; epi_tanh: the trunk's final Tanh (:102)
+ *   moments (fp64 [2 * NO], may be NULL; zeroed by the call): += column sums and sums of squares of y, the statistics
+ *   of the BatchNorm that follows; rpc_bn_finalize turns them into save_mean / save_invstd (biased variance, eps) and
+ *   updates the running statistics like torch; rpc_bn_relu_apply recomputes z = relu(bn(y)) from saved statistics
+ *   (the layer input the weight gradient needs in the backward).
+ * NI, NO > 8: 3 x TF32 on tcgen05 (x = x_hi + x_lo, w = w_hi + w_lo, x_lo w_hi + x_hi w_lo + x_hi w_hi accumulated in
+ * fp32 in tensor memory; ~1e-6 relative, NI % 8 == 0, NO % 4 == 0).  NI <= 8 or NO <= 8 (first / last layer): fp32 FMA streams.
+ * k_dev (device int32, may be NULL) bounds the rows at run time.
+ * ------------------------------------------------------------------------------------------------- */
+int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int NI, int NO, const float *w, int w_layout,
+                   const float *bias, const float *in_mean, const float *in_invstd, const float *in_gamma,
+                   const float *in_beta, int epi_tanh, double *moments, float *y, void *stream);
+int rpc_bn_finalize(const double *moments, int64_t K, const int32_t *k_dev, int H, float eps, float momentum,
+                    float *running_mean, float *running_var, float *save_mean, float *save_invstd, void *stream);
+int rpc_bn_relu_apply(const float *y, int64_t K, const int32_t *k_dev, int H, const float *mean, const float *invstd,
+                      const float *gamma, const float *beta, float *z, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,6 +27,7 @@ SYMBOLS = (
     "rpc_voxel_centers", "rpc_points_range_filter", "rpc_points_range_filter_static", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
     "rpc_attention_scratch_bytes", "rpc_attention_gate_fwd", "rpc_attention_gate_bwd", "rpc_linear_wgrad",
     "rpc_bn_scratch_bytes", "rpc_bn_relu_fwd", "rpc_bn_relu_bwd",
+    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply",
 )
 
 
@@ -131,6 +132,9 @@ def lib() -> ctypes.CDLL:
     L.rpc_bn_scratch_bytes.argtypes = []
     L.rpc_bn_relu_fwd.argtypes = [vp, i64, i32, vp, vp, ctypes.c_float, ctypes.c_float, vp, vp, vp, vp, vp, vp, vp]
     L.rpc_bn_relu_bwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp]
+    L.rpc_linear_fwd.argtypes = [vp, i64, vp, i32, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
+    L.rpc_bn_finalize.argtypes = [vp, i64, vp, i32, ctypes.c_float, ctypes.c_float, vp, vp, vp, vp, vp]
+    L.rpc_bn_relu_apply.argtypes = [vp, i64, vp, i32, vp, vp, vp, vp, vp, vp]
     L.rpc_profile_enable.restype = None
     L.rpc_profile_enable.argtypes = [i32]
     L.rpc_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]

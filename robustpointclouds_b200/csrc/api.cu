@@ -15,6 +15,7 @@
 #include "attention.cuh"
 #include "linear.cuh"
 #include "bnrelu.cuh"
+#include "mlp_tc.cuh"
 
 using namespace rpc;
 
@@ -1002,6 +1003,82 @@ RPC_API int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_me
         k_bn_relu_bwd_elemt<1><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H,
                                                               grad_y, grad_gamma, grad_beta);
     }
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+}  // extern "C"
+
+extern "C" {
+// ------------------------------------------------------------------ Linear layers of the MLP trunk (tcgen05, 3 x TF32)
+RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int NI, int NO, const float *w, int w_layout,
+                           const float *bias, const float *in_mean, const float *in_invstd, const float *in_gamma,
+                           const float *in_beta, int epi_tanh, double *moments, float *y, void *stream)
+{
+    if (K < 0 || NI < 1 || NO < 1 || NI > kTcMaxDim || NO > kTcMaxDim || (w_layout != 0 && w_layout != 1)) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!x || !w || !y) return RPC_ERR_NULL;
+    if (in_mean && (!in_invstd || !in_gamma || !in_beta)) return RPC_ERR_NULL;
+    if (misaligned(x) || misaligned(y) || misaligned(w)) return RPC_ERR_ALIGN;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (moments && cudaMemsetAsync(moments, 0, sizeof(double) * 2 * NO, st) != cudaSuccess) return RPC_ERR_CUDA;
+    TcParams p;
+    memset(&p, 0, sizeof(p));
+    p.x = x; p.w = w; p.bias = bias; p.y = y; p.k_dev = k_dev; p.K = K; p.NI = NI; p.NO = NO; p.w_layout = w_layout;
+    p.in_mean = in_mean; p.in_invstd = in_invstd; p.in_gamma = in_gamma; p.in_beta = in_beta;
+    p.epi_tanh = epi_tanh; p.moments = moments;
+    const int sms = device_sms();
+    if (NI <= 8) {                                                   // first layer / input gradient of the last: a stream
+        if (NO & 3) return RPC_ERR_CONFIG;
+        int64_t blocks = (K * (NO >> 2) + kNarrowThreads - 1) / kNarrowThreads;
+        if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
+        k_linear_narrow_in<<<(int)blocks, kNarrowThreads, 0, st>>>(p);
+    } else if (NO <= 8) {                                            // last layer: NI / 4 lanes per row
+        if (NI != 32 && NI != 64 && NI != 128) return RPC_ERR_CONFIG;
+        if (moments) return RPC_ERR_CONFIG;
+        int64_t blocks = (K * (NI >> 2) + kNarrowThreads - 1) / kNarrowThreads;
+        if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
+        k_linear_narrow_out<<<(int)blocks, kNarrowThreads, 0, st>>>(p);
+    } else {
+        if ((NI & 7) || (NO & 3)) return RPC_ERR_CONFIG;
+        const int NOp = (NO + 31) & ~31;
+        const size_t smem = tc_smem_bytes(NI, NOp) + 128;
+        static bool attr_done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+            if (cudaFuncSetAttribute(k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(tc_smem_bytes(kTcMaxDim, kTcMaxDim) + 128)) != cudaSuccess)
+                return RPC_ERR_CUDA;
+            attr_done[dev] = true;
+        }
+        int64_t tiles = (K + kTcRows - 1) / kTcRows;
+        const int grid = (int)(tiles < sms ? tiles : sms);
+        k_linear_tc<<<grid, kTcThreads, smem, st>>>(p);
+    }
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_bn_finalize(const double *moments, int64_t K, const int32_t *k_dev, int H, float eps, float momentum,
+                            float *running_mean, float *running_var, float *save_mean, float *save_invstd, void *stream)
+{
+    if (K < 1 || H < 1 || H > kTcMaxDim) return RPC_ERR_CONFIG;
+    if (!moments || !save_mean || !save_invstd) return RPC_ERR_NULL;
+    k_bn_finalize<<<1, kTcMaxDim, 0, static_cast<cudaStream_t>(stream)>>>(moments, K, k_dev, H, eps, momentum, running_mean,
+                                                                      running_var, save_mean, save_invstd);
+    return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_bn_relu_apply(const float *y, int64_t K, const int32_t *k_dev, int H, const float *mean, const float *invstd,
+                              const float *gamma, const float *beta, float *z, void *stream)
+{
+    if (K < 0 || H < 4 || (H & 3) || H > kTcMaxDim) return RPC_ERR_CONFIG;
+    if (K == 0) return RPC_OK;
+    if (!y || !mean || !invstd || !gamma || !beta || !z) return RPC_ERR_NULL;
+    if (misaligned(y) || misaligned(z)) return RPC_ERR_ALIGN;
+    int64_t blocks = (K * H / 4 + kNarrowThreads - 1) / kNarrowThreads;
+    if (blocks > (int64_t)device_sms() * 8) blocks = (int64_t)device_sms() * 8;
+    k_bn_relu_apply<<<(int)blocks, kNarrowThreads, 0, static_cast<cudaStream_t>(stream)>>>(y, K, k_dev, H, mean, invstd, gamma,
+                                                                                       beta, z);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 

@@ -453,6 +453,58 @@ def linear_wgrad(g: torch.Tensor, a: torch.Tensor, want_bias: bool = True):
     return gw, gb
 
 
+def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, transposed: bool = False,
+               bn: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]] = None, tanh: bool = False,
+               moments: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``f(x) @ B.T + bias`` for x [K, NI], NI, NO <= 128, on the tensor cores as fp32-accurate 3 x TF32
+    (``rpc_linear_fwd``; the Linear layers of /root/reference/models/adversarial/voxel_perturber.py:82-101 and the input
+    gradients autograd derives from them).  ``transposed=False``: B = w [NO, NI] (forward, nn.Linear weight);
+    ``transposed=True``: B = w.T with w [NI, NO] (input gradient: x = dL/dy, w = the same weight tensor).
+    ``bn=(mean, invstd, gamma, beta)`` applies the previous layer's BatchNorm + ReLU to x while it is loaded;
+    ``tanh`` applies the trunk's final Tanh; ``moments`` (float64 [2 * NO], zeroed by the call) receives the column sums
+    and sums of squares of the result -- what the next BatchNorm needs (``bn_finalize``)."""
+    dev = _need_cuda(x, w, bias, moments, out)
+    x, w = _f32c(x), _f32c(w)
+    K, NI = x.shape
+    NO = w.shape[1] if transposed else w.shape[0]
+    if (w.shape[0] if transposed else w.shape[1]) != NI:
+        raise ValueError("linear_fwd: weight does not match the input width")
+    y = out if out is not None else torch.empty((K, NO), dtype=torch.float32, device=dev)
+    b4 = [None] * 4 if bn is None else [_f32c(t) for t in bn]
+    st = _lib.lib().rpc_linear_fwd(_ptr(x), K, None, NI, NO, _ptr(w), int(transposed), _ptr(None if bias is None else _f32c(bias)),
+                                   _ptr(b4[0]), _ptr(b4[1]), _ptr(b4[2]), _ptr(b4[3]), int(tanh), _ptr(moments), _ptr(y),
+                                   _stream(dev))
+    _lib.check(st, "rpc_linear_fwd")
+    return y
+
+
+def bn_finalize(moments: torch.Tensor, K: int, eps: float, momentum: float, running_mean: Optional[torch.Tensor] = None,
+                running_var: Optional[torch.Tensor] = None):
+    """(save_mean, save_invstd) of a training-mode BatchNorm1d from the column moments ``linear_fwd`` accumulated;
+    running statistics updated in place like nn.BatchNorm1d."""
+    dev = _need_cuda(moments, running_mean, running_var)
+    H = moments.numel() // 2
+    mean = torch.empty((H,), dtype=torch.float32, device=dev)
+    invstd = torch.empty((H,), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_bn_finalize(_ptr(moments), K, None, H, float(eps), float(momentum), _ptr(running_mean), _ptr(running_var),
+                                    _ptr(mean), _ptr(invstd), _stream(dev))
+    _lib.check(st, "rpc_bn_finalize")
+    return mean, invstd
+
+
+def bn_relu_apply(y: torch.Tensor, mean: torch.Tensor, invstd: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``relu(batch_norm(y))`` with the saved statistics (the backward's recomputation of a layer input)."""
+    dev = _need_cuda(y, mean, invstd, gamma, beta, out)
+    y = _f32c(y)
+    K, H = y.shape
+    z = out if out is not None else torch.empty_like(y)
+    st = _lib.lib().rpc_bn_relu_apply(_ptr(y), K, None, H, _ptr(mean), _ptr(invstd), _ptr(_f32c(gamma)), _ptr(_f32c(beta)),
+                                      _ptr(z), _stream(dev))
+    _lib.check(st, "rpc_bn_relu_apply")
+    return z
+
+
 def bn_relu_fwd(y: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, momentum: float,
                 running_mean: Optional[torch.Tensor] = None, running_var: Optional[torch.Tensor] = None):
     """Training-mode ``relu(batch_norm(y))`` for y [K, H], H <= 128 (nn.BatchNorm1d -> nn.ReLU of

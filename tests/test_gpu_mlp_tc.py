@@ -1,0 +1,86 @@
+"""GPU parity of the tensor-core Linear kernels of the perturber's MLP trunk (rpc_linear_fwd / rpc_bn_finalize /
+rpc_bn_relu_apply) against fp64 torch expressions of the same products -- what the reference's
+nn.Linear / BatchNorm1d / ReLU / Tanh modules compute (models/adversarial/voxel_perturber.py:82-103).  Tolerance: 1e-5 of
+the result's scale (north_star's bar); the 3 x TF32 split is expected to land near 1e-6."""
+import numpy as np
+import pytest
+import torch
+
+from robustpointclouds_b200 import ops
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device("cuda:0")
+TOL = 1e-5
+
+
+def _rel(a, b):
+    return float((a.double() - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.mark.parametrize("K,NI,NO,transposed", [
+    (311, 64, 128, False), (1000, 128, 64, False), (128, 128, 128, False), (129, 64, 64, False), (257, 16, 32, False),
+    (5000, 128, 64, True), (5000, 64, 128, True), (40000, 64, 128, False), (1, 64, 128, False), (777, 72, 100, False),
+    (1000, 4, 64, False), (1000, 5, 64, False), (999, 4, 64, True), (1000, 64, 4, False), (1001, 64, 5, False),
+    (513, 128, 5, False), (400, 32, 4, True)])
+def test_linear_fwd_vs_fp64(K, NI, NO, transposed):
+    g = torch.Generator(DEV).manual_seed(K + NI + NO)
+    x = torch.randn(K, NI, device=DEV, generator=g) * 3
+    w = torch.randn((NI, NO) if transposed else (NO, NI), device=DEV, generator=g)
+    b = torch.randn(NO, device=DEV, generator=g)
+    ref = x.double() @ (w.double() if transposed else w.double().t()) + b.double()
+    y = ops.linear_fwd(x, w, b, transposed=transposed)
+    assert y.shape == (K, NO) and _rel(y, ref) < TOL
+    y0 = ops.linear_fwd(x, w, None, transposed=transposed)
+    assert _rel(y0, ref - b.double()) < TOL
+
+
+@pytest.mark.parametrize("K,NI,NO", [(4099, 64, 128), (1000, 128, 64), (300, 64, 4), (2000, 4, 64), (70000, 128, 64)])
+def test_linear_fwd_prologue_epilogue(K, NI, NO):
+    """fused BatchNorm + ReLU on the input, Tanh on the output, column moments of the output"""
+    g = torch.Generator(DEV).manual_seed(K)
+    x = torch.randn(K, NI, device=DEV, generator=g) * 2 + 0.5
+    w = torch.randn(NO, NI, device=DEV, generator=g) * 0.2
+    b = torch.randn(NO, device=DEV, generator=g) * 0.1
+    mean, invstd = torch.randn(NI, device=DEV, generator=g), torch.rand(NI, device=DEV, generator=g) + 0.5
+    gamma, beta = torch.randn(NI, device=DEV, generator=g), torch.randn(NI, device=DEV, generator=g) * 0.3
+    z = torch.relu((x.double() - mean.double()) * invstd.double() * gamma.double() + beta.double())
+    ref = z @ w.double().t() + b.double()
+    want_m = NO > 8
+    mom = torch.full((2 * NO,), 7.0, dtype=torch.float64, device=DEV) if want_m else None      # zeroed by the call
+    y = ops.linear_fwd(x, w, b, bn=(mean, invstd, gamma, beta), moments=mom)
+    assert _rel(y, ref) < TOL
+    if want_m:
+        np.testing.assert_allclose(mom[:NO].cpu().numpy(), ref.sum(0).cpu().numpy(), rtol=1e-5, atol=1e-5 * K)
+        np.testing.assert_allclose(mom[NO:].cpu().numpy(), (ref * ref).sum(0).cpu().numpy(), rtol=1e-5)
+    yt = ops.linear_fwd(x, w, b, bn=(mean, invstd, gamma, beta), tanh=True)
+    assert float((yt.double() - torch.tanh(ref)).abs().max()) < TOL
+    # z itself, as the backward recomputes it
+    za = ops.bn_relu_apply(x, mean, invstd, gamma, beta) if NI % 4 == 0 and NI >= 4 else None
+    if za is not None:
+        assert float((za.double() - z).abs().max()) <= 2e-6 * float(z.abs().max())
+
+
+def test_bn_finalize_matches_batch_norm():
+    K, H = 5000, 128
+    g = torch.Generator(DEV).manual_seed(3)
+    x = torch.randn(K, 64, device=DEV, generator=g)
+    w = torch.randn(H, 64, device=DEV, generator=g) * 0.3
+    b = torch.randn(H, device=DEV, generator=g)
+    mom = torch.empty(2 * H, dtype=torch.float64, device=DEV)
+    y = ops.linear_fwd(x, w, b, moments=mom)
+    rm, rv = torch.zeros(H, device=DEV), torch.ones(H, device=DEV)
+    mean, invstd = ops.bn_finalize(mom, K, 1e-3, 0.1, rm, rv)
+    bn = torch.nn.BatchNorm1d(H, eps=1e-3, momentum=0.1).to(DEV).double().train()
+    bn(y.double())
+    yd = y.double()
+    np.testing.assert_allclose(mean.cpu().numpy(), yd.mean(0).cpu().numpy(), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(invstd.cpu().numpy(), (1 / torch.sqrt(yd.var(0, unbiased=False) + 1e-3)).cpu().numpy(), rtol=1e-5)
+    np.testing.assert_allclose(rm.cpu().numpy(), bn.running_mean.cpu().numpy(), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(rv.cpu().numpy(), bn.running_var.cpu().numpy(), rtol=1e-5)
+
+
+def test_linear_fwd_argument_checks():
+    L = __import__("robustpointclouds_b200._lib", fromlist=["lib"]).lib()
+    assert L.rpc_linear_fwd(None, 10, None, 64, 129, None, 0, None, None, None, None, None, 0, None, None, None) == -2
+    assert L.rpc_linear_fwd(None, 10, None, 64, 128, None, 0, None, None, None, None, None, 0, None, None, None) == -1
+    assert L.rpc_linear_fwd(None, 0, None, 64, 128, None, 0, None, None, None, None, None, 0, None, None, None) == 0
