@@ -1033,7 +1033,7 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
         if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
         k_linear_narrow_in<<<(int)blocks, kNarrowThreads, 0, st>>>(p);
     } else if (NO <= 8) {                                            // last layer: NI / 4 lanes per row
-        if (NI != 32 && NI != 64 && NI != 128) return RPC_ERR_CONFIG;
+        if (NI != 16 && NI != 32 && NI != 64 && NI != 128) return RPC_ERR_CONFIG;
         if (moments) return RPC_ERR_CONFIG;
         int64_t blocks = (K * (NI >> 2) + kNarrowThreads - 1) / kNarrowThreads;
         if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
@@ -1042,10 +1042,11 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
         if ((NI & 7) || (NO & 3)) return RPC_ERR_CONFIG;
         const int NOp = (NO + 31) & ~31;
         const size_t smem = tc_smem_bytes(NI, NOp) + 128;
+        p.scols = tc_stage_cols(NI, NOp);
         static bool attr_done[64] = {};
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        if (dev >= 0 && dev < 64 && !attr_done[dev]) {                // the largest case: 128 x 128 weights, 32-column stages
             if (cudaFuncSetAttribute(k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(tc_smem_bytes(kTcMaxDim, kTcMaxDim) + 128)) != cudaSuccess)
                 return RPC_ERR_CUDA;

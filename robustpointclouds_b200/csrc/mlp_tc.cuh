@@ -29,8 +29,7 @@ namespace rpc {
 
 constexpr int kTcThreads = 256;
 constexpr int kTcRows = 128;                     // rows per tile = M of the MMA
-constexpr int kTcStageCols = 64;                 // columns of X per shared-memory stage
-constexpr int kTcStageBytes = kTcRows * kTcStageCols * 4;            // one of hi / lo: 32 KB
+constexpr int kTcStageCols = 64;                 // columns of X per shared-memory stage (32 when the weights take > 64 KB)
 constexpr int kTcMaxDim = 128;
 
 struct TcParams {
@@ -41,6 +40,7 @@ struct TcParams {
     const int *k_dev;                            // device row count or NULL
     long long K;
     int NI, NO, w_layout;
+    int scols;                                   // columns per stage: 64 or 32
     const float *in_mean, *in_invstd, *in_gamma, *in_beta;   // [NI] each or NULL: prologue x' = relu(bn(x)), the
                                                  // previous layer's BatchNorm + ReLU in k_bn_relu_fwd's operation order
     int epi_tanh;                                // epilogue: y = tanh(y)
@@ -140,11 +140,12 @@ __device__ __forceinline__ float warp_column_sums32(float (&v)[32])
 
 // dynamic shared memory of k_linear_tc (128-byte aligned by the launch):
 //   [0, 2 * wbytes)                  B hi, B lo: NOp rows x NI columns, chunk-major (see header comment)
-//   [.., + 4 * kTcStageBytes)        X stages: (stage 0 hi, stage 0 lo, stage 1 hi, stage 1 lo)
+//   [.., + 4 * stage bytes)          X stages: (stage 0 hi, stage 0 lo, stage 1 hi, stage 1 lo)
 //   then mean / invstd / gamma / beta [4 * 128] floats, 4 mbarriers, the TMEM base address
+__host__ __device__ inline int tc_stage_cols(int NI, int NOp) { return 2 * NOp * NI * 4 > 64 * 1024 ? 32 : kTcStageCols; }
 __host__ __device__ inline size_t tc_smem_bytes(int NI, int NOp)
 {
-    return 2 * (size_t)NOp * NI * 4 + 4 * (size_t)kTcStageBytes + 4 * kTcMaxDim * 4 + 4 * 8 + 16;
+    return 2 * (size_t)NOp * NI * 4 + 4 * (size_t)kTcRows * tc_stage_cols(NI, NOp) * 4 + 4 * kTcMaxDim * 4 + 4 * 8 + 16;
 }
 
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -157,7 +158,9 @@ k_linear_tc(const __grid_constant__ TcParams p)
     const uint32_t wbytes = (uint32_t)NOp * NI * 4;
     unsigned char *sB = tc_sm;
     unsigned char *sA = tc_sm + 2 * wbytes;
-    float4 *s_bn = reinterpret_cast<float4 *>(sA + 4 * kTcStageBytes);      // (mean, invstd, gamma, beta) per input column
+    const int scols = p.scols;
+    const uint32_t stage_bytes = (uint32_t)kTcRows * scols * 4;      // one of hi / lo
+    float4 *s_bn = reinterpret_cast<float4 *>(sA + 4 * stage_bytes);      // (mean, invstd, gamma, beta) per input column
     unsigned long long *s_bar = reinterpret_cast<unsigned long long *>(s_bn + kTcMaxDim);   // [0,1] stage free, [2,3] acc full
     uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 4);
     const uint32_t sB_u = smem_u32(sB), sA_u = smem_u32(sA), bar_u = smem_u32(s_bar);
@@ -208,7 +211,7 @@ k_linear_tc(const __grid_constant__ TcParams p)
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
     const uint32_t idesc = tc_instr_desc(NOp);
-    const int nstage = (NI + kTcStageCols - 1) / kTcStageCols;      // stages per tile (1 or 2)
+    const int nstage = (NI + scols - 1) / scols;                    // stages per tile (1 .. 4)
     uint32_t uses0 = 0, uses1 = 0;                                    // fills of stage buffer 0 / 1 so far
     // per-thread column totals for the moments: lane j of warp w owns columns (w >> 2) * NOp / 2 + 32 * g + j
     double m_sum[2] = {0.0, 0.0}, m_sq[2] = {0.0, 0.0};
@@ -277,10 +280,10 @@ k_linear_tc(const __grid_constant__ TcParams p)
             const int buf = (it * nstage + s) & 1;
             uint32_t &uses = buf ? uses1 : uses0;
             if (uses > 0) tc_mbar_wait(bar_u + 8 * buf, (uses - 1) & 1u);        // the MMAs that read this stage are done
-            const int col0 = s * kTcStageCols;
-            const int ncol = min(kTcStageCols, NI - col0);                        // multiple of 8
+            const int col0 = s * scols;
+            const int ncol = min(scols, NI - col0);                               // multiple of 8
             const int ncg = (ncol + 15) >> 4;                                     // groups of 4 chunks (64 bytes of a row)
-            unsigned char *a_hi = sA + (size_t)buf * 2 * kTcStageBytes, *a_lo = a_hi + kTcStageBytes;
+            unsigned char *a_hi = sA + (size_t)buf * 2 * stage_bytes, *a_lo = a_hi + stage_bytes;
             // a warp instruction covers 8 rows x 4 chunks: 64 contiguous bytes per row from global memory, and per
             // quarter-warp 128 contiguous bytes of shared memory (conflict-free 16-byte stores)
             const int nj = 16 * ncg;                                              // (row group, chunk group) pairs
@@ -321,7 +324,7 @@ k_linear_tc(const __grid_constant__ TcParams p)
             __syncthreads();
             if (tid == 0) {
                 tc_fence_after();
-                const uint32_t a_hi_u = sA_u + (uint32_t)buf * 2 * kTcStageBytes, a_lo_u = a_hi_u + kTcStageBytes;
+                const uint32_t a_hi_u = sA_u + (uint32_t)buf * 2 * stage_bytes, a_lo_u = a_hi_u + stage_bytes;
                 const uint32_t d = tmem_base + (uint32_t)(acc * NOp);
                 for (int k = 0; k < (ncol >> 3); ++k) {                           // K = 8 per instruction: two 16-byte chunks
                     const uint32_t ao = (uint32_t)k * 2 * 2048u;
@@ -413,7 +416,7 @@ k_linear_narrow_in(const __grid_constant__ TcParams p)
     }
 }
 
-// NO <= 8: NI / 4 lanes per row (a power of two <= 32), one float4 of the row each; shuffle reduction
+// NO <= 8: NI / 4 lanes per row (a power of two, 4 .. 32), one float4 of the row each; shuffle reduction
 __global__ void __launch_bounds__(kNarrowThreads)
 k_linear_narrow_out(const __grid_constant__ TcParams p)
 {
@@ -453,13 +456,16 @@ k_linear_narrow_out(const __grid_constant__ TcParams p)
 #pragma unroll
             for (int m = 0; m < 8; ++m)
                 if (m < NO) acc[m] += __shfl_xor_sync(0xFFFFFFFFu, acc[m], d);
-        if (row < K && sub < NO) {
-            float v = 0.0f;
+        if (row < K) {                                                 // every lane of the row holds all NO totals
 #pragma unroll
-            for (int m = 0; m < 8; ++m) v = sub == m ? acc[m] : v;
-            if (p.bias) v = __fadd_rn(v, __ldg(p.bias + sub));
-            if (p.epi_tanh) v = tanhf(v);
-            p.y[row * NO + sub] = v;
+            for (int m = 0; m < 8; ++m) {
+                if (m < NO && (m % L) == sub) {
+                    float v = acc[m];
+                    if (p.bias) v = __fadd_rn(v, __ldg(p.bias + m));
+                    if (p.epi_tanh) v = tanhf(v);
+                    p.y[row * NO + m] = v;
+                }
+            }
         }
     }
 }

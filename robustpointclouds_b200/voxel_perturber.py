@@ -208,6 +208,76 @@ class _ReluAfter(nn.ReLU):
         return super().forward(x)
 
 
+class _TrunkFn(torch.autograd.Function):
+    """The whole MLP trunk (voxel_perturber.py:82-103: five Linear + BatchNorm1d + ReLU blocks, Linear, Tanh) in training
+    mode with every product on this library's kernels: ``rpc_linear_fwd`` (tcgen05, 3 x TF32; the first / last layer as
+    streams) for the forward and the input gradients, the BatchNorm + ReLU of layer l applied while layer l + 1 loads its
+    input, the batch statistics accumulated in the producing layer's epilogue (``rpc_bn_finalize``), ``rpc_bn_relu_bwd``
+    and ``rpc_linear_wgrad`` in the backward.  Only the pre-activations y_l are kept between forward and backward; the
+    normalised activations are recomputed (``rpc_bn_relu_apply``) where the weight gradient needs them.
+    ``params`` = (W0, b0, gamma0, beta0, ..., W4, b4, gamma4, beta4, W5, b5)."""
+
+    @staticmethod
+    def forward(ctx, xn, bns, *params):
+        K = xn.shape[0]
+        x, bn, ys, stats = xn.contiguous(), None, [], []
+        nl = len(bns)
+        for l in range(nl):
+            W, b, ga, be = params[4 * l:4 * l + 4]
+            mom = torch.empty((2 * W.shape[0],), dtype=torch.float64, device=xn.device)
+            y = ops.linear_fwd(x, W, b, bn=bn, moments=mom)
+            m = bns[l]
+            mean, invstd = ops.bn_finalize(mom, K, m.eps, m.momentum, m.running_mean, m.running_var)
+            m.num_batches_tracked.add_(1)
+            bn = (mean, invstd, ga, be)
+            ys.append(y)
+            stats += [mean, invstd]
+            x = y
+        W, b = params[4 * nl:4 * nl + 2]
+        raw = ops.linear_fwd(x, W, b, bn=bn, tanh=True)
+        ctx.save_for_backward(xn, raw, *ys, *stats, *params)
+        ctx.nl = nl
+        return raw
+
+    @staticmethod
+    def backward(ctx, g_raw):
+        nl = ctx.nl
+        saved = ctx.saved_tensors
+        xn, raw = saved[0], saved[1]
+        ys, stats, params = saved[2:2 + nl], saved[2 + nl:2 + 3 * nl], saved[2 + 3 * nl:]
+        grads = [None] * len(params)
+        g = g_raw * (1.0 - raw * raw)                              # Tanh
+        W, _ = params[4 * nl:4 * nl + 2]
+        bn_of = lambda l: (stats[2 * l], stats[2 * l + 1], params[4 * l + 2], params[4 * l + 3])   # noqa: E731
+        a = ops.bn_relu_apply(ys[nl - 1], *bn_of(nl - 1))
+        grads[4 * nl], grads[4 * nl + 1] = ops.linear_wgrad(g, a)
+        g_a = ops.linear_fwd(g, W, transposed=True)
+        g_xn = None
+        for l in range(nl - 1, -1, -1):
+            W = params[4 * l]
+            g_y, gg, gb = ops.bn_relu_bwd(g_a, ys[l], *bn_of(l))
+            a = xn if l == 0 else ops.bn_relu_apply(ys[l - 1], *bn_of(l - 1), out=a if a.shape == ys[l - 1].shape else None)
+            grads[4 * l], grads[4 * l + 1] = ops.linear_wgrad(g_y, a)
+            grads[4 * l + 2], grads[4 * l + 3] = gg, gb
+            if l > 0:
+                g_a = ops.linear_fwd(g_y, W, transposed=True)
+            elif ctx.needs_input_grad[0]:
+                g_xn = ops.linear_fwd(g_y, W, transposed=True)
+        return (g_xn, None, *grads)
+
+
+def _trunk_supported(model: nn.Sequential, x: torch.Tensor) -> bool:
+    """the layer widths the tensor-core / stream kernels take (rpc_linear_fwd): C <= 8, hidden widths multiples of 8 up
+    to 128 (16 .. 128 for the layer in front of the output)"""
+    lin = [m for m in model if isinstance(m, nn.Linear)]
+    if len(lin) != 6 or not (x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and x.shape[0] >= 2):
+        return False
+    C = lin[0].in_features
+    hs = [m.out_features for m in lin[:-1]]
+    return (3 <= C <= 8 and lin[-1].out_features == C and all(h % 8 == 0 and 8 <= h <= 128 for h in hs)
+            and hs[-1] in (16, 32, 64, 128))
+
+
 def _gradient_hook(grad):
     if grad is None:
         return grad
@@ -219,7 +289,7 @@ class VoxelPerturber(nn.Module):
     def __init__(self, sensor_error_bound: float = 0.2, voxel_size: Sequence[float] = (0.05, 0.05, 0.1),
                  use_spatial_attention: bool = True, hidden_channels: Sequence[int] = (8, 16, 32),
                  nan_guards=True, fused_stats: bool = True, fused_attention: bool = True,
-                 fused_wgrad: bool = True, fused_bn: bool = True):
+                 fused_wgrad: bool = True, fused_bn: bool = True, fused_trunk: bool = True):
         super().__init__()
         voxel_size = list(voxel_size)
         self.sensor_error_bound = sensor_error_bound
@@ -246,6 +316,9 @@ class VoxelPerturber(nn.Module):
         self.fused_attention = fused_attention    # the attention gate through rpc_attention_gate_fwd/bwd
         self.fused_wgrad = fused_wgrad            # weight / bias gradients of the MLP's Linear layers: rpc_linear_wgrad
         self.fused_bn = fused_bn                  # training-mode BatchNorm1d + ReLU of the MLP: rpc_bn_relu_fwd/bwd
+        # training mode: the whole trunk through _TrunkFn (forward and input-gradient products on tcgen05, BatchNorm
+        # fused into the neighbouring layers); the per-module paths above serve eval mode and unsupported widths
+        self.fused_trunk = fused_trunk
         self._bounds_cache: Dict[Tuple[int, bool], Tuple[torch.Tensor, torch.Tensor, PerturbCfg]] = {}
 
     # ------------------------------------------------------------------ construction
@@ -365,7 +438,7 @@ class VoxelPerturber(nn.Module):
                 scale = torch.ones_like(scale)
             xn = torch.clamp(x / scale, -10.0, 10.0)
         try:
-            raw = self.model(xn)
+            raw = self._run_trunk(xn)
         except RuntimeError:
             return None
         if host and torch.isnan(raw).any():
@@ -380,6 +453,18 @@ class VoxelPerturber(nn.Module):
         if self.nan_guards == "device":
             self.guard_tripped = self.guard_tripped | torch.isnan(raw).any()
         return raw
+
+    def _run_trunk(self, xn: torch.Tensor) -> torch.Tensor:
+        if self.fused_trunk and self.training and torch.is_grad_enabled() and _trunk_supported(self.model, xn):
+            lin = [m for m in self.model if isinstance(m, nn.Linear)]
+            bns = [m for m in self.model if isinstance(m, nn.BatchNorm1d)]
+            if len(bns) == 5 and all(m.training and m.affine and m.track_running_stats and m.momentum is not None for m in bns):
+                params = []
+                for l, b in zip(lin[:-1], bns):
+                    params += [l.weight, l.bias, b.weight, b.bias]
+                params += [lin[-1].weight, lin[-1].bias]
+                return _TrunkFn.apply(xn, bns, *params)
+        return self.model(xn)
 
     @staticmethod
     def losses(p: torch.Tensor, fused: bool = False) -> Dict[str, torch.Tensor]:

@@ -143,7 +143,7 @@ def test_module_fused_wgrad_equals_nn_linear(golden_dir):
     w = torch.from_numpy(g["w"]).to(DEV)
     grads = []
     for fused in (True, False):
-        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_wgrad=fused).build(4)
+        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_wgrad=fused, fused_trunk=False).build(4)
         assert set(adv.state_dict()) == set(state)
         adv.load_state_dict(state)
         adv = adv.to(DEV).train()
@@ -164,7 +164,7 @@ def test_module_large_batch_forward_path(train):
     ys = []
     for fused in (True, False):
         torch.manual_seed(3)
-        adv = VoxelPerturber(hidden_channels=[64, 128, 64], fused_wgrad=fused, nan_guards=False).build(4, DEV).train(train)
+        adv = VoxelPerturber(hidden_channels=[64, 128, 64], fused_wgrad=fused, fused_trunk=False, nan_guards=False).build(4, DEV).train(train)
         if train:
             y, _ = adv(x)
             y.sum().backward()
@@ -215,7 +215,7 @@ def test_module_fused_bn_equals_aten(golden_dir):
     w = torch.from_numpy(g["w"]).to(DEV)
     res = []
     for fused in (True, False):
-        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_bn=fused).build(4)
+        adv = VoxelPerturber(hidden_channels=[int(h) for h in g["hidden"]], fused_bn=fused, fused_trunk=False).build(4)
         assert set(adv.state_dict()) == set(state)
         adv.load_state_dict(state)
         adv = adv.to(DEV).train()

@@ -14,14 +14,14 @@ TOL = 1e-5
 
 
 def _rel(a, b):
-    return float((a.double() - b).abs().max() / b.abs().max().clamp_min(1e-30))
+    return float((a.detach().double() - b.detach()).abs().max() / b.detach().abs().max().clamp_min(1e-30))
 
 
 @pytest.mark.parametrize("K,NI,NO,transposed", [
     (311, 64, 128, False), (1000, 128, 64, False), (128, 128, 128, False), (129, 64, 64, False), (257, 16, 32, False),
     (5000, 128, 64, True), (5000, 64, 128, True), (40000, 64, 128, False), (1, 64, 128, False), (777, 72, 100, False),
     (1000, 4, 64, False), (1000, 5, 64, False), (999, 4, 64, True), (1000, 64, 4, False), (1001, 64, 5, False),
-    (513, 128, 5, False), (400, 32, 4, True)])
+    (513, 128, 5, False), (400, 32, 4, True), (1003, 16, 5, False), (100, 16, 8, False)])
 def test_linear_fwd_vs_fp64(K, NI, NO, transposed):
     g = torch.Generator(DEV).manual_seed(K + NI + NO)
     x = torch.randn(K, NI, device=DEV, generator=g) * 3
@@ -53,7 +53,7 @@ def test_linear_fwd_prologue_epilogue(K, NI, NO):
         np.testing.assert_allclose(mom[:NO].cpu().numpy(), ref.sum(0).cpu().numpy(), rtol=1e-5, atol=1e-5 * K)
         np.testing.assert_allclose(mom[NO:].cpu().numpy(), (ref * ref).sum(0).cpu().numpy(), rtol=1e-5)
     yt = ops.linear_fwd(x, w, b, bn=(mean, invstd, gamma, beta), tanh=True)
-    assert float((yt.double() - torch.tanh(ref)).abs().max()) < TOL
+    assert float((yt.double() - torch.tanh(ref)).abs().max()) < TOL * float(ref.abs().max())     # |tanh'| <= 1
     # z itself, as the backward recomputes it
     za = ops.bn_relu_apply(x, mean, invstd, gamma, beta) if NI % 4 == 0 and NI >= 4 else None
     if za is not None:
@@ -84,3 +84,57 @@ def test_linear_fwd_argument_checks():
     assert L.rpc_linear_fwd(None, 10, None, 64, 129, None, 0, None, None, None, None, None, 0, None, None, None) == -2
     assert L.rpc_linear_fwd(None, 10, None, 64, 128, None, 0, None, None, None, None, None, 0, None, None, None) == -1
     assert L.rpc_linear_fwd(None, 0, None, 64, 128, None, 0, None, None, None, None, None, 0, None, None, None) == 0
+
+
+@pytest.mark.parametrize("C,hidden,K", [(4, [64, 128, 64], 4001), (5, [16, 32, 64], 2500), (4, [32, 64, 128], 300), (4, [8, 16, 32], 1000)])
+def test_fused_trunk_matches_module_path(C, hidden, K):
+    """VoxelPerturber(fused_trunk=True) -- every product of the trunk on rpc_linear_fwd / rpc_linear_wgrad, BatchNorm fused
+    into the neighbouring layers -- against the same weights through nn.Linear / nn.BatchNorm1d / nn.ReLU / nn.Tanh
+    (fp64 on the GPU): perturbed points, losses, every parameter gradient (1e-4 of the tensor's scale in front of the
+    +-0.1 clamp hook, like the fixture pin), running statistics.  [8, 16, 32] has a 16-wide layer in front of a 32-wide
+    one and an 8-wide output feeder: it takes the per-module path (unsupported width) and must still agree."""
+    import copy
+    from robustpointclouds_b200 import VoxelPerturber
+    torch.manual_seed(C * 1000 + K)
+    vs = [0.05, 0.05, 0.1] if C == 4 else [0.075, 0.075, 0.2]
+    adv = VoxelPerturber(hidden_channels=hidden, voxel_size=vs, nan_guards=False).build(C, DEV).train()
+    ref = copy.deepcopy(adv)
+    ref.fused_trunk = ref.fused_stats = ref.fused_attention = False
+    for m in ref.modules():
+        if hasattr(m, "fused"):
+            m.fused = False
+    ref = ref.double()
+    for q in list(adv.parameters()) + list(ref.parameters()):
+        q._backward_hooks = None                                   # compare in front of the clamp
+    g = torch.Generator(DEV).manual_seed(7)
+    x = torch.rand(K, C, device=DEV, generator=g) * torch.tensor([70.0, 80.0, 4.0, 1.0, 0.5][:C], device=DEV)
+    w = torch.randn(K, C, device=DEV, generator=g) * 0.01
+
+    def run(m, x_, w_):
+        y, ld = m(x_)
+        (y * w_).sum().add(ld["l2_norm"] + 2 * ld["intensity_loss"] + 3 * ld["bias_loss"] + 4 * ld["imbalance_loss"]).backward()
+        return y, ld
+
+    y, ld = run(adv, x, w)
+    # the reference copy runs ATen in fp64; its tail kernel needs fp32, so mirror the tail with torch ops
+    from robustpointclouds_b200.voxel_perturber import perturber_bounds
+    xd = x.double()
+    xn = torch.clamp(xd / (xd.std(0, keepdim=True) + 1e-6), -10, 10)
+    raw = ref.model(xn) * ref.attention(xn)
+    eb, fb = perturber_bounds(C, True)
+    p = torch.clamp(raw * eb.to(DEV).double(), -fb.to(DEV).double(), fb.to(DEV).double())
+    yr = xd + p
+    lr = VoxelPerturber.losses(p, False)
+    (yr * w.double()).sum().add(lr["l2_norm"] + 2 * lr["intensity_loss"] + 3 * lr["bias_loss"] + 4 * lr["imbalance_loss"]).backward()
+    assert _rel(y, yr) < TOL
+    for k in ld:
+        assert abs(float(ld[k]) - float(lr[k])) <= 1e-5 * max(abs(float(lr[k])), 1e-3), k
+    for (k, q), (_, r) in zip(adv.named_parameters(), ref.named_parameters()):
+        scale = max(float(r.grad.abs().max()), 1e-6)
+        # (a Linear bias in front of a BatchNorm has a gradient of exactly zero: fp32 leaves ~1e-8 of rounding there)
+        assert float((q.grad.double() - r.grad).abs().max()) <= max(1e-4 * scale, 1e-6), (k, scale)
+    for (k, b), (_, rb) in zip(adv.named_buffers(), ref.named_buffers()):
+        if b.dtype.is_floating_point:
+            np.testing.assert_allclose(b.cpu().numpy(), rb.cpu().numpy(), rtol=2e-5, atol=1e-6, err_msg=k)
+        else:
+            assert int(b) == int(rb), k

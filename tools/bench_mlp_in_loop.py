@@ -9,7 +9,8 @@ U(-1, 1) stand-in --
 
 timed with CUDA events per step (median of 30 after 5 warm-ups), three ways: every fused kernel of this library on
 (`fused_stats`, `fused_attention`, `fused_wgrad`), the last one off, all off (the ATen formulas the reference runs around its MLP), and the split of
-the fused run into voxelize / perturber / VFE+backward.  The MLP trunk itself is cuBLAS + ATen BatchNorm in all of them.
+the fused run into voxelize / perturber / VFE+backward.  `trunk on tcgen05` runs the whole trunk through _TrunkFn (rpc_linear_fwd: 3 x TF32 tcgen05 products, BatchNorm fused into
+the neighbouring layers); in the others its products are cuBLAS.
     python tools/bench_mlp_in_loop.py [kitti|nuscenes ...]"""
 import os
 import statistics
@@ -49,14 +50,16 @@ for preset in sys.argv[1:] or ["kitti", "nuscenes"]:
     M = int(vd0["voxels"].shape[0])
     w = torch.randn((M, C), device=dev, generator=torch.Generator(dev).manual_seed(1))
     res = {}
-    variants = (("fused", True, True, True), ("fused, ATen BatchNorm + ReLU", True, True, False),
-                ("fused, nn.Linear backward, ATen BatchNorm + ReLU", True, False, False), ("aten", False, False, False))
+    variants = (("trunk on tcgen05", True, True, True, True), ("fused", True, True, True, False),
+                ("fused, ATen BatchNorm + ReLU", True, True, False, False),
+                ("fused, nn.Linear backward, ATen BatchNorm + ReLU", True, False, False, False), ("aten", False, False, False, False))
     if os.environ.get("RPC_BENCH_VARIANTS"):                        # e.g. "fused" for an ncu launch list of one variant
         variants = tuple(v for v in variants if v[0] in os.environ["RPC_BENCH_VARIANTS"].split(";"))
-    for name, fused, wgrad, bn in variants:
+    for name, fused, wgrad, bn, trunk in variants:
         torch.manual_seed(0)
         adv = rpc.VoxelPerturber(hidden_channels=[64, 128, 64], voxel_size=d["voxel_size"], nan_guards="device",
-                                 fused_stats=fused, fused_attention=fused, fused_wgrad=wgrad, fused_bn=bn).build(C, dev).train()
+                                 fused_stats=fused, fused_attention=fused, fused_wgrad=wgrad, fused_bn=bn,
+                                 fused_trunk=trunk).build(C, dev).train()
         adv._return_loss_dict = True
         state = {}
 
@@ -85,5 +88,7 @@ for preset in sys.argv[1:] or ["kitti", "nuscenes"]:
         adv.flush_metrics()
         print(f"{preset} B={B} N={N} M={M} K={K} [{name}]: step {tot * 1e3:.0f} us = {N / tot / 1e3:.1f} M points/s "
               f"(voxelize {tv * 1e3:.0f} us, perturb + VFE forward {tf * 1e3:.0f} us, backward {(tot - tv - tf) * 1e3:.0f} us)")
+    if "aten" in res and "trunk on tcgen05" in res:
+        print(f"{preset}: trunk on tcgen05 vs cuBLAS + per-module kernels: {res['fused'] / res['trunk on tcgen05']:.2f}x, vs ATen: {res['aten'] / res['trunk on tcgen05']:.2f}x")
     if "aten" in res and "fused" in res:
         print(f"{preset}: fused kernels around the MLP vs ATen formulas: {res['aten'] / res['fused']:.2f}x")
