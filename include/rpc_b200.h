@@ -361,8 +361,9 @@ int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, cons
  *   of the BatchNorm that follows; rpc_bn_finalize turns them into save_mean / save_invstd (biased variance, eps) and
  *   updates the running statistics like torch; rpc_bn_relu_apply recomputes z = relu(bn(y)) from saved statistics
  *   (the layer input the weight gradient needs in the backward).
- * NI, NO > 8: 3 x TF32 on tcgen05 (x = x_hi + x_lo, w = w_hi + w_lo, x_lo w_hi + x_hi w_lo + x_hi w_hi accumulated in
- * fp32 in tensor memory; ~1e-6 relative, NI % 8 == 0, NO % 4 == 0).  NI <= 8 or NO <= 8 (first / last layer): fp32 FMA streams.
+ * NI > 8 (NI % 8 == 0, any NO): 3 x TF32 on tcgen05 (x = x_hi + x_lo, w = w_hi + w_lo, x_lo w_hi + x_hi w_lo + x_hi w_hi
+ * accumulated in fp32 in tensor memory; ~1e-6 relative).  NI <= 8 (first layer, input gradient of the last; NO % 4 == 0): an
+ * fp32 FMA stream.
  * k_dev (device int32, may be NULL) bounds the rows at run time.
  * ------------------------------------------------------------------------------------------------- */
 int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int NI, int NO, const float *w, int w_layout,

@@ -1032,21 +1032,14 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
         int64_t blocks = (K * (NO >> 2) + kNarrowThreads - 1) / kNarrowThreads;
         if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
         k_linear_narrow_in<<<(int)blocks, kNarrowThreads, 0, st>>>(p);
-    } else if (NO <= 8) {                                            // last layer: NI / 4 lanes per row
-        if (NI != 16 && NI != 32 && NI != 64 && NI != 128) return RPC_ERR_CONFIG;
-        if (moments) return RPC_ERR_CONFIG;
-        int64_t blocks = (K * (NI >> 2) + kNarrowThreads - 1) / kNarrowThreads;
-        if (blocks > (int64_t)sms * 8) blocks = (int64_t)sms * 8;
-        k_linear_narrow_out<<<(int)blocks, kNarrowThreads, 0, st>>>(p);
-    } else {
-        if ((NI & 7) || (NO & 3)) return RPC_ERR_CONFIG;
+    } else {                                                         // (the last layer, NO = C, also goes here: N padded to 32)
+        if (NI & 7) return RPC_ERR_CONFIG;
         const int NOp = (NO + 31) & ~31;
         const size_t smem = tc_smem_bytes(NI, NOp) + 128;
-        p.scols = tc_stage_cols(NI, NOp);
         static bool attr_done[64] = {};
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !attr_done[dev]) {                // the largest case: 128 x 128 weights, 32-column stages
+        if (dev >= 0 && dev < 64 && !attr_done[dev]) {                // the largest case: 128 x 128 weights
             if (cudaFuncSetAttribute(k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)(tc_smem_bytes(kTcMaxDim, kTcMaxDim) + 128)) != cudaSuccess)
                 return RPC_ERR_CUDA;
@@ -1054,7 +1047,7 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
         }
         int64_t tiles = (K + kTcRows - 1) / kTcRows;
         const int grid = (int)(tiles < sms ? tiles : sms);
-        k_linear_tc<<<grid, kTcThreads, smem, st>>>(p);
+        k_linear_tc<<<grid, kTcThreads2, smem, st>>>(p);
     }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }

@@ -11,25 +11,27 @@
 // accumulated in fp32 in tensor memory: relative error ~1e-6, inside the 1e-5 parity bar, where single-pass TF32
 // (1e-3) is not.
 //
-// One persistent CTA per SM, 256 threads:
+// One persistent CTA per SM, 13 warps with fixed roles that meet only at mbarriers:
 //   * the weight matrix is split once into hi / lo and kept in shared memory in the tcgen05 K-major canonical layout
 //     without swizzle (8 x 16-byte core matrices; SBO = 128 B between 8-row groups, LBO between 16-byte K chunks);
-//   * per tile, all warps bring 128 rows x 64 columns of X through registers (optional fused prologue: the previous
-//     layer's BatchNorm + ReLU, x' = relu((x - mean) * invstd * gamma + beta), so the normalised activation never exists in HBM),
-//     split them and store hi / lo into one of two shared-memory stages, then one thread issues the 3 x (NI / 8)
-//     tcgen05.mma (M = 128, N = NO, K = 8) into one of two TMEM accumulators and commits to mbarriers;
-//   * the epilogue of tile t (tcgen05.ld -> + bias [-> tanh] -> global, and the per-column sum / sum of squares the
-//     next BatchNorm needs) runs after the loads and the MMA issue of tile t + 1, so the tensor core, the loads and
-//     the stores of neighbouring tiles overlap.
-// Layers with NI <= 8 or NO <= 8 (the first and the last of the trunk) are streams, not contractions: k_linear_narrow_*.
+//   * 8 loader warps bring 128 rows x 32 columns of X per stage through registers (optional fused prologue: the
+//     previous layer's BatchNorm + ReLU, x' = relu((x - mean) * invstd * gamma + beta), so the normalised activation never
+//     exists in HBM), split them and store hi / lo into one of two shared-memory stages; four stage loads stay in flight
+//     per thread (64 KB per SM);
+//   * one thread issues the 3 x (columns / 8) tcgen05.mma (M = 128, N = NO, K = 8) of a stage into one of two TMEM
+//     accumulators and commits to the "stage free" / "accumulator full" mbarriers;
+//   * 4 epilogue warps (one per TMEM lane quadrant) take the finished accumulator 32 columns at a time:
+//     tcgen05.ld -> + bias [-> tanh] -> a padded per-warp slab in shared memory -> full 128-byte lines to global memory,
+//     and, lane = column, the per-column sum / sum of squares the next BatchNorm needs (no shuffles).
+// The first version (all warps doing load -> MMA -> epilogue in turn) ran at 1.2 TB/s: profiles/r02_linear_tc.txt.
+// The first layer (NI = C <= 8) and the input gradient of the last one are streams, not contractions: k_linear_narrow_in.
+// The last layer (NO = C) runs on the tensor cores with N padded to 32 (a 16-lanes-per-row shuffle kernel was 2.3 x slower).
 #pragma once
 #include "common.cuh"
 
 namespace rpc {
 
-constexpr int kTcThreads = 256;
 constexpr int kTcRows = 128;                     // rows per tile = M of the MMA
-constexpr int kTcStageCols = 64;                 // columns of X per shared-memory stage (32 when the weights take > 64 KB)
 constexpr int kTcMaxDim = 128;
 
 struct TcParams {
@@ -40,7 +42,6 @@ struct TcParams {
     const int *k_dev;                            // device row count or NULL
     long long K;
     int NI, NO, w_layout;
-    int scols;                                   // columns per stage: 64 or 32
     const float *in_mean, *in_invstd, *in_gamma, *in_beta;   // [NI] each or NULL: prologue x' = relu(bn(x)), the
                                                  // previous layer's BatchNorm + ReLU in k_bn_relu_fwd's operation order
     int epi_tanh;                                // epilogue: y = tanh(y)
@@ -121,67 +122,85 @@ __device__ __forceinline__ float bn_relu_value(float x, float mean, float invstd
     return t < 0.0f ? 0.0f : t;
 }
 
-// column totals of a [32 lanes] x [32 columns] block held one row per lane: after the butterfly lane j holds column j
-__device__ __forceinline__ float warp_column_sums32(float (&v)[32])
+// 32 consecutive fp32 columns of this thread's TMEM lane (issue only; tc_ld_wait before the registers are read)
+__device__ __forceinline__ void tc_ld32_issue(uint32_t taddr, uint32_t (&r)[32])
 {
-    const int lane = threadIdx.x & 31;
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) {
-        const bool up = lane & d;
-#pragma unroll
-        for (int i = 0; i < d; ++i) {
-            const float send = up ? v[i] : v[i + d];
-            const float keep = up ? v[i + d] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xFFFFFFFFu, send, d);
-        }
-    }
-    return v[0];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 
-// dynamic shared memory of k_linear_tc (128-byte aligned by the launch):
-//   [0, 2 * wbytes)                  B hi, B lo: NOp rows x NI columns, chunk-major (see header comment)
-//   [.., + 4 * stage bytes)          X stages: (stage 0 hi, stage 0 lo, stage 1 hi, stage 1 lo)
-//   then mean / invstd / gamma / beta [4 * 128] floats, 4 mbarriers, the TMEM base address
-__host__ __device__ inline int tc_stage_cols(int NI, int NOp) { return 2 * NOp * NI * 4 > 64 * 1024 ? 32 : kTcStageCols; }
+// ---- layout of k_linear_tc's dynamic shared memory
+//   B hi, B lo          2 x NOp x NI x 4 bytes, chunk-major canonical layout (LBO = NOp * 16, SBO = 128)
+//   X stages            2 x (hi, lo) x 128 rows x 32 columns x 4 bytes = 64 KB (LBO = 2048, SBO = 128)
+//   epilogue slabs      4 warps x 32 rows x 36 floats (padded rows: conflict-free 16-byte writes by row and reads by column)
+//   BatchNorm constants of the prologue (float4 per input column), bias, 8 mbarriers, the TMEM base address
+constexpr int kTcLoadWarps = 8, kTcEpiWarps = 4;
+constexpr int kTcLoaders = kTcLoadWarps * 32;
+constexpr int kTcThreads2 = (kTcLoadWarps + kTcEpiWarps + 1) * 32;     // + the MMA warp
+constexpr int kTcSC = 32;                                              // columns of X per stage
+constexpr int kTcStageB = kTcRows * kTcSC * 4;                         // one of hi / lo: 16 KB
+constexpr int kTcSlabStride = 36;                                      // floats per slab row
+constexpr int kTcDepth = 4;                                            // stage loads a loader thread keeps in flight
+
 __host__ __device__ inline size_t tc_smem_bytes(int NI, int NOp)
 {
-    return 2 * (size_t)NOp * NI * 4 + 4 * (size_t)kTcRows * tc_stage_cols(NI, NOp) * 4 + 4 * kTcMaxDim * 4 + 4 * 8 + 16;
+    return 2 * (size_t)NOp * NI * 4 + 4 * (size_t)kTcStageB + (size_t)kTcEpiWarps * 32 * kTcSlabStride * 4 +
+           (size_t)kTcMaxDim * 16 + kTcMaxDim * 4 + 8 * 8 + 16;
 }
 
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kTcThreads2, 1)
 k_linear_tc(const __grid_constant__ TcParams p)
 {
     extern __shared__ __align__(128) unsigned char tc_sm[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NI = p.NI, NO = p.NO;
-    const int NOp = (NO + 31) & ~31;                               // N of the MMA (16 | N at M = 128; 32 for the epilogue's column split)
+    const int NOp = (NO + 31) & ~31;                               // N of the MMA (16 | N at M = 128; 32-column epilogue groups)
     const uint32_t wbytes = (uint32_t)NOp * NI * 4;
     unsigned char *sB = tc_sm;
     unsigned char *sA = tc_sm + 2 * wbytes;
-    const int scols = p.scols;
-    const uint32_t stage_bytes = (uint32_t)kTcRows * scols * 4;      // one of hi / lo
-    float4 *s_bn = reinterpret_cast<float4 *>(sA + 4 * stage_bytes);      // (mean, invstd, gamma, beta) per input column
-    unsigned long long *s_bar = reinterpret_cast<unsigned long long *>(s_bn + kTcMaxDim);   // [0,1] stage free, [2,3] acc full
-    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 4);
+    float *s_slab = reinterpret_cast<float *>(sA + 4 * kTcStageB);
+    float4 *s_bn = reinterpret_cast<float4 *>(s_slab + kTcEpiWarps * 32 * kTcSlabStride);
+    float *s_bias = reinterpret_cast<float *>(s_bn + kTcMaxDim);
+    unsigned long long *s_bar = reinterpret_cast<unsigned long long *>(s_bias + kTcMaxDim);
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(s_bar + 8);
     const uint32_t sB_u = smem_u32(sB), sA_u = smem_u32(sA), bar_u = smem_u32(s_bar);
+    // barriers: [0,1] stage full (256 loader arrivals), [2,3] stage free (MMA commit), [4,5] accumulator full (commit),
+    // [6,7] accumulator free (128 epilogue arrivals)
+    const uint32_t bar_afull = bar_u, bar_afree = bar_u + 16, bar_cfull = bar_u + 32, bar_cfree = bar_u + 48;
     long long K = p.K;
     if (p.k_dev) K = min(K, (long long)*p.k_dev);
     const long long ntiles = (K + kTcRows - 1) / kTcRows;
-    const int tmem_cols = NOp <= 32 ? 64 : NOp <= 64 ? 128 : 256;                      // two accumulators
+    const int tmem_cols = NOp <= 32 ? 64 : NOp <= 64 ? 128 : 256;   // two accumulators
+    const int nstage = (NI + kTcSC - 1) / kTcSC;                     // stages per tile (1 .. 4)
+    const long long my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const long long njobs = my_tiles * nstage;                       // (tile, stage) pairs of this CTA, in order
 
-    // ---- set-up: barriers, tensor memory, weights (hi / lo, canonical layout), prologue constants
+    // ---- set-up: barriers, tensor memory, weights (hi / lo, canonical layout), prologue / epilogue constants
     if (tid == 0) {
-        for (int i = 0; i < 4; ++i) tc_mbar_init(bar_u + 8 * i, 1);
+        tc_mbar_init(bar_afull, kTcLoaders); tc_mbar_init(bar_afull + 8, kTcLoaders);
+        tc_mbar_init(bar_afree, 1); tc_mbar_init(bar_afree + 8, 1);
+        tc_mbar_init(bar_cfull, 1); tc_mbar_init(bar_cfull + 8, 1);
+        tc_mbar_init(bar_cfree, kTcEpiWarps * 32); tc_mbar_init(bar_cfree + 8, kTcEpiWarps * 32);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {
-        __syncwarp();
+    if (warp == kTcLoadWarps + kTcEpiWarps) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     {
         const int nch = NI >> 2;                                       // 16-byte chunks per row
-        for (int e = tid; e < NOp * nch; e += kTcThreads) {
+        for (int e = tid; e < NOp * nch; e += kTcThreads2) {
             int n, c;
             float v[4] = {0.f, 0.f, 0.f, 0.f};
             if (p.w_layout == 0) {                                     // B[n][k] = w[n * NI + k]: chunks of a row are contiguous
@@ -202,129 +221,89 @@ k_linear_tc(const __grid_constant__ TcParams p)
             *reinterpret_cast<uint4 *>(sB + wbytes + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
         if (p.in_mean)
-            for (int c = tid; c < NI; c += kTcThreads)
+            for (int c = tid; c < NI; c += kTcThreads2)
                 s_bn[c] = make_float4(__ldg(p.in_mean + c), __ldg(p.in_invstd + c), __ldg(p.in_gamma + c), __ldg(p.in_beta + c));
+        for (int c = tid; c < kTcMaxDim; c += kTcThreads2) s_bias[c] = (p.bias && c < NO) ? __ldg(p.bias + c) : 0.0f;
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
-    const uint32_t idesc = tc_instr_desc(NOp);
-    const int nstage = (NI + scols - 1) / scols;                    // stages per tile (1 .. 4)
-    uint32_t uses0 = 0, uses1 = 0;                                    // fills of stage buffer 0 / 1 so far
-    // per-thread column totals for the moments: lane j of warp w owns columns (w >> 2) * NOp / 2 + 32 * g + j
-    double m_sum[2] = {0.0, 0.0}, m_sq[2] = {0.0, 0.0};
 
-    // ---- epilogue of one tile: TMEM -> registers -> (+ bias, tanh) -> global; column moments
-    auto epilogue = [&](long long tile, int it) {
-        const int acc = it & 1;
-        tc_mbar_wait(bar_u + 8 * (2 + acc), (uint32_t)(it >> 1) & 1u);
-        tc_fence_after();
-        const int q = warp & 3, h = warp >> 2;
-        const long long row = tile * kTcRows + q * 32 + lane;
-        const bool live = row < K;
-        const int half = NOp >> 1;
-        for (int g = 0; g * 32 < half; ++g) {
-            const int c0 = h * half + g * 32;                       // first column of this group
-            const int nv = min(32, half - g * 32);                  // 16 or 32 columns
-            float v[32];
-            {
-                float t[16];
-                tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * NOp + c0), t);
+    if (warp < kTcLoadWarps) {
+        // ================= loaders: global -> registers -> (BatchNorm + ReLU) -> hi / lo -> shared-memory stage
+        // A warp instruction covers 8 rows x 4 chunks: 64 contiguous bytes per row from global memory, and per quarter-warp
+        // 128 contiguous bytes of shared memory (conflict-free 16-byte stores).  kTcDepth stage loads stay in flight per
+        // thread (64 KB per SM), so the conversion of one stage overlaps the memory latency of the next ones.
+        const int r8 = lane & 7, cq = lane >> 3;
+        float4 v[kTcDepth][4];
+        auto issue = [&](long long j, float4 (&slot)[4]) {
+            if (j >= njobs) return;
+            const long long ti = j / nstage;
+            const int s = (int)(j - ti * nstage);
+            const long long tile = blockIdx.x + ti * gridDim.x;
+            const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) v[i] = t[i];
-                if (nv > 16) tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * NOp + c0 + 16), t);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) v[16 + i] = nv > 16 ? t[i] : 0.0f;
+            for (int u = 0; u < 4; ++u) {
+                const int jj = warp + 8 * u, rg = jj >> 1, ch = (jj & 1) * 4 + cq;
+                const long long row = tile * kTcRows + rg * 8 + r8;
+                slot[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row < K && ch * 4 < ncol) slot[u] = __ldg(reinterpret_cast<const float4 *>(p.x + row * NI + col0) + ch);
             }
+        };
+        auto consume = [&](long long j, float4 (&slot)[4]) {
+            if (j >= njobs) return;
+            const long long ti = j / nstage;
+            const int s = (int)(j - ti * nstage);
+            const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
+            const int buf = (int)(j & 1);
+            if (j >= 2) tc_mbar_wait(bar_afree + 8 * buf, (uint32_t)((j >> 1) - 1) & 1u);     // the MMAs that read this stage are done
+            unsigned char *a_hi = sA + (size_t)buf * 2 * kTcStageB, *a_lo = a_hi + kTcStageB;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int c = c0 + i;
-                float y = v[i];
-                if (p.bias && c < NO) y = __fadd_rn(y, __ldg(p.bias + c));
-                if (p.epi_tanh) y = tanhf(y);
-                v[i] = (live && c < NO && i < nv) ? y : 0.0f;
-            }
-            if (live) {
-                float *dst = p.y + row * NO + c0;
-                if ((NO & 3) == 0) {
+            for (int u = 0; u < 4; ++u) {
+                const int jj = warp + 8 * u, rg = jj >> 1, ch = (jj & 1) * 4 + cq;
+                if (ch * 4 >= ncol) continue;
+                float e[4] = {slot[u].x, slot[u].y, slot[u].z, slot[u].w};
+                if (p.in_mean) {
 #pragma unroll
-                    for (int i = 0; i < 32; i += 4)
-                        if (i < nv && c0 + i < NO) *reinterpret_cast<float4 *>(dst + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (i < nv && c0 + i < NO) dst[i] = v[i];
-                }
-            }
-            if (p.moments) {
-                float sq[32];
-#pragma unroll
-                for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
-                const float s1 = warp_column_sums32(v), s2 = warp_column_sums32(sq);
-                if (g == 0) { m_sum[0] += (double)s1; m_sq[0] += (double)s2; }
-                else        { m_sum[1] += (double)s1; m_sq[1] += (double)s2; }
-            }
-        }
-        tc_fence_before();
-    };
-
-    // ---- main loop: loads + MMA issue of tile `it`, then the epilogue of tile `it - 1`
-    const int r8 = lane & 7, cq = lane >> 3;
-    int it = 0;
-    long long prev_tile = -1;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        for (int s = 0; s < nstage; ++s) {
-            const int buf = (it * nstage + s) & 1;
-            uint32_t &uses = buf ? uses1 : uses0;
-            if (uses > 0) tc_mbar_wait(bar_u + 8 * buf, (uses - 1) & 1u);        // the MMAs that read this stage are done
-            const int col0 = s * scols;
-            const int ncol = min(scols, NI - col0);                               // multiple of 8
-            const int ncg = (ncol + 15) >> 4;                                     // groups of 4 chunks (64 bytes of a row)
-            unsigned char *a_hi = sA + (size_t)buf * 2 * stage_bytes, *a_lo = a_hi + stage_bytes;
-            // a warp instruction covers 8 rows x 4 chunks: 64 contiguous bytes per row from global memory, and per
-            // quarter-warp 128 contiguous bytes of shared memory (conflict-free 16-byte stores)
-            const int nj = 16 * ncg;                                              // (row group, chunk group) pairs
-            for (int j0 = warp; j0 < nj; j0 += 8 * 4) {
-                float4 v[4];
-                int rg[4], ch[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int j = j0 + 8 * u;
-                    rg[u] = j / ncg;
-                    ch[u] = (j - rg[u] * ncg) * 4 + cq;
-                    const long long row = tile * kTcRows + rg[u] * 8 + r8;
-                    v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (j < nj && row < K && ch[u] * 4 < ncol)
-                        v[u] = __ldg(reinterpret_cast<const float4 *>(p.x + row * NI + col0) + ch[u]);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (j0 + 8 * u >= nj || ch[u] * 4 >= ncol) continue;
-                    float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-                    if (p.in_mean) {
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            const float4 b = s_bn[col0 + ch[u] * 4 + q];
-                            e[q] = bn_relu_value(e[q], b.x, b.y, b.z, b.w);
-                        }
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 b = s_bn[col0 + ch * 4 + q];
+                        e[q] = bn_relu_value(e[q], b.x, b.y, b.z, b.w);
                     }
-                    uint32_t hi[4], lo[4];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) split_tf32(e[q], hi[q], lo[q]);
-                    const uint32_t off = (uint32_t)ch[u] * 2048u + (uint32_t)rg[u] * 128u + (uint32_t)r8 * 16u;
-                    *reinterpret_cast<uint4 *>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                    *reinterpret_cast<uint4 *>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                 }
+                uint32_t hi[4], lo[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) split_tf32(e[q], hi[q], lo[q]);
+                const uint32_t off = (uint32_t)ch * 2048u + (uint32_t)rg * 128u + (uint32_t)r8 * 16u;
+                *reinterpret_cast<uint4 *>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4 *>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            tc_fence_before();
-            __syncthreads();
-            if (tid == 0) {
+            tc_mbar_arrive(bar_afull + 8 * buf);
+        };
+#pragma unroll
+        for (int d = 0; d < kTcDepth; ++d) issue(d, v[d]);
+        for (long long j = 0; j < njobs; j += kTcDepth) {
+#pragma unroll
+            for (int d = 0; d < kTcDepth; ++d) {
+                consume(j + d, v[d]);
+                issue(j + d + kTcDepth, v[d]);
+            }
+        }
+    } else if (warp == kTcLoadWarps + kTcEpiWarps) {
+        // ================= MMA issuer: one thread
+        if (lane == 0) {
+            const uint32_t idesc = tc_instr_desc(NOp);
+            for (long long j = 0; j < njobs; ++j) {
+                const long long it = j / nstage;
+                const int s = (int)(j - it * nstage);
+                const int acc = (int)(it & 1), buf = (int)(j & 1);
+                const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
+                if (s == 0 && it >= 2) tc_mbar_wait(bar_cfree + 8 * acc, (uint32_t)((it >> 1) - 1) & 1u);   // epilogue has drained it
+                tc_mbar_wait(bar_afull + 8 * buf, (uint32_t)(j >> 1) & 1u);
                 tc_fence_after();
-                const uint32_t a_hi_u = sA_u + (uint32_t)buf * 2 * stage_bytes, a_lo_u = a_hi_u + stage_bytes;
+                const uint32_t a_hi_u = sA_u + (uint32_t)buf * 2 * kTcStageB, a_lo_u = a_hi_u + kTcStageB;
                 const uint32_t d = tmem_base + (uint32_t)(acc * NOp);
                 for (int k = 0; k < (ncol >> 3); ++k) {                           // K = 8 per instruction: two 16-byte chunks
                     const uint32_t ao = (uint32_t)k * 2 * 2048u;
@@ -336,45 +315,105 @@ k_linear_tc(const __grid_constant__ TcParams p)
                     tc_mma_tf32(d, ah, bl, idesc, 1u);
                     tc_mma_tf32(d, ah, bh, idesc, 1u);
                 }
-                tc_commit(bar_u + 8 * buf);                                       // stage free when these MMAs have read it
-                if (s == nstage - 1) tc_commit(bar_u + 8 * (2 + acc));            // accumulator complete
+                tc_commit(bar_afree + 8 * buf);                                   // stage free when these MMAs have read it
+                if (s == nstage - 1) tc_commit(bar_cfull + 8 * acc);              // accumulator complete
             }
-            ++uses;
         }
-        if (prev_tile >= 0) epilogue(prev_tile, it - 1);
-        prev_tile = tile;
-    }
-    if (prev_tile >= 0) epilogue(prev_tile, it - 1);
-
-    // ---- moments out, tensor memory back
-    if (p.moments) {
-        const int h = warp >> 2, half = NOp >> 1;
+        __syncwarp();
+    } else {
+        // ================= epilogue: TMEM -> registers -> (+ bias, tanh) -> padded slab -> full-line stores, column moments
+        const int q = warp & 3;                                    // TMEM lane quadrant of this warp (warp id % 4)
+        float *slab = s_slab + (size_t)(warp - kTcLoadWarps) * 32 * kTcSlabStride;
+        double m_sum[4] = {0.0, 0.0, 0.0, 0.0}, m_sq[4] = {0.0, 0.0, 0.0, 0.0};   // lane = column g * 32 + lane
+        const int ngrp = NOp >> 5;
+        for (long long it = 0; it < my_tiles; ++it) {
+            const long long tile = blockIdx.x + it * gridDim.x;
+            const int acc = (int)(it & 1);
+            tc_mbar_wait(bar_cfull + 8 * acc, (uint32_t)(it >> 1) & 1u);
+            tc_fence_after();
+            const long long row0 = tile * kTcRows + q * 32;
+            const int nrow = (int)max(0LL, min(32LL, K - row0));   // live rows of this warp's slab
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
-            const int c = h * half + g * 32 + lane;
-            if (g * 32 + lane < half && c < NO) {
-                atomicAdd(p.moments + c, g ? m_sum[1] : m_sum[0]);
-                atomicAdd(p.moments + NO + c, g ? m_sq[1] : m_sq[0]);
+            for (int g = 0; g < 4; ++g) {
+                if (g >= ngrp) break;
+                uint32_t r[32];
+                tc_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * NOp + g * 32), r);
+                tc_ld_wait();
+                if (g == ngrp - 1) {                               // the accumulator has been read completely
+                    tc_fence_before();
+                    tc_mbar_arrive(bar_cfree + 8 * acc);
+                }
+                __syncwarp();                                      // the previous group's slab reads are done
+#pragma unroll
+                for (int i = 0; i < 32; i += 4) {
+                    float o[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        o[c] = __fadd_rn(__uint_as_float(r[i + c]), s_bias[g * 32 + i + c]);
+                        if (p.epi_tanh) o[c] = tanhf(o[c]);
+                    }
+                    *reinterpret_cast<float4 *>(slab + lane * kTcSlabStride + i) = make_float4(o[0], o[1], o[2], o[3]);
+                }
+                __syncwarp();
+                if (p.moments) {
+                    float s1 = 0.0f, s2 = 0.0f;
+                    for (int rr = 0; rr < nrow; ++rr) {
+                        const float t = slab[rr * kTcSlabStride + lane];
+                        s1 += t;
+                        s2 = fmaf(t, t, s2);
+                    }
+                    m_sum[g] += (double)s1;
+                    m_sq[g] += (double)s2;
+                }
+                const int c4 = lane & 7;
+                if ((NO & 3) == 0) {
+                    if (g * 32 + c4 * 4 < NO) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int rr = i * 4 + (lane >> 3);
+                            if (rr < nrow)
+                                *reinterpret_cast<float4 *>(p.y + (row0 + rr) * NO + g * 32 + c4 * 4) =
+                                    *reinterpret_cast<const float4 *>(slab + rr * kTcSlabStride + c4 * 4);
+                        }
+                    }
+                } else if (g * 32 + lane < NO) {                    // odd widths (the 5-wide output layer): lane = column
+                    for (int rr = 0; rr < nrow; ++rr) p.y[(row0 + rr) * NO + g * 32 + lane] = slab[rr * kTcSlabStride + lane];
+                }
+            }
+        }
+        if (p.moments) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int c = g * 32 + lane;
+                if (g < ngrp && c < NO) {
+                    atomicAdd(p.moments + c, m_sum[g]);
+                    atomicAdd(p.moments + NO + c, m_sq[g]);
+                }
             }
         }
     }
+
+    // ---- tensor memory back
     tc_fence_before();
     __syncthreads();
-    if (warp == 0)
+    if (warp == kTcLoadWarps + kTcEpiWarps)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Streams: the first layer (NI = C <= 8 inputs) and the last one (NO = C <= 8 outputs) of the trunk, and the input
-// gradient of the last layer.  Same TcParams; fp32 FMA, weights in shared memory.
+// Stream: the first layer of the trunk (NI = C <= 8 inputs) and the input gradient of the last layer.  Same TcParams;
+// fp32 FMA, weights in shared memory.
 constexpr int kNarrowThreads = 256;
 
-// NI <= 8: thread = (row, four output columns); a row's threads are neighbours, so the stores are contiguous
+// NI <= 8: thread = (row, four output columns); a row's threads are neighbours, so the stores are contiguous.  Four rows
+// are in flight per thread.
+constexpr int kNarrowU = 4;
 __global__ void __launch_bounds__(kNarrowThreads)
 k_linear_narrow_in(const __grid_constant__ TcParams p)
 {
     __shared__ __align__(16) float s_w[8 * kTcMaxDim];               // [c][m]
     __shared__ __align__(16) float s_b[kTcMaxDim];
+    __shared__ float4 s_bn[8];
     __shared__ double s_m[2 * kTcMaxDim];
     const int NI = p.NI, NO = p.NO, tid = threadIdx.x;
     for (int e = tid; e < NI * NO; e += kNarrowThreads) {
@@ -383,6 +422,8 @@ k_linear_narrow_in(const __grid_constant__ TcParams p)
     }
     for (int m = tid; m < NO; m += kNarrowThreads) s_b[m] = p.bias ? __ldg(p.bias + m) : 0.0f;
     for (int m = tid; m < 2 * NO; m += kNarrowThreads) s_m[m] = 0.0;
+    if (p.in_mean && tid < NI)
+        s_bn[tid] = make_float4(__ldg(p.in_mean + tid), __ldg(p.in_invstd + tid), __ldg(p.in_gamma + tid), __ldg(p.in_beta + tid));
     __syncthreads();
     long long K = p.K;
     if (p.k_dev) K = min(K, (long long)*p.k_dev);
@@ -393,20 +434,37 @@ k_linear_narrow_in(const __grid_constant__ TcParams p)
     float ms[4] = {0.f, 0.f, 0.f, 0.f}, mq[4] = {0.f, 0.f, 0.f, 0.f};
     const int m0 = (int)(t0 % gpr) * 4;
     if (t0 < stride) {
-        for (long long e = t0; e < K * gpr; e += stride) {
-            const long long row = e / gpr;
-            float acc[4] = {s_b[m0], s_b[m0 + 1], s_b[m0 + 2], s_b[m0 + 3]};
-            for (int c = 0; c < NI; ++c) {
-                float xv = __ldg(p.x + row * NI + c);
-                if (p.in_mean) xv = bn_relu_value(xv, __ldg(p.in_mean + c), __ldg(p.in_invstd + c), __ldg(p.in_gamma + c), __ldg(p.in_beta + c));
-                const float4 w4 = *reinterpret_cast<const float4 *>(s_w + c * NO + m0);
-                acc[0] = fmaf(xv, w4.x, acc[0]); acc[1] = fmaf(xv, w4.y, acc[1]);
-                acc[2] = fmaf(xv, w4.z, acc[2]); acc[3] = fmaf(xv, w4.w, acc[3]);
+        const long long total = K * gpr;
+        for (long long e0 = t0; e0 < total; e0 += kNarrowU * stride) {
+            float xv[kNarrowU][8];
+#pragma unroll
+            for (int u = 0; u < kNarrowU; ++u) {
+                const long long e = e0 + u * stride;
+                const long long row = e / gpr;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) xv[u][c] = (e < total && c < NI) ? __ldg(p.x + row * NI + c) : 0.0f;
             }
-            if (p.epi_tanh)
-                for (int q = 0; q < 4; ++q) acc[q] = tanhf(acc[q]);
-            *reinterpret_cast<float4 *>(p.y + row * NO + m0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-            for (int q = 0; q < 4; ++q) { ms[q] += acc[q]; mq[q] = fmaf(acc[q], acc[q], mq[q]); }
+#pragma unroll
+            for (int u = 0; u < kNarrowU; ++u) {
+                const long long e = e0 + u * stride;
+                if (e >= total) break;
+                const long long row = e / gpr;
+                float acc[4] = {s_b[m0], s_b[m0 + 1], s_b[m0 + 2], s_b[m0 + 3]};
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    if (c >= NI) break;
+                    float t = xv[u][c];
+                    if (p.in_mean) { const float4 b = s_bn[c]; t = bn_relu_value(t, b.x, b.y, b.z, b.w); }
+                    const float4 w4 = *reinterpret_cast<const float4 *>(s_w + c * NO + m0);
+                    acc[0] = fmaf(t, w4.x, acc[0]); acc[1] = fmaf(t, w4.y, acc[1]);
+                    acc[2] = fmaf(t, w4.z, acc[2]); acc[3] = fmaf(t, w4.w, acc[3]);
+                }
+                if (p.epi_tanh)
+                    for (int q = 0; q < 4; ++q) acc[q] = tanhf(acc[q]);
+                *reinterpret_cast<float4 *>(p.y + row * NO + m0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { ms[q] += acc[q]; mq[q] = fmaf(acc[q], acc[q], mq[q]); }
+            }
         }
     }
     if (p.moments) {
@@ -415,61 +473,6 @@ k_linear_narrow_in(const __grid_constant__ TcParams p)
         for (int m = tid; m < 2 * NO; m += kNarrowThreads) atomicAdd(p.moments + m, s_m[m]);
     }
 }
-
-// NO <= 8: NI / 4 lanes per row (a power of two, 4 .. 32), one float4 of the row each; shuffle reduction
-__global__ void __launch_bounds__(kNarrowThreads)
-k_linear_narrow_out(const __grid_constant__ TcParams p)
-{
-    __shared__ __align__(16) float s_w[8 * kTcMaxDim];               // [m][k]
-    __shared__ float4 s_bn[kTcMaxDim];
-    const int NI = p.NI, NO = p.NO, tid = threadIdx.x;
-    for (int e = tid; e < NI * NO; e += kNarrowThreads) {
-        const int m = e / NI, k = e - m * NI;
-        s_w[m * NI + k] = p.w_layout == 0 ? __ldg(p.w + m * NI + k) : __ldg(p.w + k * NO + m);
-    }
-    if (p.in_mean)
-        for (int k = tid; k < NI; k += kNarrowThreads)
-            s_bn[k] = make_float4(__ldg(p.in_mean + k), __ldg(p.in_invstd + k), __ldg(p.in_gamma + k), __ldg(p.in_beta + k));
-    __syncthreads();
-    long long K = p.K;
-    if (p.k_dev) K = min(K, (long long)*p.k_dev);
-    const int L = NI >> 2;                                             // lanes per row
-    const int sub = tid % L;
-    const long long rows_per_pass = (long long)gridDim.x * kNarrowThreads / L;
-    const bool relu_in = p.in_mean != nullptr;
-    for (long long row = ((long long)blockIdx.x * kNarrowThreads + tid) / L; row < (K + 31) / 32 * 32; row += rows_per_pass) {
-        float4 xv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row < K) xv = __ldg(reinterpret_cast<const float4 *>(p.x + row * NI) + sub);
-        float e[4] = {xv.x, xv.y, xv.z, xv.w};
-        if (relu_in)
-            for (int q = 0; q < 4; ++q) { const float4 b = s_bn[4 * sub + q]; e[q] = bn_relu_value(e[q], b.x, b.y, b.z, b.w); }
-        float acc[8];
-#pragma unroll
-        for (int m = 0; m < 8; ++m) {
-            acc[m] = 0.0f;
-            if (m < NO) {
-                const float4 w4 = *reinterpret_cast<const float4 *>(s_w + m * NI + 4 * sub);
-                acc[m] = fmaf(e[0], w4.x, fmaf(e[1], w4.y, fmaf(e[2], w4.z, e[3] * w4.w)));
-            }
-        }
-        for (int d = L >> 1; d >= 1; d >>= 1)
-#pragma unroll
-            for (int m = 0; m < 8; ++m)
-                if (m < NO) acc[m] += __shfl_xor_sync(0xFFFFFFFFu, acc[m], d);
-        if (row < K) {                                                 // every lane of the row holds all NO totals
-#pragma unroll
-            for (int m = 0; m < 8; ++m) {
-                if (m < NO && (m % L) == sub) {
-                    float v = acc[m];
-                    if (p.bias) v = __fadd_rn(v, __ldg(p.bias + m));
-                    if (p.epi_tanh) v = tanhf(v);
-                    p.y[row * NO + m] = v;
-                }
-            }
-        }
-    }
-}
-
 
 // mean / invstd of a BatchNorm1d from the column moments the producing layer's epilogue accumulated; running statistics
 // like torch (biased variance normalises, the unbiased one is tracked) -- what block 0 of k_bn_relu_fwd does

@@ -1,0 +1,12 @@
+"""a few launches of rpc_linear_fwd (64 -> 128 with BatchNorm prologue + moments, then 128 -> 64) for an ncu capture"""
+import torch
+from robustpointclouds_b200 import ops
+dev = torch.device("cuda:0"); K = 835414
+for NI, NO in [(64, 128), (128, 64)]:
+    x = torch.randn(K, NI, device=dev); w = torch.randn(NO, NI, device=dev) * 0.1; b = torch.randn(NO, device=dev)
+    y = torch.empty(K, NO, device=dev); mom = torch.empty(2 * NO, dtype=torch.float64, device=dev)
+    bn = tuple(torch.rand(NI, device=dev) + 0.5 for _ in range(4))
+    for _ in range(3):
+        ops.linear_fwd(x, w, b, out=y, bn=bn, moments=mom)
+torch.cuda.synchronize()
+print("ok")
