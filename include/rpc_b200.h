@@ -331,6 +331,12 @@ int rpc_attention_gate_bwd(const float *g_out, const float *xn, const float *t, 
  * ------------------------------------------------------------------------------------------------- */
 int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, int N, float *grad_w, float *grad_b,
                      void *stream);
+/* the same with the layer input given as the previous layer's pre-activation: a = relu(batch_norm(a_pre)) with the saved
+ * statistics bn_mean / bn_invstd / bn_gamma / bn_beta [N], recomputed while the operand is staged (all four NULL: a_pre is
+ * the input itself) */
+int rpc_linear_wgrad_bn(const float *g, const float *a_pre, const float *bn_mean, const float *bn_invstd,
+                        const float *bn_gamma, const float *bn_beta, int64_t K, int M, int N, float *grad_w, float *grad_b,
+                        void *stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Training-mode BatchNorm1d + ReLU of the perturber's MLP (third slice of SURVEY 8f row 2;
@@ -373,6 +379,31 @@ int rpc_bn_finalize(const double *moments, int64_t K, const int32_t *k_dev, int 
                     float *running_mean, float *running_var, float *save_mean, float *save_invstd, void *stream);
 int rpc_bn_relu_apply(const float *y, int64_t K, const int32_t *k_dev, int H, const float *mean, const float *invstd,
                       const float *gamma, const float *beta, float *z, void *stream);
+
+/* The whole training-mode trunk in one call each way (the same launches as the per-layer entry points, issued from C):
+ * `self.model(voxel_features_normalized)` of models/adversarial/voxel_perturber.py:176 and its autograd.
+ * nl hidden layers Linear(width[l-1] -> width[l]) + BatchNorm1d + ReLU (width[-1] = C), then Linear(width[nl-1] -> C) + Tanh.
+ *   y[l]   [K, width[l]]  pre-activations, kept for the backward (host array of nl device pointers)
+ *   stats  [2 * sum width] per layer (mean [width], invstd [width]);  scratch: 2 * sum width doubles (forward),
+ *          2 * 128 doubles (backward);  raw [K, C] = the trunk's output
+ *   work   2 * K * max(width, C) floats of scratch for the backward
+ *   grad_w / grad_b [nl + 1], grad_gamma / grad_beta [nl]: host arrays of device pointers, shapes of the parameters
+ *   grad_xn [K, C] or NULL (the normalised input carries no gradient in extract_feat)
+ * Widths: multiples of 8 in 8 .. 128, the last hidden one >= 16; 2 <= K. */
+#define RPC_TRUNK_MAX_HIDDEN 6
+typedef struct rpc_trunk_desc {
+    int32_t C, nl;
+    int32_t width[RPC_TRUNK_MAX_HIDDEN];
+    const float *w[RPC_TRUNK_MAX_HIDDEN + 1], *b[RPC_TRUNK_MAX_HIDDEN + 1];      /* nl + 1 Linear layers */
+    const float *gamma[RPC_TRUNK_MAX_HIDDEN], *beta[RPC_TRUNK_MAX_HIDDEN];
+    float *running_mean[RPC_TRUNK_MAX_HIDDEN], *running_var[RPC_TRUNK_MAX_HIDDEN];    /* may be NULL */
+    float eps[RPC_TRUNK_MAX_HIDDEN], momentum[RPC_TRUNK_MAX_HIDDEN];
+} rpc_trunk_desc;
+int rpc_trunk_fwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, float *stats, double *scratch,
+                  float *raw, void *stream);
+int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, const float *stats, const float *raw,
+                  const float *g_raw, float *work, double *scratch, float *const *grad_w, float *const *grad_b,
+                  float *const *grad_gamma, float *const *grad_beta, float *grad_xn, void *stream);
 
 #ifdef __cplusplus
 }

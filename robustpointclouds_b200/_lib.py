@@ -27,7 +27,7 @@ SYMBOLS = (
     "rpc_voxel_centers", "rpc_points_range_filter", "rpc_points_range_filter_static", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
     "rpc_attention_scratch_bytes", "rpc_attention_gate_fwd", "rpc_attention_gate_bwd", "rpc_linear_wgrad",
     "rpc_bn_scratch_bytes", "rpc_bn_relu_fwd", "rpc_bn_relu_bwd",
-    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply",
+    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply", "rpc_trunk_fwd", "rpc_trunk_bwd", "rpc_linear_wgrad_bn",
 )
 
 
@@ -58,6 +58,18 @@ class PerturbCfg(ctypes.Structure):
         for i, (a, b) in enumerate(zip(eb, fb)):
             c.eb[i], c.fb[i] = float(a), float(b)
         return c
+
+
+RPC_TRUNK_MAX_HIDDEN = 6
+
+
+class TrunkDesc(ctypes.Structure):
+    """``rpc_trunk_desc``: the layers of VoxelPerturber's MLP trunk (voxel_perturber.py:82-103) as device pointers."""
+    _fields_ = [("C", ctypes.c_int32), ("nl", ctypes.c_int32), ("width", ctypes.c_int32 * RPC_TRUNK_MAX_HIDDEN),
+                ("w", ctypes.c_void_p * (RPC_TRUNK_MAX_HIDDEN + 1)), ("b", ctypes.c_void_p * (RPC_TRUNK_MAX_HIDDEN + 1)),
+                ("gamma", ctypes.c_void_p * RPC_TRUNK_MAX_HIDDEN), ("beta", ctypes.c_void_p * RPC_TRUNK_MAX_HIDDEN),
+                ("running_mean", ctypes.c_void_p * RPC_TRUNK_MAX_HIDDEN), ("running_var", ctypes.c_void_p * RPC_TRUNK_MAX_HIDDEN),
+                ("eps", ctypes.c_float * RPC_TRUNK_MAX_HIDDEN), ("momentum", ctypes.c_float * RPC_TRUNK_MAX_HIDDEN)]
 
 
 class RpcError(RuntimeError):
@@ -128,6 +140,7 @@ def lib() -> ctypes.CDLL:
     L.rpc_attention_gate_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp]
     L.rpc_attention_gate_bwd.argtypes = [vp] * 7 + [i64, i32] + [vp] * 8
     L.rpc_linear_wgrad.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp]
+    L.rpc_linear_wgrad_bn.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, i32, vp, vp, vp]
     L.rpc_bn_scratch_bytes.restype = ctypes.c_size_t
     L.rpc_bn_scratch_bytes.argtypes = []
     L.rpc_bn_relu_fwd.argtypes = [vp, i64, i32, vp, vp, ctypes.c_float, ctypes.c_float, vp, vp, vp, vp, vp, vp, vp]
@@ -135,6 +148,9 @@ def lib() -> ctypes.CDLL:
     L.rpc_linear_fwd.argtypes = [vp, i64, vp, i32, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, vp, vp]
     L.rpc_bn_finalize.argtypes = [vp, i64, vp, i32, ctypes.c_float, ctypes.c_float, vp, vp, vp, vp, vp]
     L.rpc_bn_relu_apply.argtypes = [vp, i64, vp, i32, vp, vp, vp, vp, vp, vp]
+    tdp, vpp = ctypes.POINTER(TrunkDesc), ctypes.POINTER(vp)
+    L.rpc_trunk_fwd.argtypes = [tdp, vp, i64, vpp, vp, vp, vp, vp]
+    L.rpc_trunk_bwd.argtypes = [tdp, vp, i64, vpp, vp, vp, vp, vp, vp, vpp, vpp, vpp, vpp, vp, vp]
     L.rpc_profile_enable.restype = None
     L.rpc_profile_enable.argtypes = [i32]
     L.rpc_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_char_p), i32]

@@ -899,9 +899,12 @@ RPC_API int rpc_attention_gate_bwd(const float *g_out, const float *xn, const fl
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
-RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, int N, float *grad_w, float *grad_b,
-                             void *stream)
+RPC_API int rpc_linear_wgrad_bn(const float *g, const float *a, const float *bn_mean, const float *bn_invstd,
+                                const float *bn_gamma, const float *bn_beta, int64_t K, int M, int N, float *grad_w,
+                                float *grad_b, void *stream)
 {
+    if (bn_mean && (!bn_invstd || !bn_gamma || !bn_beta)) return RPC_ERR_NULL;
+    const BnIn bn = {bn_mean, bn_invstd, bn_gamma, bn_beta};
     if (K < 0 || M < 1 || N < 1 || M > 128 || N > 128) return RPC_ERR_CONFIG;
     if (!grad_w) return RPC_ERR_NULL;
     if (K > 0 && (!g || !a)) return RPC_ERR_NULL;
@@ -912,6 +915,7 @@ RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, i
     if (M <= 8 || N <= 8) {
         // skinny layer: a stream over the wide operand; the wider of the two is "wide" (ties: g)
         const bool wide_is_g = M >= N;
+        if (wide_is_g && bn_mean) return RPC_ERR_CONFIG;                // (a prologue on the narrow operand is not needed by the trunk)
         const int W = wide_is_g ? M : N, S = wide_is_g ? N : M;
         const float *wide = wide_is_g ? g : a, *narrow = wide_is_g ? a : g;
         if (S == 4 && misaligned(narrow)) return RPC_ERR_ALIGN;
@@ -920,8 +924,8 @@ RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, i
         if (blocks > (int64_t)device_sms() * 8) blocks = (int64_t)device_sms() * 8;
 #define RPC_CASE(S_)                                                                                                   \
     case S_:                                                                                                           \
-        if (wide_is_g) k_linear_wgrad_skinny<S_, true><<<(int)blocks, kSkinnyThreads, 0, st>>>(wide, narrow, K, W, grad_w, grad_b);   \
-        else k_linear_wgrad_skinny<S_, false><<<(int)blocks, kSkinnyThreads, 0, st>>>(wide, narrow, K, W, grad_w, grad_b);            \
+        if (wide_is_g) k_linear_wgrad_skinny<S_, true><<<(int)blocks, kSkinnyThreads, 0, st>>>(wide, narrow, K, W, grad_w, grad_b, bn);   \
+        else k_linear_wgrad_skinny<S_, false><<<(int)blocks, kSkinnyThreads, 0, st>>>(wide, narrow, K, W, grad_w, grad_b, bn);            \
         break;
         switch (S) {
             RPC_CASE(1) RPC_CASE(2) RPC_CASE(3) RPC_CASE(4) RPC_CASE(5) RPC_CASE(6) RPC_CASE(7) RPC_CASE(8)
@@ -940,12 +944,18 @@ RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, i
         int64_t ctas = (int64_t)device_sms() * per_sm;                                                                \
         const int64_t chunk = ((K + ctas - 1) / ctas + kLinKT - 1) / kLinKT * kLinKT;                                 \
         ctas = (K + chunk - 1) / chunk;                                                                               \
-        k_linear_wgrad<TM_, TN_><<<(int)ctas, LinTile<TM_, TN_>::NT, 0, st>>>(g, a, K, M, N, chunk, grad_w, grad_b);  \
+        k_linear_wgrad<TM_, TN_><<<(int)ctas, LinTile<TM_, TN_>::NT, 0, st>>>(g, a, K, M, N, chunk, grad_w, grad_b, bn);  \
     }
     RPC_CASE(16, 16) RPC_CASE(16, 64) RPC_CASE(16, 128) RPC_CASE(64, 16) RPC_CASE(64, 64) RPC_CASE(64, 128)
     RPC_CASE(128, 16) RPC_CASE(128, 64) RPC_CASE(128, 128)
 #undef RPC_CASE
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_linear_wgrad(const float *g, const float *a, int64_t K, int M, int N, float *grad_w, float *grad_b,
+                             void *stream)
+{
+    return rpc_linear_wgrad_bn(g, a, nullptr, nullptr, nullptr, nullptr, K, M, N, grad_w, grad_b, stream);
 }
 
 // 16-byte columns per thread pay from ~32 M elements up (K = 835 k: 3.7 -> 4.2-4.6 TB/s); below that the kernels are
@@ -1074,6 +1084,114 @@ RPC_API int rpc_bn_relu_apply(const float *y, int64_t K, const int32_t *k_dev, i
     k_bn_relu_apply<<<(int)blocks, kNarrowThreads, 0, static_cast<cudaStream_t>(stream)>>>(y, K, k_dev, H, mean, invstd, gamma,
                                                                                        beta, z);
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ the whole trunk in one call each way
+// The per-layer entry points above issued from Python cost ~15 us of interpreter time each; at the KITTI batch
+// (K = 0.13 M rows) that was twice the kernels' own time.  rpc_trunk_fwd / rpc_trunk_bwd issue the same launches from C.
+namespace {
+__global__ void __launch_bounds__(256)
+k_tanh_bwd(const float *__restrict__ g, const float *__restrict__ t, int64_t n, float *__restrict__ out)
+{
+    for (int64_t e = (int64_t)blockIdx.x * 256 + threadIdx.x; e < n; e += (int64_t)gridDim.x * 256) {
+        const float tv = __ldg(t + e);
+        out[e] = __fmul_rn(__ldg(g + e), __fsub_rn(1.0f, __fmul_rn(tv, tv)));          // ATen's tanh_backward
+    }
+}
+int trunk_check(const rpc_trunk_desc *t)
+{
+    if (!t) return RPC_ERR_NULL;
+    if (t->nl < 1 || t->nl > RPC_TRUNK_MAX_HIDDEN || t->C < 3 || t->C > RPC_MAX_CHANNELS) return RPC_ERR_CONFIG;
+    for (int l = 0; l < t->nl; ++l) {
+        if (t->width[l] < 8 || t->width[l] > kTcMaxDim || (t->width[l] & 7)) return RPC_ERR_CONFIG;
+        if (!t->w[l] || !t->b[l] || !t->gamma[l] || !t->beta[l]) return RPC_ERR_NULL;
+    }
+    if (t->width[t->nl - 1] < 16) return RPC_ERR_CONFIG;
+    if (!t->w[t->nl] || !t->b[t->nl]) return RPC_ERR_NULL;
+    return RPC_OK;
+}
+}  // namespace
+
+extern "C" {
+
+RPC_API int rpc_trunk_fwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, float *stats, double *scratch,
+                          float *raw, void *stream)
+{
+    int rc = trunk_check(t);
+    if (rc != RPC_OK) return rc;
+    if (K < 2) return RPC_ERR_CONFIG;
+    if (!xn || !y || !stats || !scratch || !raw) return RPC_ERR_NULL;
+    const float *x = xn;
+    int ni = t->C;
+    const float *mean = nullptr, *invstd = nullptr, *ga = nullptr, *be = nullptr;
+    float *st_l = stats;
+    for (int l = 0; l < t->nl; ++l) {
+        const int no = t->width[l];
+        if (!y[l]) return RPC_ERR_NULL;
+        rc = rpc_linear_fwd(x, K, nullptr, ni, no, t->w[l], 0, t->b[l], mean, invstd, ga, be, 0, scratch, y[l], stream);
+        if (rc != RPC_OK) return rc;
+        rc = rpc_bn_finalize(scratch, K, nullptr, no, t->eps[l], t->momentum[l], t->running_mean[l], t->running_var[l], st_l,
+                             st_l + no, stream);
+        if (rc != RPC_OK) return rc;
+        mean = st_l; invstd = st_l + no; ga = t->gamma[l]; be = t->beta[l];
+        st_l += 2 * no;
+        scratch += 2 * no;                                         // (a fresh accumulator per layer: no ordering assumptions)
+        x = y[l]; ni = no;
+    }
+    return rpc_linear_fwd(x, K, nullptr, ni, t->C, t->w[t->nl], 0, t->b[t->nl], mean, invstd, ga, be, 1, nullptr, raw, stream);
+}
+
+RPC_API int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, const float *stats,
+                          const float *raw, const float *g_raw, float *work, double *scratch, float *const *grad_w,
+                          float *const *grad_b, float *const *grad_gamma, float *const *grad_beta, float *grad_xn, void *stream)
+{
+    int rc = trunk_check(t);
+    if (rc != RPC_OK) return rc;
+    if (K < 2) return RPC_ERR_CONFIG;
+    if (!xn || !y || !stats || !raw || !g_raw || !work || !scratch || !grad_w || !grad_b || !grad_gamma || !grad_beta) return RPC_ERR_NULL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nl = t->nl, C = t->C;
+    int maxw = C;
+    const float *st_of[RPC_TRUNK_MAX_HIDDEN];
+    {
+        const float *s = stats;
+        for (int l = 0; l < nl; ++l) { st_of[l] = s; s += 2 * t->width[l]; if (t->width[l] > maxw) maxw = t->width[l]; }
+    }
+    float *g_a = work, *g_y = work + (size_t)K * maxw;                                      // two [K, maxw] areas
+    // Tanh, then the output layer: weight gradient against a = relu(bn(y[nl-1])), input gradient
+    {
+        int64_t n = K * C, blocks = (n + 255) / 256;
+        if (blocks > (int64_t)device_sms() * 8) blocks = (int64_t)device_sms() * 8;
+        k_tanh_bwd<<<(int)blocks, 256, 0, st>>>(g_raw, raw, n, g_y);
+        if (cudaPeekAtLastError() != cudaSuccess) return RPC_ERR_CUDA;
+    }
+    const int hl = t->width[nl - 1];
+    rc = rpc_linear_wgrad_bn(g_y, y[nl - 1], st_of[nl - 1], st_of[nl - 1] + hl, t->gamma[nl - 1], t->beta[nl - 1], K, C, hl,
+                             grad_w[nl], grad_b[nl], stream);
+    if (rc != RPC_OK) return rc;
+    rc = rpc_linear_fwd(g_y, K, nullptr, C, hl, t->w[nl], 1, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, g_a, stream);
+    if (rc != RPC_OK) return rc;
+    for (int l = nl - 1; l >= 0; --l) {
+        const int h = t->width[l], hin = l > 0 ? t->width[l - 1] : C;
+        rc = rpc_bn_relu_bwd(g_a, y[l], st_of[l], st_of[l] + h, t->gamma[l], t->beta[l], K, h, scratch, g_y, grad_gamma[l],
+                             grad_beta[l], stream);
+        if (rc != RPC_OK) return rc;
+        // (the layer input relu(bn(y[l-1])) is recomputed while the weight-gradient kernel stages it)
+        if (l > 0)
+            rc = rpc_linear_wgrad_bn(g_y, y[l - 1], st_of[l - 1], st_of[l - 1] + hin, t->gamma[l - 1], t->beta[l - 1], K, h, hin,
+                                     grad_w[l], grad_b[l], stream);
+        else
+            rc = rpc_linear_wgrad(g_y, xn, K, h, C, grad_w[l], grad_b[l], stream);
+        if (rc != RPC_OK) return rc;
+        float *dst = l > 0 ? g_a : grad_xn;
+        if (dst) {
+            rc = rpc_linear_fwd(g_y, K, nullptr, h, hin, t->w[l], 1, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, dst, stream);
+            if (rc != RPC_OK) return rc;
+        }
+    }
+    return RPC_OK;
 }
 
 }  // extern "C"

@@ -16,6 +16,15 @@ namespace rpc {
 
 constexpr int kLinKT = 16;                      // rows per shared-memory tile
 
+// optional prologue on the layer input: a = relu(batch_norm(a_pre)) with saved statistics, applied while the operand is
+// staged (the trunk keeps only pre-activations between forward and backward; operation order of k_bn_relu_fwd)
+struct BnIn { const float *mean, *invstd, *gamma, *beta; };
+__device__ __forceinline__ float lin_bn_relu(float x, const float4 &b)
+{
+    const float t = __fadd_rn(__fmul_rn(__fmul_rn(__fsub_rn(x, b.x), b.y), b.z), b.w);
+    return t < 0.0f ? 0.0f : t;
+}
+
 // thread tiling: 8 x 8 accumulators per thread where the tile is at least 64 wide (4 LDS.128 per 64 FMAs), 2 where it is 16
 template <int TM, int TN> struct LinTile {
     static constexpr int RM = TM >= 64 ? 8 : 2, RN = TN >= 64 ? 8 : 2;
@@ -36,13 +45,21 @@ __device__ __forceinline__ int lin_col(int t, int c)
 template <int TM, int TN>
 __global__ void __launch_bounds__(LinTile<TM, TN>::NT)
 k_linear_wgrad(const float *__restrict__ g, const float *__restrict__ a, int64_t K, int M, int N, int64_t chunk,
-               float *__restrict__ gw, float *__restrict__ gb)
+               float *__restrict__ gw, float *__restrict__ gb, const BnIn bn)
 {
     using T = LinTile<TM, TN>;
     constexpr int RM = T::RM, RN = T::RN, NT = T::NT;
     __shared__ __align__(16) float sg[kLinKT][TM];
     __shared__ __align__(16) float sa[kLinKT][TN];
+    __shared__ float4 s_bn[TN];
     const int tid = threadIdx.x, ty = tid / T::TXD, tx = tid % T::TXD;
+    const bool has_bn = bn.mean != nullptr;
+    if (has_bn) {
+        for (int n = tid; n < TN; n += NT)
+            s_bn[n] = n < N ? make_float4(__ldg(bn.mean + n), __ldg(bn.invstd + n), __ldg(bn.gamma + n), __ldg(bn.beta + n))
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+    }
     const int64_t r0 = (int64_t)blockIdx.x * chunk, r1 = min(r0 + chunk, K);
     float acc[RM][RN], bs[RM];
 #pragma unroll
@@ -79,10 +96,19 @@ k_linear_wgrad(const float *__restrict__ g, const float *__restrict__ a, int64_t
                 const int e = tid + q * NT;
                 if (e < T::G4) reinterpret_cast<float4 *>(&sg[0][0])[e] = pg[q];
             }
+            const int rows_v = (int)min((int64_t)kLinKT, r1 - row);
 #pragma unroll
             for (int q = 0; q < T::AV; ++q) {
                 const int e = tid + q * NT;
-                if (e < T::A4) reinterpret_cast<float4 *>(&sa[0][0])[e] = pa[q];
+                if (e < T::A4) {
+                    float4 v = pa[q];
+                    if (has_bn && e < rows_v * TN / 4) {                 // (rows beyond the chunk stay zero)
+                        const int n = (e * 4) % TN;
+                        v.x = lin_bn_relu(v.x, s_bn[n]); v.y = lin_bn_relu(v.y, s_bn[n + 1]);
+                        v.z = lin_bn_relu(v.z, s_bn[n + 2]); v.w = lin_bn_relu(v.w, s_bn[n + 3]);
+                    }
+                    reinterpret_cast<float4 *>(&sa[0][0])[e] = v;
+                }
             }
         } else {
             const int rows = (int)min((int64_t)kLinKT, r1 - row);
@@ -92,7 +118,9 @@ k_linear_wgrad(const float *__restrict__ g, const float *__restrict__ a, int64_t
             }
             for (int e = tid; e < kLinKT * TN; e += NT) {
                 const int kk = e / TN, n = e % TN;
-                sa[kk][n] = (kk < rows && n < N) ? __ldg(a + (row + kk) * N + n) : 0.0f;
+                float v = (kk < rows && n < N) ? __ldg(a + (row + kk) * N + n) : 0.0f;
+                if (has_bn && kk < rows && n < N) v = lin_bn_relu(v, s_bn[n]);
+                sa[kk][n] = v;
             }
         }
         __syncthreads();
@@ -148,10 +176,13 @@ constexpr int kSkinnyThreads = 256;
 template <int S, bool WIDE_IS_G>
 __global__ void __launch_bounds__(kSkinnyThreads)
 k_linear_wgrad_skinny(const float *__restrict__ wide, const float *__restrict__ narrow, int64_t K, int W,
-                      float *__restrict__ gw, float *__restrict__ gb)
+                      float *__restrict__ gw, float *__restrict__ gb, const BnIn bn)
 {
     const int groups = kSkinnyThreads / W;                          // rows taken per CTA iteration
     const int tid = threadIdx.x, r = tid / W, j = tid - r * W;
+    const bool has_bn = !WIDE_IS_G && bn.mean != nullptr;           // the layer input is the wide operand
+    float4 bj = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (has_bn && r < groups) bj = make_float4(__ldg(bn.mean + j), __ldg(bn.invstd + j), __ldg(bn.gamma + j), __ldg(bn.beta + j));
     float acc[S], colsum = 0.0f, nsum[S];
 #pragma unroll
     for (int s = 0; s < S; ++s) { acc[s] = 0.0f; nsum[s] = 0.0f; }
@@ -165,6 +196,7 @@ k_linear_wgrad_skinny(const float *__restrict__ wide, const float *__restrict__ 
                 const int64_t k = k0 + u * stride;
                 const bool ok = k < K;
                 w[u] = ok ? __ldg(wide + k * W + j) : 0.0f;
+                if (has_bn && ok) w[u] = lin_bn_relu(w[u], bj);
                 if constexpr (S == 4) {
                     const float4 t = ok ? __ldg(reinterpret_cast<const float4 *>(narrow) + k) : make_float4(0.f, 0.f, 0.f, 0.f);
                     nv[u][0] = t.x; nv[u][1] = t.y; nv[u][2] = t.z; nv[u][3] = t.w;

@@ -505,6 +505,77 @@ def bn_relu_apply(y: torch.Tensor, mean: torch.Tensor, invstd: torch.Tensor, gam
     return z
 
 
+def _ptr_array(tensors):
+    arr = (ctypes.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr
+
+
+def trunk_desc(C: int, widths: Sequence[int], weights, biases, gammas, betas, running_means, running_vars, eps, momentum):
+    """``rpc_trunk_desc`` of a trunk with ``len(widths)`` hidden layers; the tensors must stay alive while it is used."""
+    d = _lib.TrunkDesc()
+    d.C, d.nl = int(C), len(widths)
+    for l, h in enumerate(widths):
+        d.width[l] = int(h)
+        d.gamma[l], d.beta[l] = gammas[l].data_ptr(), betas[l].data_ptr()
+        d.running_mean[l] = None if running_means[l] is None else running_means[l].data_ptr()
+        d.running_var[l] = None if running_vars[l] is None else running_vars[l].data_ptr()
+        d.eps[l], d.momentum[l] = float(eps[l]), float(momentum[l])
+    for l in range(len(widths) + 1):
+        d.w[l], d.b[l] = weights[l].data_ptr(), biases[l].data_ptr()
+    return d
+
+
+def trunk_fwd(desc, xn: torch.Tensor, widths: Sequence[int]):
+    """Training-mode forward of the whole trunk (``rpc_trunk_fwd``): -> (raw [K, C], ybuf, ys, stats).  ``ys[l]`` [K, widths[l]]
+    are the pre-activations (views of the flat ``ybuf``), ``stats`` the per-layer (mean, invstd) the backward needs."""
+    dev = _need_cuda(xn)
+    K, C = xn.shape
+    tot = sum(widths)
+    ybuf = torch.empty((K * tot,), dtype=torch.float32, device=dev)
+    ys, o = [], 0
+    for h in widths:
+        ys.append(ybuf[o:o + K * h].view(K, h))
+        o += K * h
+    stats = torch.empty((2 * tot,), dtype=torch.float32, device=dev)
+    scratch = torch.empty((2 * tot,), dtype=torch.float64, device=dev)
+    raw = torch.empty((K, C), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_trunk_fwd(ctypes.byref(desc), _ptr(xn), K, _ptr_array(ys), _ptr(stats), _ptr(scratch), _ptr(raw), _stream(dev))
+    _lib.check(st, "rpc_trunk_fwd")
+    return raw, ybuf, ys, stats
+
+
+def trunk_bwd(desc, xn: torch.Tensor, widths: Sequence[int], ys, stats: torch.Tensor, raw: torch.Tensor, g_raw: torch.Tensor,
+              param_shapes, want_grad_xn: bool = False):
+    """Backward of ``trunk_fwd`` (``rpc_trunk_bwd``): -> (grad_w list, grad_b list, grad_gamma list, grad_beta list, grad_xn)."""
+    dev = _need_cuda(xn, g_raw)
+    K, C = xn.shape
+    g_raw = _f32c(g_raw)
+    maxw = max(max(widths), C)
+    work = torch.empty((2 * K * maxw,), dtype=torch.float32, device=dev)
+    scratch = torch.empty((2 * 128,), dtype=torch.float64, device=dev)
+    nl = len(widths)
+    n_w = sum(a * b for a, b in param_shapes)
+    flat = torch.empty((n_w + sum(a for a, _ in param_shapes) + 2 * sum(widths),), dtype=torch.float32, device=dev)
+    gw, gb, gg, gbe, o = [], [], [], [], 0
+    for a, b in param_shapes:
+        gw.append(flat[o:o + a * b].view(a, b)); o += a * b
+    for a, _ in param_shapes:
+        gb.append(flat[o:o + a]); o += a
+    for h in widths:
+        gg.append(flat[o:o + h]); o += h
+    for h in widths:
+        gbe.append(flat[o:o + h]); o += h
+    gxn = torch.empty_like(xn) if want_grad_xn else None
+    st = _lib.lib().rpc_trunk_bwd(ctypes.byref(desc), _ptr(xn), K, _ptr_array(ys), _ptr(stats), _ptr(raw), _ptr(g_raw), _ptr(work),
+                                  _ptr(scratch), _ptr_array(gw), _ptr_array(gb), _ptr_array(gg), _ptr_array(gbe), _ptr(gxn),
+                                  _stream(dev))
+    _lib.check(st, "rpc_trunk_bwd")
+    assert nl == len(gg)
+    return gw, gb, gg, gbe, gxn
+
+
 def bn_relu_fwd(y: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, momentum: float,
                 running_mean: Optional[torch.Tensor] = None, running_var: Optional[torch.Tensor] = None):
     """Training-mode ``relu(batch_norm(y))`` for y [K, H], H <= 128 (nn.BatchNorm1d -> nn.ReLU of

@@ -214,68 +214,60 @@ class _TrunkFn(torch.autograd.Function):
     streams) for the forward and the input gradients, the BatchNorm + ReLU of layer l applied while layer l + 1 loads its
     input, the batch statistics accumulated in the producing layer's epilogue (``rpc_bn_finalize``), ``rpc_bn_relu_bwd``
     and ``rpc_linear_wgrad`` in the backward.  Only the pre-activations y_l are kept between forward and backward; the
-    normalised activations are recomputed (``rpc_bn_relu_apply``) where the weight gradient needs them.
-    ``params`` = (W0, b0, gamma0, beta0, ..., W4, b4, gamma4, beta4, W5, b5)."""
+    normalised activations are recomputed (``rpc_bn_relu_apply``) where the weight gradient needs them.  One C call each
+    way (``rpc_trunk_fwd`` / ``rpc_trunk_bwd``): issued layer by layer from Python the launches cost twice the kernels'
+    own time at the KITTI batch.  ``params`` = (W0, b0, gamma0, beta0, ..., W4, b4, gamma4, beta4, W5, b5)."""
 
     @staticmethod
     def forward(ctx, xn, bns, *params):
-        K = xn.shape[0]
-        x, bn, ys, stats = xn.contiguous(), None, [], []
         nl = len(bns)
-        for l in range(nl):
-            W, b, ga, be = params[4 * l:4 * l + 4]
-            mom = torch.empty((2 * W.shape[0],), dtype=torch.float64, device=xn.device)
-            y = ops.linear_fwd(x, W, b, bn=bn, moments=mom)
-            m = bns[l]
-            mean, invstd = ops.bn_finalize(mom, K, m.eps, m.momentum, m.running_mean, m.running_var)
-            m.num_batches_tracked.add_(1)
-            bn = (mean, invstd, ga, be)
-            ys.append(y)
-            stats += [mean, invstd]
-            x = y
-        W, b = params[4 * nl:4 * nl + 2]
-        raw = ops.linear_fwd(x, W, b, bn=bn, tanh=True)
-        ctx.save_for_backward(xn, raw, *ys, *stats, *params)
-        ctx.nl = nl
+        xn = xn.contiguous()
+        widths = [int(params[4 * l].shape[0]) for l in range(nl)]
+        desc = ops.trunk_desc(xn.shape[1], widths, [params[4 * l] for l in range(nl)] + [params[4 * nl]],
+                              [params[4 * l + 1] for l in range(nl)] + [params[4 * nl + 1]],
+                              [params[4 * l + 2] for l in range(nl)], [params[4 * l + 3] for l in range(nl)],
+                              [m.running_mean for m in bns], [m.running_var for m in bns], [m.eps for m in bns],
+                              [m.momentum for m in bns])
+        raw, ybuf, ys, stats = ops.trunk_fwd(desc, xn, widths)
+        torch._foreach_add_([m.num_batches_tracked for m in bns], 1)
+        ctx.save_for_backward(xn, raw, ybuf, stats, *params)
+        ctx.nl, ctx.widths, ctx.bns = nl, widths, bns
         return raw
 
     @staticmethod
     def backward(ctx, g_raw):
-        nl = ctx.nl
-        saved = ctx.saved_tensors
-        xn, raw = saved[0], saved[1]
-        ys, stats, params = saved[2:2 + nl], saved[2 + nl:2 + 3 * nl], saved[2 + 3 * nl:]
-        grads = [None] * len(params)
-        g = g_raw * (1.0 - raw * raw)                              # Tanh
-        W, _ = params[4 * nl:4 * nl + 2]
-        bn_of = lambda l: (stats[2 * l], stats[2 * l + 1], params[4 * l + 2], params[4 * l + 3])   # noqa: E731
-        a = ops.bn_relu_apply(ys[nl - 1], *bn_of(nl - 1))
-        grads[4 * nl], grads[4 * nl + 1] = ops.linear_wgrad(g, a)
-        g_a = ops.linear_fwd(g, W, transposed=True)
-        g_xn = None
-        for l in range(nl - 1, -1, -1):
-            W = params[4 * l]
-            g_y, gg, gb = ops.bn_relu_bwd(g_a, ys[l], *bn_of(l))
-            a = xn if l == 0 else ops.bn_relu_apply(ys[l - 1], *bn_of(l - 1), out=a if a.shape == ys[l - 1].shape else None)
-            grads[4 * l], grads[4 * l + 1] = ops.linear_wgrad(g_y, a)
-            grads[4 * l + 2], grads[4 * l + 3] = gg, gb
-            if l > 0:
-                g_a = ops.linear_fwd(g_y, W, transposed=True)
-            elif ctx.needs_input_grad[0]:
-                g_xn = ops.linear_fwd(g_y, W, transposed=True)
+        nl, widths = ctx.nl, ctx.widths
+        xn, raw, ybuf, stats = ctx.saved_tensors[:4]
+        params = ctx.saved_tensors[4:]
+        K = xn.shape[0]
+        ys, o = [], 0
+        for h in widths:
+            ys.append(ybuf[o:o + K * h].view(K, h))
+            o += K * h
+        bns = ctx.bns
+        desc = ops.trunk_desc(xn.shape[1], widths, [params[4 * l] for l in range(nl)] + [params[4 * nl]],
+                              [params[4 * l + 1] for l in range(nl)] + [params[4 * nl + 1]],
+                              [params[4 * l + 2] for l in range(nl)], [params[4 * l + 3] for l in range(nl)],
+                              [None] * nl, [None] * nl, [m.eps for m in bns], [m.momentum for m in bns])
+        shapes = [tuple(params[4 * l].shape) for l in range(nl)] + [tuple(params[4 * nl].shape)]
+        gw, gb, gg, gbe, g_xn = ops.trunk_bwd(desc, xn, widths, ys, stats, raw, g_raw, shapes, ctx.needs_input_grad[0])
+        grads = []
+        for l in range(nl):
+            grads += [gw[l], gb[l], gg[l], gbe[l]]
+        grads += [gw[nl], gb[nl]]
         return (g_xn, None, *grads)
 
 
 def _trunk_supported(model: nn.Sequential, x: torch.Tensor) -> bool:
-    """the layer widths the tensor-core / stream kernels take (rpc_linear_fwd): C <= 8, hidden widths multiples of 8 up
-    to 128 (16 .. 128 for the layer in front of the output)"""
+    """the layer widths rpc_trunk_fwd / rpc_trunk_bwd take: C <= 8, hidden widths multiples of 8 up to 128 (at least 16
+    next to the input and the output)"""
     lin = [m for m in model if isinstance(m, nn.Linear)]
     if len(lin) != 6 or not (x.is_cuda and x.dim() == 2 and x.dtype == torch.float32 and x.shape[0] >= 2):
         return False
     C = lin[0].in_features
     hs = [m.out_features for m in lin[:-1]]
     return (3 <= C <= 8 and lin[-1].out_features == C and all(h % 8 == 0 and 8 <= h <= 128 for h in hs)
-            and hs[-1] in (16, 32, 64, 128))
+            and hs[0] >= 16 and hs[-1] >= 16)
 
 
 def _gradient_hook(grad):
