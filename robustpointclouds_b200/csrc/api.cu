@@ -1036,6 +1036,7 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
     p.x = x; p.w = w; p.bias = bias; p.y = y; p.k_dev = k_dev; p.K = K; p.NI = NI; p.NO = NO; p.w_layout = w_layout;
     p.in_mean = in_mean; p.in_invstd = in_invstd; p.in_gamma = in_gamma; p.in_beta = in_beta;
     p.epi_tanh = epi_tanh; p.moments = moments;
+    { static const char *dbg = getenv("RPC_TC_DBG"); p.dbg = dbg ? atoi(dbg) : 0; }
     const int sms = device_sms();
     if (NI <= 8) {                                                   // first layer / input gradient of the last: a stream
         if (NO & 3) return RPC_ERR_CONFIG;
@@ -1045,13 +1046,14 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
     } else {                                                         // (the last layer, NO = C, also goes here: N padded to 32)
         if (NI & 7) return RPC_ERR_CONFIG;
         const int NOp = (NO + 31) & ~31;
-        const size_t smem = tc_smem_bytes(NI, NOp) + 128;
+        const size_t smem = tc_smem_bytes(NI, NOp);
+        constexpr size_t kSmemMax = 227 * 1024;                        // per CTA on sm_100
+        if (smem > kSmemMax) return RPC_ERR_CONFIG;                    // (128 -> 128: the weights alone take 128 KB)
         static bool attr_done[64] = {};
         int dev = 0;
         cudaGetDevice(&dev);
-        if (dev >= 0 && dev < 64 && !attr_done[dev]) {                // the largest case: 128 x 128 weights
-            if (cudaFuncSetAttribute(k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)(tc_smem_bytes(kTcMaxDim, kTcMaxDim) + 128)) != cudaSuccess)
+        if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+            if (cudaFuncSetAttribute(k_linear_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax) != cudaSuccess)
                 return RPC_ERR_CUDA;
             attr_done[dev] = true;
         }

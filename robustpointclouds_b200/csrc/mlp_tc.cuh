@@ -13,14 +13,14 @@
 //
 // One persistent CTA per SM, 13 warps with fixed roles that meet only at mbarriers:
 //   * the weight matrix is split once into hi / lo and kept in shared memory in the tcgen05 K-major canonical layout
-//     without swizzle (8 x 16-byte core matrices; SBO = 128 B between 8-row groups, LBO between 16-byte K chunks);
+//     with 128-byte swizzle (rows of 32 TF32, 8-row groups 1024 bytes apart);
 //   * 8 loader warps bring 128 rows x 32 columns of X per stage through registers (optional fused prologue: the
 //     previous layer's BatchNorm + ReLU, x' = relu((x - mean) * invstd * gamma + beta), so the normalised activation never
 //     exists in HBM), split them and store hi / lo into one of two shared-memory stages; four stage loads stay in flight
 //     per thread (64 KB per SM);
 //   * one thread issues the 3 x (columns / 8) tcgen05.mma (M = 128, N = NO, K = 8) of a stage into one of two TMEM
 //     accumulators and commits to the "stage free" / "accumulator full" mbarriers;
-//   * 4 epilogue warps (one per TMEM lane quadrant) take the finished accumulator 32 columns at a time:
+//   * 8 epilogue warps (two per TMEM lane quadrant, alternate 32-column groups) take the finished accumulator:
 //     tcgen05.ld -> + bias [-> tanh] -> a padded per-warp slab in shared memory -> full 128-byte lines to global memory,
 //     and, lane = column, the per-column sum / sum of squares the next BatchNorm needs (no shuffles).
 // The first version (all warps doing load -> MMA -> epilogue in turn) ran at 1.2 TB/s: profiles/r02_linear_tc.txt.
@@ -45,6 +45,7 @@ struct TcParams {
     const float *in_mean, *in_invstd, *in_gamma, *in_beta;   // [NI] each or NULL: prologue x' = relu(bn(x)), the
                                                  // previous layer's BatchNorm + ReLU in k_bn_relu_fwd's operation order
     int epi_tanh;                                // epilogue: y = tanh(y)
+    int dbg;                                     // experiments (RPC_TC_DBG): 1 = one MMA per K step instead of three, 2 = none
     double *moments;                             // [2 * NO] or NULL: += column sums and sums of squares of y
 };
 
@@ -63,12 +64,14 @@ __device__ __forceinline__ void split_tf32(float v, uint32_t &hi, uint32_t &lo)
     lo = to_tf32(__fsub_rn(v, __uint_as_float(hi)));
 }
 
-// shared-memory matrix descriptor, K-major, no swizzle: start address, leading (K chunk) and stride (8-row group)
-// byte offsets in 16-byte units, descriptor version 1 (sm_100)
-__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+// shared-memory matrix descriptor, K-major, 128-byte swizzle: rows of 32 TF32 (128 bytes), 8-row groups 1024 bytes apart
+// (SBO), the 16-byte chunk c of row r stored at chunk position c ^ (r & 7); the start address may be advanced by 32
+// bytes per K = 8 step inside the row (the hardware applies the XOR to the address bits); descriptor version 1 (sm_100).
+// The first version of this kernel used the unswizzled "interleaved" layout: correct, but every tcgen05.mma then
+// occupied the tensor pipe for ~2 cycles per output column, four times the swizzled rate (profiles/r02_linear_tc.txt).
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr)
 {
-    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
-           (1ull << 46);
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 // instruction descriptor: D = fp32, A = B = TF32, both K-major, M = 128, N = n
 __device__ __forceinline__ uint32_t tc_instr_desc(int n)
@@ -141,11 +144,11 @@ __device__ __forceinline__ void tc_mbar_arrive(uint32_t bar)
 }
 
 // ---- layout of k_linear_tc's dynamic shared memory
-//   B hi, B lo          2 x NOp x NI x 4 bytes, chunk-major canonical layout (LBO = NOp * 16, SBO = 128)
-//   X stages            2 x (hi, lo) x 128 rows x 32 columns x 4 bytes = 64 KB (LBO = 2048, SBO = 128)
-//   epilogue slabs      4 warps x 32 rows x 36 floats (padded rows: conflict-free 16-byte writes by row and reads by column)
+//   B hi, B lo          2 x ceil(NI / 32) blocks of NOp rows x 128 bytes (32 columns of K), 128-byte swizzle
+//   X stages            2 x (hi, lo) x 128 rows x 128 bytes (32 columns) = 64 KB, 128-byte swizzle
+//   epilogue slabs      8 warps x 32 rows x 36 floats (padded rows: conflict-free 16-byte writes by row and reads by column)
 //   BatchNorm constants of the prologue (float4 per input column), bias, 8 mbarriers, the TMEM base address
-constexpr int kTcLoadWarps = 8, kTcEpiWarps = 4;
+constexpr int kTcLoadWarps = 8, kTcEpiWarps = 8;               // (two epilogue warps per TMEM lane quadrant)
 constexpr int kTcLoaders = kTcLoadWarps * 32;
 constexpr int kTcThreads2 = (kTcLoadWarps + kTcEpiWarps + 1) * 32;     // + the MMA warp
 constexpr int kTcSC = 32;                                              // columns of X per stage
@@ -155,18 +158,20 @@ constexpr int kTcDepth = 4;                                            // stage 
 
 __host__ __device__ inline size_t tc_smem_bytes(int NI, int NOp)
 {
-    return 2 * (size_t)NOp * NI * 4 + 4 * (size_t)kTcStageB + (size_t)kTcEpiWarps * 32 * kTcSlabStride * 4 +
-           (size_t)kTcMaxDim * 16 + kTcMaxDim * 4 + 8 * 8 + 16;
+    return 2 * (size_t)((NI + kTcSC - 1) / kTcSC) * NOp * 128 + 4 * (size_t)kTcStageB + (size_t)kTcEpiWarps * 32 * kTcSlabStride * 4 +
+           (size_t)kTcMaxDim * 16 + kTcMaxDim * 4 + 8 * 8 + 16 + 1024;               // (+ 1024: the swizzle atoms need that alignment)
 }
 
 __global__ void __launch_bounds__(kTcThreads2, 1)
 k_linear_tc(const __grid_constant__ TcParams p)
 {
-    extern __shared__ __align__(128) unsigned char tc_sm[];
+    extern __shared__ __align__(1024) unsigned char tc_sm_raw[];
+    unsigned char *tc_sm = tc_sm_raw + ((1024u - (smem_u32(tc_sm_raw) & 1023u)) & 1023u);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int NI = p.NI, NO = p.NO;
     const int NOp = (NO + 31) & ~31;                               // N of the MMA (16 | N at M = 128; 32-column epilogue groups)
-    const uint32_t wbytes = (uint32_t)NOp * NI * 4;
+    const uint32_t wblock = (uint32_t)NOp * 128;                    // one 32-column block of B
+    const uint32_t wbytes = (uint32_t)((NI + kTcSC - 1) / kTcSC) * wblock;
     unsigned char *sB = tc_sm;
     unsigned char *sA = tc_sm + 2 * wbytes;
     float *s_slab = reinterpret_cast<float *>(sA + 4 * kTcStageB);
@@ -216,7 +221,7 @@ k_linear_tc(const __grid_constant__ TcParams p)
             }
             uint32_t hi[4], lo[4];
             for (int q = 0; q < 4; ++q) split_tf32(v[q], hi[q], lo[q]);
-            const uint32_t off = (uint32_t)c * (NOp * 16) + (uint32_t)(n >> 3) * 128 + (uint32_t)(n & 7) * 16;
+            const uint32_t off = (uint32_t)(c >> 3) * wblock + (uint32_t)n * 128 + (uint32_t)(((c & 7) ^ (n & 7)) * 16);
             *reinterpret_cast<uint4 *>(sB + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4 *>(sB + wbytes + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
         }
@@ -275,7 +280,7 @@ k_linear_tc(const __grid_constant__ TcParams p)
                 uint32_t hi[4], lo[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) split_tf32(e[q], hi[q], lo[q]);
-                const uint32_t off = (uint32_t)ch * 2048u + (uint32_t)rg * 128u + (uint32_t)r8 * 16u;
+                const uint32_t off = (uint32_t)(rg * 8 + r8) * 128u + (uint32_t)((ch ^ r8) * 16);
                 *reinterpret_cast<uint4 *>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                 *reinterpret_cast<uint4 *>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
@@ -305,15 +310,17 @@ k_linear_tc(const __grid_constant__ TcParams p)
                 tc_fence_after();
                 const uint32_t a_hi_u = sA_u + (uint32_t)buf * 2 * kTcStageB, a_lo_u = a_hi_u + kTcStageB;
                 const uint32_t d = tmem_base + (uint32_t)(acc * NOp);
-                for (int k = 0; k < (ncol >> 3); ++k) {                           // K = 8 per instruction: two 16-byte chunks
-                    const uint32_t ao = (uint32_t)k * 2 * 2048u;
-                    const uint32_t bo = (uint32_t)((col0 >> 2) + 2 * k) * (uint32_t)(NOp * 16);
-                    const uint64_t ah = tc_smem_desc(a_hi_u + ao, 2048u, 128u), al = tc_smem_desc(a_lo_u + ao, 2048u, 128u);
-                    const uint64_t bh = tc_smem_desc(sB_u + bo, (uint32_t)NOp * 16u, 128u);
-                    const uint64_t bl = tc_smem_desc(sB_u + wbytes + bo, (uint32_t)NOp * 16u, 128u);
-                    tc_mma_tf32(d, al, bh, idesc, (s | k) ? 1u : 0u);             // small terms first
-                    tc_mma_tf32(d, ah, bl, idesc, 1u);
-                    tc_mma_tf32(d, ah, bh, idesc, 1u);
+                for (int k = 0; k < (ncol >> 3); ++k) {                           // K = 8 per instruction: 32 bytes of every row
+                    const uint32_t ko = (uint32_t)k * 32u, bo = (uint32_t)s * wblock + ko;
+                    const uint64_t ah = tc_smem_desc(a_hi_u + ko), al = tc_smem_desc(a_lo_u + ko);
+                    const uint64_t bh = tc_smem_desc(sB_u + bo), bl = tc_smem_desc(sB_u + wbytes + bo);
+                    if (p.dbg == 0) {
+                        tc_mma_tf32(d, al, bh, idesc, (s | k) ? 1u : 0u);         // small terms first
+                        tc_mma_tf32(d, ah, bl, idesc, 1u);
+                        tc_mma_tf32(d, ah, bh, idesc, 1u);
+                    } else if (p.dbg == 1) {
+                        tc_mma_tf32(d, ah, bh, idesc, (s | k) ? 1u : 0u);
+                    }
                 }
                 tc_commit(bar_afree + 8 * buf);                                   // stage free when these MMAs have read it
                 if (s == nstage - 1) tc_commit(bar_cfull + 8 * acc);              // accumulator complete
@@ -323,8 +330,9 @@ k_linear_tc(const __grid_constant__ TcParams p)
     } else {
         // ================= epilogue: TMEM -> registers -> (+ bias, tanh) -> padded slab -> full-line stores, column moments
         const int q = warp & 3;                                    // TMEM lane quadrant of this warp (warp id % 4)
+        const int half = (warp - kTcLoadWarps) >> 2;               // the quadrant's two warps take alternate column groups
         float *slab = s_slab + (size_t)(warp - kTcLoadWarps) * 32 * kTcSlabStride;
-        double m_sum[4] = {0.0, 0.0, 0.0, 0.0}, m_sq[4] = {0.0, 0.0, 0.0, 0.0};   // lane = column g * 32 + lane
+        double m_sum[2] = {0.0, 0.0}, m_sq[2] = {0.0, 0.0};        // lane = column (2 * u + half) * 32 + lane
         const int ngrp = NOp >> 5;
         for (long long it = 0; it < my_tiles; ++it) {
             const long long tile = blockIdx.x + it * gridDim.x;
@@ -333,37 +341,41 @@ k_linear_tc(const __grid_constant__ TcParams p)
             tc_fence_after();
             const long long row0 = tile * kTcRows + q * 32;
             const int nrow = (int)max(0LL, min(32LL, K - row0));   // live rows of this warp's slab
+            uint32_t r[2][32];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
+            for (int u = 0; u < 2; ++u) {                          // all of this warp's columns first: the accumulator is
+                const int g = 2 * u + half;                        // released before the slab work starts
+                if (g < ngrp) tc_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * NOp + g * 32), r[u]);
+            }
+            tc_ld_wait();
+            tc_fence_before();
+            tc_mbar_arrive(bar_cfree + 8 * acc);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int g = 2 * u + half;
                 if (g >= ngrp) break;
-                uint32_t r[32];
-                tc_ld32_issue(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * NOp + g * 32), r);
-                tc_ld_wait();
-                if (g == ngrp - 1) {                               // the accumulator has been read completely
-                    tc_fence_before();
-                    tc_mbar_arrive(bar_cfree + 8 * acc);
-                }
                 __syncwarp();                                      // the previous group's slab reads are done
 #pragma unroll
                 for (int i = 0; i < 32; i += 4) {
                     float o[4];
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        o[c] = __fadd_rn(__uint_as_float(r[i + c]), s_bias[g * 32 + i + c]);
+                        o[c] = __fadd_rn(__uint_as_float(r[u][i + c]), s_bias[g * 32 + i + c]);
                         if (p.epi_tanh) o[c] = tanhf(o[c]);
                     }
                     *reinterpret_cast<float4 *>(slab + lane * kTcSlabStride + i) = make_float4(o[0], o[1], o[2], o[3]);
                 }
                 __syncwarp();
-                if (p.moments) {
-                    float s1 = 0.0f, s2 = 0.0f;
-                    for (int rr = 0; rr < nrow; ++rr) {
-                        const float t = slab[rr * kTcSlabStride + lane];
-                        s1 += t;
-                        s2 = fmaf(t, t, s2);
+                if (p.moments) {                                   // lane = column: four independent partial sums
+                    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const float t = rr < nrow ? slab[rr * kTcSlabStride + lane] : 0.0f;
+                        s1[rr & 3] += t;
+                        s2[rr & 3] = fmaf(t, t, s2[rr & 3]);
                     }
-                    m_sum[g] += (double)s1;
-                    m_sq[g] += (double)s2;
+                    m_sum[u] += (double)((s1[0] + s1[1]) + (s1[2] + s1[3]));
+                    m_sq[u] += (double)((s2[0] + s2[1]) + (s2[2] + s2[3]));
                 }
                 const int c4 = lane & 7;
                 if ((NO & 3) == 0) {
@@ -383,11 +395,11 @@ k_linear_tc(const __grid_constant__ TcParams p)
         }
         if (p.moments) {
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                const int c = g * 32 + lane;
+            for (int u = 0; u < 2; ++u) {
+                const int g = 2 * u + half, c = g * 32 + lane;
                 if (g < ngrp && c < NO) {
-                    atomicAdd(p.moments + c, m_sum[g]);
-                    atomicAdd(p.moments + NO + c, m_sq[g]);
+                    atomicAdd(p.moments + c, m_sum[u]);
+                    atomicAdd(p.moments + NO + c, m_sq[u]);
                 }
             }
         }
