@@ -480,10 +480,10 @@ def measure(args, name, B_override, points, steps, warmup, coll, rank, world, de
     h_in_raw.copy_(h_raw)
     e2e_steps = max(3, min(steps, 100))
 
-    def e2e_measure(pipe):
+    def e2e_measure(pipe, with_raw=True):
         def e2e_run(k):
             for _ in range(k):
-                pipe.submit(h_in_pts, h_in_raw, gfe)
+                pipe.submit(h_in_pts, h_in_raw if with_raw else None, gfe)
                 if world > 1 and par is None:
                     psum.copy_(pgrad)
                     dist.all_reduce(psum)
@@ -529,6 +529,19 @@ def measure(args, name, B_override, points, steps, warmup, coll, rank, world, de
         lb = [e2e_measure(lean_pipe) for _ in range(3)]
         lean = (float(np.median(lb)), lean_pipe.d2h_bytes, lb)
         del lean_pipe
+
+    # what the reference's training step would move and nothing else: points in; feats, coors,
+    # num_points, voxel_num out; the perturbation is resident on the device (where the perturber produces it) and its
+    # gradient stays there (where the perturber's backward consumes it).  The perturber's own cost is not in this number:
+    # profiles/r02_mlp_in_loop.txt has the step with the real MLP.
+    real = None
+    if full and not dynamic:
+        real_pipe = StepPipeline(cfg, bounds, n, dev, depth=2, dynamic=False, use_graph=not args.no_graph, pre_step=l2_flush,
+                                 host_fields=StepPipeline.LEAN_FIELDS, raw_on_device=True, grad_to_host=False)
+        real_pipe.set_raw(raw)
+        rb = [e2e_measure(real_pipe, with_raw=False) for _ in range(3)]
+        real = (float(np.median(rb)), real_pipe.h2d_bytes, real_pipe.d2h_bytes, rb)
+        del real_pipe
 
     # ---- per-kernel durations (CUDA events inside the library, same steps, cold L2, no graph)
     stages, phases = {}, {}
@@ -595,6 +608,12 @@ def measure(args, name, B_override, points, steps, warmup, coll, rank, world, de
                            "ms_per_step": round(lean[0] / e2e_steps, 5),
                            "blocks_ms_per_step": [round(b / e2e_steps, 5) for b in lean[2]],
                            "how": "as e2e, StepPipeline(host_fields=LEAN_FIELDS): feats, coors, num_points, voxel_num and grad_raw return to the host, the zero-padded voxels stay on the device"}
+    if real is not None:
+        res["e2e_real"] = {"value": round(total_pts / (real[0] / e2e_steps * 1e-3) / 1e6, 2), "unit": "M points/s",
+                           "h2d_bytes_per_step": real[1], "d2h_bytes_per_step": real[2],
+                           "ms_per_step": round(real[0] / e2e_steps, 5),
+                           "blocks_ms_per_step": [round(b / e2e_steps, 5) for b in real[3]],
+                           "how": "StepPipeline(raw_on_device=True, grad_to_host=False, host_fields=LEAN_FIELDS): points in; feats, coors, num_points, voxel_num out; the perturbation and its gradient stay on the device (stand-in perturbation, the MLP's own cost is in profiles/r02_mlp_in_loop.txt)"}
     if full and world == 1 and not args.no_cpu:
         res["cpu_baseline"] = cpu_baseline(name, clouds, raws, p)
     return res
@@ -650,7 +669,7 @@ def run_b200(args):
             "unit": "M points/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": head["config"], "clocks": head["clocks"],
-            "e2e": head["e2e"], "e2e_lean": head.get("e2e_lean"), "gpu_launches": head["gpu_launches"],
+            "e2e": head["e2e"], "e2e_lean": head.get("e2e_lean"), "e2e_real": head.get("e2e_real"), "gpu_launches": head["gpu_launches"],
             "roofline": head["roofline"],
         }
         if "cpu_baseline" in head:

@@ -28,13 +28,18 @@ class StepPipeline:
 
     def __init__(self, cfg: VoxelCfg, bounds: PerturbCfg, n_per_sample: Sequence[int], device: torch.device,
                  depth: int = 2, dynamic: bool = False, use_graph: bool = True, pre_step=None,
-                 host_fields: Optional[Sequence[str]] = None):
+                 host_fields: Optional[Sequence[str]] = None, raw_on_device: bool = False, grad_to_host: bool = True):
         """``pre_step``: optional callable run on the compute stream in front of every step (bench.py's L2 flush).
         ``host_fields``: which outputs travel back to the host (default: all of ``_HOST_FIELDS``; ``grad_raw`` always
         does).  The zero-padded ``voxels`` tensor is 35 % (KITTI) to 70 % (nuScenes) of the device->host bytes and is
         only an intermediate once the VFE mean is fused -- what the reference hands on after HardSimpleVFE is
         ``feats`` + ``coors`` (adversarial_voxelnet.py:135-140) -- so a caller that continues with the middle encoder
-        leaves it out: ``host_fields=StepPipeline.LEAN_FIELDS``.  Outputs left out stay device tensors in ``outs``."""
+        leaves it out: ``host_fields=StepPipeline.LEAN_FIELDS``.  Outputs left out stay device tensors in ``outs``.
+        ``raw_on_device=True`` / ``grad_to_host=False``: what the reference's training step moves and nothing else --
+        the perturbation is produced on the device by the perturber (``d_raw[k]``, written by the caller on ``s_cmp`` or
+        set once with ``set_raw``) and its gradient feeds the perturber's backward on the device (``graw[k]``), so only
+        ``points`` cross PCIe on the way in and the voxel outputs on the way out (``submit(h_points, None, grad)``)."""
+        self.raw_on_device, self.grad_to_host = raw_on_device, grad_to_host
         self.host_fields = tuple(self._HOST_FIELDS if host_fields is None else host_fields)
         unknown = set(self.host_fields) - set(self._HOST_FIELDS)
         if unknown:
@@ -68,7 +73,8 @@ class StepPipeline:
                 o = self._fwd(k, None)                                   # shapes of the outputs at capacity
                 named = {f.name: getattr(o, f.name) for f in dataclasses.fields(o)
                          if isinstance(getattr(o, f.name), torch.Tensor) and f.name in self.host_fields}
-                named["grad_raw"] = torch.empty((N, C), **f32)
+                if grad_to_host:
+                    named["grad_raw"] = torch.empty((N, C), **f32)
                 if not self._layout:
                     off = 0
                     for name, t in named.items():
@@ -78,7 +84,7 @@ class StepPipeline:
                 pack = torch.empty((self._pack_bytes,), dtype=torch.uint8, device=device)
                 views = self._views(pack)
                 self.d_pack.append(pack)
-                self.graw.append(views.pop("grad_raw"))
+                self.graw.append(views.pop("grad_raw") if grad_to_host else torch.empty((N, C), **f32))
                 self.outs.append(dataclasses.replace(o, **views))
         torch.cuda.synchronize(device)
         self.h_pack = [torch.empty((self._pack_bytes,), dtype=torch.uint8).pin_memory() for _ in range(depth)]
@@ -132,22 +138,33 @@ class StepPipeline:
         self.graphs[k].replay()
 
     # ---------------------------------------------------------------------------------------------
+    def set_raw(self, raw: torch.Tensor) -> None:
+        """``raw_on_device``: the perturbation of every slot := ``raw`` [sum n, C] (device), stream-ordered on ``s_cmp``"""
+        with torch.cuda.stream(self.s_cmp):
+            self.s_cmp.wait_stream(torch.cuda.current_stream(self.dev))
+            for d in self.d_raw:
+                d.copy_(raw, non_blocking=True)
+
     @property
     def h2d_bytes(self) -> int:
-        return 2 * self.d_pts[0].numel() * 4
+        return (1 if self.raw_on_device else 2) * self.d_pts[0].numel() * 4
 
     @property
     def d2h_bytes(self) -> int:
         return int(self._pack_bytes)                                 # what the one device->host copy moves
 
-    def submit(self, h_points: torch.Tensor, h_raw: torch.Tensor, grad_feats: torch.Tensor) -> int:
-        """Enqueue one step: ``h_points`` / ``h_raw`` pinned host [sum n, C]; ``grad_feats`` device [cap, F] (the
-        gradient the detector sends back).  Returns a ticket for ``result``."""
+    def submit(self, h_points: torch.Tensor, h_raw: Optional[torch.Tensor], grad_feats: torch.Tensor) -> int:
+        """Enqueue one step: ``h_points`` / ``h_raw`` pinned host [sum n, C] (``h_raw=None`` with ``raw_on_device``);
+        ``grad_feats`` device [cap, F] (the gradient the detector sends back).  Returns a ticket for ``result``."""
+        if (h_raw is None) != self.raw_on_device:
+            raise ValueError("h_raw must be None exactly when the pipeline was built with raw_on_device=True")
         k = self.count % self.depth
         with torch.cuda.stream(self.s_in):
             self.s_in.wait_event(self.ev_cmp[k])                         # kernels that read this slot's inputs are done
             nb = h_points.numel() * h_points.element_size()
-            if (h_raw.data_ptr() == h_points.data_ptr() + nb and h_points.is_contiguous() and h_raw.is_contiguous()
+            if h_raw is None:
+                self.d_pts[k].copy_(h_points, non_blocking=True)
+            elif (h_raw.data_ptr() == h_points.data_ptr() + nb and h_points.is_contiguous() and h_raw.is_contiguous()
                     and h_points.dtype == torch.float32 and h_raw.dtype == torch.float32):
                 both = torch.as_strided(h_points, tuple(self.d_in[k].shape), self.d_in[k].stride())
                 self.d_in[k].copy_(both, non_blocking=True)              # the halves of one pinned buffer: one copy

@@ -420,8 +420,11 @@ class VoxelPerturber(nn.Module):
             return None
         if self.nan_guards == "device":
             self.guard_tripped = torch.isnan(x).any()
-        if self.fused_stats and x.is_cuda and x.shape[0] >= 2:
-            xn = ops.normalize_fwd(x.detach())                   # x carries no gradient into the network (:157-168)
+        if self.fused_stats and x.is_cuda and x.shape[0] >= 2 and not x.requires_grad:
+            # (the kernel has no backward: it serves the extract_feat path, where x carries no gradient; an input that
+            # does -- the post-VFE variant behind a learned encoder -- takes the ATen formula, which keeps x in the graph
+            # like the reference's clone / divide / clamp, voxel_perturber.py:157-168)
+            xn = ops.normalize_fwd(x)
         else:
             scale = torch.std(x, dim=0, keepdim=True) + 1e-6
             if self.nan_guards == "device":

@@ -148,3 +148,20 @@ def test_device_nan_guards(golden_dir):
     assert not any(torch.isnan(q).any() for q in adv.parameters())
     y, ld = adv(x)
     assert not adv.check_guards() and float(ld["l2_norm"].detach()) > 0.0
+
+
+def test_input_gradient_flows_with_fused_stats():
+    """An input that requires grad (the post-VFE variant behind a learned encoder) keeps its path through the
+    normalisation, the MLP and the attention, like the reference's clone / divide / clamp (voxel_perturber.py:157-168):
+    fused_stats=True must give the same d/dx as the ATen formulas."""
+    grads = []
+    for fused in (True, False):
+        torch.manual_seed(3)
+        adv = VoxelPerturber(hidden_channels=[16, 32, 64], fused_stats=fused, nan_guards=False).build(4, DEV).train()
+        g = torch.Generator(DEV).manual_seed(9)
+        x = (torch.rand(257, 4, device=DEV, generator=g) * torch.tensor([70.0, 80.0, 4.0, 1.0], device=DEV)).requires_grad_(True)
+        y, ld = adv(x)
+        (y.square().sum() + sum(ld.values())).backward()
+        grads.append(x.grad.clone())
+    assert float((grads[0] - 2 * x.detach()).abs().max()) > 1e-3           # more than the identity path: the network's share
+    torch.testing.assert_close(grads[0], grads[1], rtol=1e-4, atol=1e-5)

@@ -93,3 +93,35 @@ def test_pipeline_lean_host_fields():
     assert torch.equal(lean.outs[0].voxels[:M].cpu(), a["voxels"][:M])       # still produced, on the device
     with pytest.raises(ValueError):
         StepPipeline(cfg, bounds, n, dev, host_fields=("voxels", "nonsense"))
+
+
+def test_pipeline_raw_on_device_gradient_on_device():
+    """raw_on_device=True, grad_to_host=False: only points cross PCIe on the way in, the gradient stays where the
+    perturber's backward reads it; every result equals the host-fed pipeline's, over several steps and both slots"""
+    dev = torch.device("cuda:0")
+    k = synth.KITTI
+    C, P, V = k["C"], k["max_num_points"], 3000
+    n = [6001, 4000]
+    cfg = VoxelCfg.make(k["voxel_size"], k["point_cloud_range"], P, V, C, C)
+    eb, fb = orc.perturber_bounds(C, True)
+    bounds = PerturbCfg.make(eb, fb)
+    full = StepPipeline(cfg, bounds, n, dev, host_fields=StepPipeline.LEAN_FIELDS)
+    real = StepPipeline(cfg, bounds, n, dev, host_fields=StepPipeline.LEAN_FIELDS, raw_on_device=True, grad_to_host=False)
+    assert real.h2d_bytes * 2 == full.h2d_bytes and real.d2h_bytes < full.d2h_bytes - sum(n) * C * 4 + 1024
+    gf = torch.randn((sum(min(x, V) for x in n), C), device=dev, generator=torch.Generator(dev).manual_seed(5))
+    hp, hr = full.alloc_host_inputs()
+    for step in range(3):
+        hp.copy_(torch.from_numpy(np.concatenate([synth.make_cloud("kitti", m, "lidar", 70 + 10 * step + i) for i, m in enumerate(n)])))
+        hr.copy_(torch.from_numpy(synth.make_raw(hp.numpy(), 71 + step)))
+        real.set_raw(hr.to(dev))
+        a = full.result(full.submit(hp, hr, gf))
+        t = real.submit(hp, None, gf)
+        b = real.result(t)
+        assert "grad_raw" in a and "grad_raw" not in b
+        for name in b:
+            assert torch.equal(a[name], b[name]), name
+        assert torch.equal(real.graw[t % real.depth].cpu(), a["grad_raw"])
+    with pytest.raises(ValueError):
+        real.submit(hp, hr, gf)
+    with pytest.raises(ValueError):
+        full.submit(hp, None, gf)
