@@ -11,7 +11,7 @@
 // accumulated in fp32 in tensor memory: relative error ~1e-6, inside the 1e-5 parity bar, where single-pass TF32
 // (1e-3) is not.
 //
-// One persistent CTA per SM, 13 warps with fixed roles that meet only at mbarriers:
+// One persistent CTA per SM, 17 warps with fixed roles that meet only at mbarriers:
 //   * the weight matrix is split once into hi / lo and kept in shared memory in the tcgen05 K-major canonical layout
 //     with 128-byte swizzle (rows of 32 TF32, 8-row groups 1024 bytes apart);
 //   * 8 loader warps bring 128 rows x 32 columns of X per stage through registers (optional fused prologue: the
@@ -67,8 +67,9 @@ __device__ __forceinline__ void split_tf32(float v, uint32_t &hi, uint32_t &lo)
 // shared-memory matrix descriptor, K-major, 128-byte swizzle: rows of 32 TF32 (128 bytes), 8-row groups 1024 bytes apart
 // (SBO), the 16-byte chunk c of row r stored at chunk position c ^ (r & 7); the start address may be advanced by 32
 // bytes per K = 8 step inside the row (the hardware applies the XOR to the address bits); descriptor version 1 (sm_100).
-// The first version of this kernel used the unswizzled "interleaved" layout: correct, but every tcgen05.mma then
-// occupied the tensor pipe for ~2 cycles per output column, four times the swizzled rate (profiles/r02_linear_tc.txt).
+// The first version of this kernel used the unswizzled "interleaved" layout (8 x 16-byte core matrices, LBO between K
+// chunks): equally correct and, measured, equally fast -- the tensor pipe is not what bounds this kernel
+// (profiles/r02_linear_tc.txt; a three-stage ring was measured too and was slower: 273 vs 197 us); the swizzled layout is kept because it is the one the hardware documentation centres on.
 __device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr)
 {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
