@@ -93,17 +93,23 @@ class Workspace:
 
 
 _default_ws = Workspace()
-# rpc_voxelize_hard keeps its hash table, rows, lists and counters all-zero BETWEEN calls (every call restores what
-# it touched), so its workspace belongs to it alone: nothing else may write there.  A fresh (torch.empty) buffer is
-# recognised by the header and zeroed once by the kernel itself.  25 % headroom: ragged batches of a training run
+_scratch_ws = Workspace()        # the small fp64 accumulators of the reduction kernels (zeroed by every call that uses them)
+
+
+def _scratch64(n: int, dev: torch.device) -> torch.Tensor:
+    """n doubles of per-(device, stream) scratch: the kernels that use it are stream-ordered and zero it themselves, so
+    one cached buffer replaces a torch.empty per call (part of the Python overhead around the small kernels)"""
+    return _scratch_ws.get(8 * n, dev)[:8 * n].view(torch.float64)
+# rpc_voxelize_hard has a workspace of its own per (device, stream): a captured CUDA graph bakes the address in, and
+# nothing else should be scribbling there while a step is in flight.  25 % headroom: ragged batches of a training run
 # change the layout a little every step without outgrowing the buffer.
 _hard_ws = Workspace(headroom=1.25)
 
 
 def hard_workspace_bytes(cfg: VoxelCfg, n_per_sample: Sequence[int]) -> int:
     """``rpc_workspace_bytes``: smallest workspace ``hard_voxelize`` accepts for this batch.  A caller that keeps
-    its own workspace (a captured CUDA graph must) allocates it once with ``torch.empty`` -- the kernel recognises a
-    fresh buffer and zeroes it itself -- and never lets anything else write to it."""
+    its own workspace (a captured CUDA graph must) allocates it once with ``torch.empty``; every call initialises what
+    it reads."""
     n = _lib.lib().rpc_workspace_bytes(ctypes.byref(cfg), len(n_per_sample), _lib.counts(n_per_sample))
     if n == 0:
         raise _lib.RpcError(-2, "rpc_workspace_bytes")
@@ -429,7 +435,7 @@ def attention_gate_bwd(g_out: torch.Tensor, xn: torch.Tensor, t: torch.Tensor, w
     grad_t = torch.empty_like(t)
     grad_xn = torch.empty_like(xn) if want_grad_xn else None
     gw1, gb1, gw2, gb2 = (torch.empty_like(q) for q in (w1, b1, w2, b2))
-    scratch = torch.empty((_lib.lib().rpc_attention_scratch_bytes() // 8,), dtype=torch.float64, device=dev)
+    scratch = _scratch64(_lib.lib().rpc_attention_scratch_bytes() // 8, dev)
     st = _lib.lib().rpc_attention_gate_bwd(_ptr(g_out), _ptr(xn), _ptr(t), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), K, C,
                                            _ptr(scratch), _ptr(grad_t), _ptr(grad_xn), _ptr(gw1), _ptr(gb1), _ptr(gw2),
                                            _ptr(gb2), _stream(dev))
@@ -539,7 +545,7 @@ def trunk_fwd(desc, xn: torch.Tensor, widths: Sequence[int]):
         ys.append(ybuf[o:o + K * h].view(K, h))
         o += K * h
     stats = torch.empty((2 * tot,), dtype=torch.float32, device=dev)
-    scratch = torch.empty((2 * tot,), dtype=torch.float64, device=dev)
+    scratch = _scratch64(2 * tot, dev)
     raw = torch.empty((K, C), dtype=torch.float32, device=dev)
     st = _lib.lib().rpc_trunk_fwd(ctypes.byref(desc), _ptr(xn), K, _ptr_array(ys), _ptr(stats), _ptr(scratch), _ptr(raw), _stream(dev))
     _lib.check(st, "rpc_trunk_fwd")
@@ -554,7 +560,7 @@ def trunk_bwd(desc, xn: torch.Tensor, widths: Sequence[int], ys, stats: torch.Te
     g_raw = _f32c(g_raw)
     maxw = max(max(widths), C)
     work = torch.empty((2 * K * maxw,), dtype=torch.float32, device=dev)
-    scratch = torch.empty((2 * 128,), dtype=torch.float64, device=dev)
+    scratch = _scratch64(2 * 128, dev)
     nl = len(widths)
     n_w = sum(a * b for a, b in param_shapes)
     flat = torch.empty((n_w + sum(a for a, _ in param_shapes) + 2 * sum(widths),), dtype=torch.float32, device=dev)
@@ -587,7 +593,7 @@ def bn_relu_fwd(y: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: f
     z = torch.empty_like(y)
     mean = torch.empty((H,), dtype=torch.float32, device=dev)
     invstd = torch.empty((H,), dtype=torch.float32, device=dev)
-    scratch = torch.empty((_lib.lib().rpc_bn_scratch_bytes() // 8,), dtype=torch.float64, device=dev)
+    scratch = _scratch64(_lib.lib().rpc_bn_scratch_bytes() // 8, dev)
     st = _lib.lib().rpc_bn_relu_fwd(_ptr(y), K, H, _ptr(_f32c(gamma)), _ptr(_f32c(beta)), float(eps), float(momentum),
                                     _ptr(running_mean), _ptr(running_var), _ptr(scratch), _ptr(mean), _ptr(invstd),
                                     _ptr(z), _stream(dev))
@@ -604,7 +610,7 @@ def bn_relu_bwd(g: torch.Tensor, y: torch.Tensor, mean: torch.Tensor, invstd: to
     gy = torch.empty_like(y)
     gg = torch.empty((H,), dtype=torch.float32, device=dev)
     gb = torch.empty((H,), dtype=torch.float32, device=dev)
-    scratch = torch.empty((_lib.lib().rpc_bn_scratch_bytes() // 8,), dtype=torch.float64, device=dev)
+    scratch = _scratch64(_lib.lib().rpc_bn_scratch_bytes() // 8, dev)
     st = _lib.lib().rpc_bn_relu_bwd(_ptr(g), _ptr(y), _ptr(mean), _ptr(invstd), _ptr(_f32c(gamma)), _ptr(_f32c(beta)), K, H,
                                     _ptr(scratch), _ptr(gy), _ptr(gg), _ptr(gb), _stream(dev))
     _lib.check(st, "rpc_bn_relu_bwd")
@@ -619,7 +625,7 @@ def normalize_fwd(x: torch.Tensor) -> torch.Tensor:
     x = _f32c(x)
     K, C = x.shape
     xn = torch.empty_like(x)
-    mom = torch.empty((_lib.lib().rpc_moments_bytes() // 8,), dtype=torch.float64, device=dev)
+    mom = _scratch64(_lib.lib().rpc_moments_bytes() // 8, dev)
     st = _lib.lib().rpc_normalize_fwd(_ptr(x), K, None, C, _ptr(mom), _ptr(xn), _stream(dev))
     _lib.check(st, "rpc_normalize_fwd")
     return xn
@@ -630,7 +636,7 @@ def perturb_losses_fwd(p: torch.Tensor):
     dev = _need_cuda(p)
     p = _f32c(p)
     K, C = p.shape
-    mom = torch.empty((_lib.lib().rpc_moments_bytes() // 8,), dtype=torch.float64, device=dev)
+    mom = _scratch64(_lib.lib().rpc_moments_bytes() // 8, dev)
     losses = torch.empty((4,), dtype=torch.float32, device=dev)
     consts = torch.empty((32,), dtype=torch.float32, device=dev)
     st = _lib.lib().rpc_perturb_losses_fwd(_ptr(p), K, None, C, _ptr(mom), _ptr(losses), _ptr(consts), _stream(dev))

@@ -58,8 +58,7 @@ class StepPipeline:
         self.d_raw = [b[1] for b in self.d_in]
         self.outs: List = []
         self.graphs: List[Optional[torch.cuda.CUDAGraph]] = [None] * depth
-        # every slot owns its workspace (a captured graph bakes the address in, and rpc_voxelize_hard keeps its
-        # table clean between calls: nothing else may write there) and a persistent copy of the gradient the caller
+        # every slot owns its workspace (a captured graph bakes the address in) and a persistent copy of the gradient the caller
         # hands in, so that ONE capture per slot serves every step
         ws_bytes = (ops.dynamic_workspace_bytes if dynamic else ops.hard_workspace_bytes)(cfg, self.n)
         self.ws = [torch.empty((ws_bytes + 256,), dtype=torch.uint8, device=device) for _ in range(depth)]
