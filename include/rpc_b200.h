@@ -368,7 +368,7 @@ int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, cons
  *   updates the running statistics like torch; rpc_bn_relu_apply recomputes z = relu(bn(y)) from saved statistics
  *   (the layer input the weight gradient needs in the backward).
  * NI > 8 (NI % 8 == 0, any NO): 3 x TF32 on tcgen05 (x = x_hi + x_lo, w = w_hi + w_lo, x_lo w_hi + x_hi w_lo + x_hi w_hi
- * accumulated in fp32 in tensor memory; ~1e-6 relative; the weights stay in shared memory, which rules out 128 -> 128: RPC_ERR_CONFIG).  NI <= 8 (first layer, input gradient of the last; NO % 4 == 0): an
+ * accumulated in fp32 in tensor memory; ~1e-6 relative; the weights stay in 64 KB of shared memory, which rules out 128 -> 128 and 128 <-> 96: RPC_ERR_CONFIG).  NI <= 8 (first layer, input gradient of the last; NO % 4 == 0): an
  * fp32 FMA stream.
  * k_dev (device int32, may be NULL) bounds the rows at run time.
  * ------------------------------------------------------------------------------------------------- */

@@ -1198,6 +1198,14 @@ RPC_API int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, f
 
 }  // extern "C"
 
+extern "C" {
+// experiment counters of k_linear_tc (RPC_TC_DBG=4; tools only, not in the header)
+RPC_API int rpc_debug_tc_stats(unsigned long long *out16)
+{
+    return cudaMemcpyFromSymbol(out16, g_tc_stats, sizeof(unsigned long long) * 16) == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+}  // extern "C"
+
 // ------------------------------------------------------------------ allocation-free variant (static device scratch)
 // rpc_points_range_filter_static: rpc_points_range_filter with its per-tile count scratch in a file-scope device
 // array, for callers that cannot provide a workspace (CUDA-graph capture, tight serving loops, harnesses that

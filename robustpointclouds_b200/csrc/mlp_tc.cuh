@@ -21,7 +21,8 @@
 //   * one thread issues the 3 x (columns / 8) tcgen05.mma (M = 128, N = NO, K = 8) of a stage into one of two TMEM
 //     accumulators and commits to the "stage free" / "accumulator full" mbarriers;
 //   * 8 epilogue warps (two per TMEM lane quadrant, alternate 32-column groups) take the finished accumulator:
-//     tcgen05.ld -> + bias [-> tanh] -> a padded per-warp slab in shared memory -> full 128-byte lines to global memory,
+//     tcgen05.ld -> + bias [-> tanh] -> a padded per-warp slab in shared memory -> full 128-byte lines to global memory
+//     (st.global; one 128-byte cp.async.bulk per row was measured and is slower: 231 vs 211 us at 64 -> 128),
 //     and, lane = column, the per-column sum / sum of squares the next BatchNorm needs (no shuffles).
 // The first version (all warps doing load -> MMA -> epilogue in turn) ran at 1.2 TB/s: profiles/r02_linear_tc.txt.
 // The first layer (NI = C <= 8) and the input gradient of the last one are streams, not contractions: k_linear_narrow_in.
@@ -45,7 +46,8 @@ struct TcParams {
     const float *in_mean, *in_invstd, *in_gamma, *in_beta;   // [NI] each or NULL: prologue x' = relu(bn(x)), the
                                                  // previous layer's BatchNorm + ReLU in k_bn_relu_fwd's operation order
     int epi_tanh;                                // epilogue: y = tanh(y)
-    int dbg;                                     // experiments (RPC_TC_DBG): 1 = one MMA per K step instead of three, 2 = none
+    int dbg;                                     // experiments (RPC_TC_DBG): 1 = one MMA per K step instead of three, 2 = none,
+                                                 // 4 = role cycle counters (tools/dbg_tc_stats.py), 5 = no global stores
     double *moments;                             // [2 * NO] or NULL: += column sums and sums of squares of y
 };
 
@@ -147,19 +149,23 @@ __device__ __forceinline__ void tc_mbar_arrive(uint32_t bar)
 // ---- layout of k_linear_tc's dynamic shared memory
 //   B hi, B lo          2 x ceil(NI / 32) blocks of NOp rows x 128 bytes (32 columns of K), 128-byte swizzle
 //   X stages            2 x (hi, lo) x 128 rows x 128 bytes (32 columns) = 64 KB, 128-byte swizzle
+//   raw ring            3 x 128 rows x 128 bytes of fp32 on their way from global memory (cp.async), same chunk layout
 //   epilogue slabs      8 warps x 32 rows x 36 floats (padded rows: conflict-free 16-byte writes by row and reads by column)
 //   BatchNorm constants of the prologue (float4 per input column), bias, 8 mbarriers, the TMEM base address
+// experiment counters of CTA 0 (RPC_TC_DBG = 4): cycles spent by one loader thread, the MMA thread and one epilogue thread
+__device__ unsigned long long g_tc_stats[16];
+
 constexpr int kTcLoadWarps = 8, kTcEpiWarps = 8;               // (two epilogue warps per TMEM lane quadrant)
 constexpr int kTcLoaders = kTcLoadWarps * 32;
 constexpr int kTcThreads2 = (kTcLoadWarps + kTcEpiWarps + 1) * 32;     // + the MMA warp
 constexpr int kTcSC = 32;                                              // columns of X per stage
 constexpr int kTcStageB = kTcRows * kTcSC * 4;                         // one of hi / lo: 16 KB
 constexpr int kTcSlabStride = 36;                                      // floats per slab row
-constexpr int kTcDepth = 4;                                            // stage loads a loader thread keeps in flight
+constexpr int kTcRaw = 3;                                              // raw fp32 stages in flight ahead of the conversion (cp.async)
 
 __host__ __device__ inline size_t tc_smem_bytes(int NI, int NOp)
 {
-    return 2 * (size_t)((NI + kTcSC - 1) / kTcSC) * NOp * 128 + 4 * (size_t)kTcStageB + (size_t)kTcEpiWarps * 32 * kTcSlabStride * 4 +
+    return 2 * (size_t)((NI + kTcSC - 1) / kTcSC) * NOp * 128 + (4 + kTcRaw) * (size_t)kTcStageB + (size_t)kTcEpiWarps * 32 * kTcSlabStride * 4 +
            (size_t)kTcMaxDim * 16 + kTcMaxDim * 4 + 8 * 8 + 16 + 1024;               // (+ 1024: the swizzle atoms need that alignment)
 }
 
@@ -175,7 +181,9 @@ k_linear_tc(const __grid_constant__ TcParams p)
     const uint32_t wbytes = (uint32_t)((NI + kTcSC - 1) / kTcSC) * wblock;
     unsigned char *sB = tc_sm;
     unsigned char *sA = tc_sm + 2 * wbytes;
-    float *s_slab = reinterpret_cast<float *>(sA + 4 * kTcStageB);
+    unsigned char *sRaw = sA + 4 * kTcStageB;                        // raw fp32 ring of the loaders
+    const uint32_t sRaw_u = smem_u32(sRaw);
+    float *s_slab = reinterpret_cast<float *>(sRaw + kTcRaw * kTcStageB);
     float4 *s_bn = reinterpret_cast<float4 *>(s_slab + kTcEpiWarps * 32 * kTcSlabStride);
     float *s_bias = reinterpret_cast<float *>(s_bn + kTcMaxDim);
     unsigned long long *s_bar = reinterpret_cast<unsigned long long *>(s_bias + kTcMaxDim);
@@ -238,39 +246,68 @@ k_linear_tc(const __grid_constant__ TcParams p)
     const uint32_t tmem_base = *s_tmem;
 
     if (warp < kTcLoadWarps) {
-        // ================= loaders: global -> registers -> (BatchNorm + ReLU) -> hi / lo -> shared-memory stage
+        // ================= loaders: global -> (cp.async) raw ring -> (BatchNorm + ReLU) -> hi / lo -> shared-memory stage
         // A warp instruction covers 8 rows x 4 chunks: 64 contiguous bytes per row from global memory, and per quarter-warp
-        // 128 contiguous bytes of shared memory (conflict-free 16-byte stores).  kTcDepth stage loads stay in flight per
-        // thread (64 KB per SM), so the conversion of one stage overlaps the memory latency of the next ones.
+        // 128 contiguous bytes of shared memory (conflict-free 16-byte accesses).  The raw fp32 chunks travel with cp.async
+        // into a three-deep ring (kTcRaw stages ahead of the conversion, no registers held: with the loads in registers the
+        // compiler sank them to their first use under the 96-register cap of a 17-warp CTA and every stage paid the memory
+        // latency -- 1730 cycles of "work" per stage, profiles/r02_linear_tc.txt); every thread reads back exactly the
+        // chunks it copied, so the ring needs no barrier, only cp.async.wait_group.
         const int r8 = lane & 7, cq = lane >> 3;
-        float4 v[kTcDepth][4];
-        auto issue = [&](long long j, float4 (&slot)[4]) {
-            if (j >= njobs) return;
-            const long long ti = j / nstage;
-            const int s = (int)(j - ti * nstage);
-            const long long tile = blockIdx.x + ti * gridDim.x;
-            const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
+        long long st_wait = 0, st_work = 0;
+        auto chunk_off = [&](int u, int &ch) -> uint32_t {
+            const int jj = warp + 8 * u, rg = jj >> 1;
+            ch = (jj & 1) * 4 + cq;
+            return (uint32_t)(rg * 8 + r8) * 128u + (uint32_t)((ch ^ r8) * 16);
+        };
+        auto issue = [&](bool live, int rb, long long tile, int s) {
+            if (live) {
+                const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    int ch;
+                    const uint32_t off = chunk_off(u, ch);
+                    if (ch * 4 >= ncol) continue;
+                    const long long row = tile * kTcRows + ((warp + 8 * u) >> 1) * 8 + r8;
+                    const bool ok = row < K;                            // rows beyond K are zero-filled (src-size 0)
+                    const float *src = p.x + (ok ? row : 0) * NI + col0 + ch * 4;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sRaw_u + (uint32_t)rb * kTcStageB + off),
+                                 "l"(src), "r"(ok ? 16 : 0) : "memory");
+                }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");          // (empty groups keep the count uniform)
+        };
+        long long tile_i = blockIdx.x, tile_c = blockIdx.x;
+        int s_i = 0, s_c = 0;
+        for (int d = 0; d < kTcRaw; ++d) {
+            issue(d < njobs, d, tile_i, s_i);
+            if (++s_i == nstage) { s_i = 0; tile_i += gridDim.x; }
+        }
+        int rb = 0;
+        for (long long j = 0; j < njobs; ++j) {
+            const int col0 = s_c * kTcSC, ncol = min(kTcSC, NI - col0);
+            const int buf = (int)(j & 1);
+            asm volatile("cp.async.wait_group %0;" ::"n"(kTcRaw - 1) : "memory");   // this thread's chunks of job j have landed
+            float4 v[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int jj = warp + 8 * u, rg = jj >> 1, ch = (jj & 1) * 4 + cq;
-                const long long row = tile * kTcRows + rg * 8 + r8;
-                slot[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (row < K && ch * 4 < ncol) slot[u] = __ldg(reinterpret_cast<const float4 *>(p.x + row * NI + col0) + ch);
+                int ch;
+                const uint32_t off = chunk_off(u, ch);
+                v[u] = *reinterpret_cast<const float4 *>(sRaw + (size_t)rb * kTcStageB + off);
             }
-        };
-        auto consume = [&](long long j, float4 (&slot)[4]) {
-            if (j >= njobs) return;
-            const long long ti = j / nstage;
-            const int s = (int)(j - ti * nstage);
-            const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
-            const int buf = (int)(j & 1);
+            issue(j + kTcRaw < njobs, rb, tile_i, s_i);                   // refill the slot just read
+            if (++s_i == nstage) { s_i = 0; tile_i += gridDim.x; }
+            const long long t0 = clock64();
             if (j >= 2) tc_mbar_wait(bar_afree + 8 * buf, (uint32_t)((j >> 1) - 1) & 1u);     // the MMAs that read this stage are done
+            const long long t1 = clock64();
+            st_wait += t1 - t0;
             unsigned char *a_hi = sA + (size_t)buf * 2 * kTcStageB, *a_lo = a_hi + kTcStageB;
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int jj = warp + 8 * u, rg = jj >> 1, ch = (jj & 1) * 4 + cq;
+                int ch;
+                const uint32_t off = chunk_off(u, ch);
                 if (ch * 4 >= ncol) continue;
-                float e[4] = {slot[u].x, slot[u].y, slot[u].z, slot[u].w};
+                float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
                 if (p.in_mean) {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
@@ -281,33 +318,33 @@ k_linear_tc(const __grid_constant__ TcParams p)
                 uint32_t hi[4], lo[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) split_tf32(e[q], hi[q], lo[q]);
-                const uint32_t off = (uint32_t)(rg * 8 + r8) * 128u + (uint32_t)((ch ^ r8) * 16);
                 *reinterpret_cast<uint4 *>(a_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                 *reinterpret_cast<uint4 *>(a_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             tc_mbar_arrive(bar_afull + 8 * buf);
-        };
-#pragma unroll
-        for (int d = 0; d < kTcDepth; ++d) issue(d, v[d]);
-        for (long long j = 0; j < njobs; j += kTcDepth) {
-#pragma unroll
-            for (int d = 0; d < kTcDepth; ++d) {
-                consume(j + d, v[d]);
-                issue(j + d + kTcDepth, v[d]);
-            }
+            st_work += clock64() - t1;
+            if (++s_c == nstage) { s_c = 0; tile_c += gridDim.x; }
+            if (++rb == kTcRaw) rb = 0;
         }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        if (p.dbg == 4 && blockIdx.x == 0 && tid == 0) { g_tc_stats[0] = st_wait; g_tc_stats[1] = st_work; g_tc_stats[2] = njobs; }
     } else if (warp == kTcLoadWarps + kTcEpiWarps) {
         // ================= MMA issuer: one thread
         if (lane == 0) {
             const uint32_t idesc = tc_instr_desc(NOp);
+            long long mw_c = 0, mw_a = 0, mi = 0;
+            long long it = 0;
+            int s = 0;
             for (long long j = 0; j < njobs; ++j) {
-                const long long it = j / nstage;
-                const int s = (int)(j - it * nstage);
                 const int acc = (int)(it & 1), buf = (int)(j & 1);
                 const int col0 = s * kTcSC, ncol = min(kTcSC, NI - col0);
+                const long long t0 = clock64();
                 if (s == 0 && it >= 2) tc_mbar_wait(bar_cfree + 8 * acc, (uint32_t)((it >> 1) - 1) & 1u);   // epilogue has drained it
+                const long long t1 = clock64();
                 tc_mbar_wait(bar_afull + 8 * buf, (uint32_t)(j >> 1) & 1u);
+                const long long t2 = clock64();
+                mw_c += t1 - t0; mw_a += t2 - t1;
                 tc_fence_after();
                 const uint32_t a_hi_u = sA_u + (uint32_t)buf * 2 * kTcStageB, a_lo_u = a_hi_u + kTcStageB;
                 const uint32_t d = tmem_base + (uint32_t)(acc * NOp);
@@ -325,7 +362,10 @@ k_linear_tc(const __grid_constant__ TcParams p)
                 }
                 tc_commit(bar_afree + 8 * buf);                                   // stage free when these MMAs have read it
                 if (s == nstage - 1) tc_commit(bar_cfull + 8 * acc);              // accumulator complete
+                mi += clock64() - t2;
+                if (++s == nstage) { s = 0; ++it; }
             }
+            if (p.dbg == 4 && blockIdx.x == 0) { g_tc_stats[3] = mw_c; g_tc_stats[4] = mw_a; g_tc_stats[5] = mi; }
         }
         __syncwarp();
     } else {
@@ -335,10 +375,14 @@ k_linear_tc(const __grid_constant__ TcParams p)
         float *slab = s_slab + (size_t)(warp - kTcLoadWarps) * 32 * kTcSlabStride;
         double m_sum[2] = {0.0, 0.0}, m_sq[2] = {0.0, 0.0};        // lane = column (2 * u + half) * 32 + lane
         const int ngrp = NOp >> 5;
+        long long ew = 0, el = 0, es = 0;
         for (long long it = 0; it < my_tiles; ++it) {
             const long long tile = blockIdx.x + it * gridDim.x;
             const int acc = (int)(it & 1);
+            const long long e0 = clock64();
             tc_mbar_wait(bar_cfull + 8 * acc, (uint32_t)(it >> 1) & 1u);
+            const long long e1 = clock64();
+            ew += e1 - e0;
             tc_fence_after();
             const long long row0 = tile * kTcRows + q * 32;
             const int nrow = (int)max(0LL, min(32LL, K - row0));   // live rows of this warp's slab
@@ -351,27 +395,32 @@ k_linear_tc(const __grid_constant__ TcParams p)
             tc_ld_wait();
             tc_fence_before();
             tc_mbar_arrive(bar_cfree + 8 * acc);
+            const long long e2 = clock64();
+            el += e2 - e1;
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 const int g = 2 * u + half;
                 if (g >= ngrp) break;
                 __syncwarp();                                      // the previous group's slab reads are done
+                const bool live_row = lane < nrow;                 // rows beyond K go into the slab as zeros (moments)
 #pragma unroll
                 for (int i = 0; i < 32; i += 4) {
-                    float o[4];
+                    const float4 b4 = *reinterpret_cast<const float4 *>(s_bias + g * 32 + i);
+                    float o[4] = {__fadd_rn(__uint_as_float(r[u][i]), b4.x), __fadd_rn(__uint_as_float(r[u][i + 1]), b4.y),
+                                  __fadd_rn(__uint_as_float(r[u][i + 2]), b4.z), __fadd_rn(__uint_as_float(r[u][i + 3]), b4.w)};
+                    if (p.epi_tanh) {
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        o[c] = __fadd_rn(__uint_as_float(r[u][i + c]), s_bias[g * 32 + i + c]);
-                        if (p.epi_tanh) o[c] = tanhf(o[c]);
+                        for (int c = 0; c < 4; ++c) o[c] = tanhf(o[c]);
                     }
-                    *reinterpret_cast<float4 *>(slab + lane * kTcSlabStride + i) = make_float4(o[0], o[1], o[2], o[3]);
+                    *reinterpret_cast<float4 *>(slab + lane * kTcSlabStride + i) =
+                        live_row ? make_float4(o[0], o[1], o[2], o[3]) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
                 __syncwarp();
                 if (p.moments) {                                   // lane = column: four independent partial sums
                     float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                     for (int rr = 0; rr < 32; ++rr) {
-                        const float t = rr < nrow ? slab[rr * kTcSlabStride + lane] : 0.0f;
+                        const float t = slab[rr * kTcSlabStride + lane];
                         s1[rr & 3] += t;
                         s2[rr & 3] = fmaf(t, t, s2[rr & 3]);
                     }
@@ -379,7 +428,8 @@ k_linear_tc(const __grid_constant__ TcParams p)
                     m_sq[u] += (double)((s2[0] + s2[1]) + (s2[2] + s2[3]));
                 }
                 const int c4 = lane & 7;
-                if ((NO & 3) == 0) {
+                if (p.dbg == 5) {                                  // experiment: no global stores (203 -> 109 us at 64 -> 128)
+                } else if ((NO & 3) == 0) {
                     if (g * 32 + c4 * 4 < NO) {
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
@@ -393,6 +443,10 @@ k_linear_tc(const __grid_constant__ TcParams p)
                     for (int rr = 0; rr < nrow; ++rr) p.y[(row0 + rr) * NO + g * 32 + lane] = slab[rr * kTcSlabStride + lane];
                 }
             }
+            es += clock64() - e2;
+        }
+        if (p.dbg == 4 && blockIdx.x == 0 && warp == kTcLoadWarps && lane == 0) {
+            g_tc_stats[6] = ew; g_tc_stats[7] = el; g_tc_stats[8] = es; g_tc_stats[9] = my_tiles;
         }
         if (p.moments) {
 #pragma unroll

@@ -267,7 +267,9 @@ def _trunk_supported(model: nn.Sequential, x: torch.Tensor) -> bool:
     C = lin[0].in_features
     hs = [m.out_features for m in lin[:-1]]
     return (3 <= C <= 8 and lin[-1].out_features == C and all(h % 8 == 0 and 8 <= h <= 128 for h in hs)
-            and hs[0] >= 16 and hs[-1] >= 16 and all(a * b < 128 * 128 for a, b in zip(hs[:-1], hs[1:])))
+            and hs[0] >= 16 and hs[-1] >= 16
+            # the weights of a layer (hi + lo, 32-column blocks x 32-row groups) stay in 64 KB of shared memory, both ways
+            and all(-(-a // 32) * -(-b // 32) <= 8 for a, b in zip(hs[:-1], hs[1:])))
 
 
 def _gradient_hook(grad):
