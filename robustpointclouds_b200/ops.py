@@ -554,7 +554,8 @@ def trunk_fwd(desc, xn: torch.Tensor, widths: Sequence[int]):
 
 def trunk_bwd(desc, xn: torch.Tensor, widths: Sequence[int], ys, stats: torch.Tensor, raw: torch.Tensor, g_raw: torch.Tensor,
               param_shapes, want_grad_xn: bool = False):
-    """Backward of ``trunk_fwd`` (``rpc_trunk_bwd``): -> (grad_w list, grad_b list, grad_gamma list, grad_beta list, grad_xn)."""
+    """Backward of ``trunk_fwd`` (``rpc_trunk_bwd``): -> (grad_w list, grad_b list, grad_gamma list, grad_beta list, grad_xn,
+    flat) where ``flat`` is the one buffer all parameter gradients are views of."""
     dev = _need_cuda(xn, g_raw)
     K, C = xn.shape
     g_raw = _f32c(g_raw)
@@ -579,7 +580,7 @@ def trunk_bwd(desc, xn: torch.Tensor, widths: Sequence[int], ys, stats: torch.Te
                                   _stream(dev))
     _lib.check(st, "rpc_trunk_bwd")
     assert nl == len(gg)
-    return gw, gb, gg, gbe, gxn
+    return gw, gb, gg, gbe, gxn, flat
 
 
 def bn_relu_fwd(y: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, momentum: float,

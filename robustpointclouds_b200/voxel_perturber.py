@@ -232,6 +232,9 @@ class _TrunkFn(torch.autograd.Function):
         torch._foreach_add_([m.num_batches_tracked for m in bns], 1)
         ctx.save_for_backward(xn, raw, ybuf, stats, *params)
         ctx.nl, ctx.widths, ctx.bns = nl, widths, bns
+        # (gradients are pre-clamped only for parameters that carry the hook, i.e. the usual case; a caller that removed
+        # the hooks gets raw gradients)
+        ctx.hooked = all(getattr(q, "_backward_hooks", None) for q in params)
         return raw
 
     @staticmethod
@@ -250,11 +253,17 @@ class _TrunkFn(torch.autograd.Function):
                               [params[4 * l + 2] for l in range(nl)], [params[4 * l + 3] for l in range(nl)],
                               [None] * nl, [None] * nl, [m.eps for m in bns], [m.momentum for m in bns])
         shapes = [tuple(params[4 * l].shape) for l in range(nl)] + [tuple(params[4 * nl].shape)]
-        gw, gb, gg, gbe, g_xn = ops.trunk_bwd(desc, xn, widths, ys, stats, raw, g_raw, shapes, ctx.needs_input_grad[0])
+        gw, gb, gg, gbe, g_xn, flat = ops.trunk_bwd(desc, xn, widths, ys, stats, raw, g_raw, shapes, ctx.needs_input_grad[0])
         grads = []
         for l in range(nl):
             grads += [gw[l], gb[l], gg[l], gbe[l]]
         grads += [gw[nl], gb[nl]]
+        if ctx.hooked:
+            # the reference's gradient hook (nan_to_num, clamp +-0.1; voxel_perturber.py:465-475) on all of them at once
+            torch.clamp_(torch.nan_to_num_(flat, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
+            _PRECLAMPED.clear()
+            for t in grads:
+                _PRECLAMPED[t.data_ptr()] = t.numel()
         return (g_xn, None, *grads)
 
 
@@ -272,9 +281,18 @@ def _trunk_supported(model: nn.Sequential, x: torch.Tensor) -> bool:
             and all(-(-a // 32) * -(-b // 32) <= 8 for a, b in zip(hs[:-1], hs[1:])))
 
 
+# storage pointers of gradients that left _TrunkFn.backward already through nan_to_num + clamp (one pass over the flat
+# buffer they are views of): the per-parameter hook recognises them and returns without launching anything.  With 22
+# trunk parameters the reference's hook is 44 tiny launches and their Python overhead per step -- a quarter of the KITTI
+# step's wall time (profiles/r02_mlp_in_loop_launches.txt).
+_PRECLAMPED: Dict[int, int] = {}
+
+
 def _gradient_hook(grad):
     if grad is None:
         return grad
+    if _PRECLAMPED.pop(grad.data_ptr(), None) == grad.numel():
+        return None                                          # same values the two ops below would produce
     return torch.clamp(torch.nan_to_num(grad, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
 
 
