@@ -16,6 +16,7 @@
 #include "linear.cuh"
 #include "bnrelu.cuh"
 #include "mlp_tc.cuh"
+#include "wgrad_tc.cuh"
 
 using namespace rpc;
 
@@ -912,6 +913,27 @@ RPC_API int rpc_linear_wgrad_bn(const float *g, const float *a, const float *bn_
     if (cudaMemsetAsync(grad_w, 0, sizeof(float) * M * N, st) != cudaSuccess) return RPC_ERR_CUDA;
     if (grad_b && cudaMemsetAsync(grad_b, 0, sizeof(float) * M, st) != cudaSuccess) return RPC_ERR_CUDA;
     if (K == 0) return RPC_OK;
+    // 128 x 64 / 64 x 128 layers (the trunk of the KITTI config): 3 x TF32 on tcgen05, the result in one TMEM accumulator
+    static const bool no_tc = getenv("RPC_WGRAD_SIMT") != nullptr;     // (A/B switch)
+    if (!no_tc && ((M == 128 && N == 64) || (M == 64 && N == 128)) && K >= 4096 && !misaligned(g) && !misaligned(a)) {
+        WgParams wp;
+        memset(&wp, 0, sizeof(wp));
+        wp.g = g; wp.a = a; wp.K = K; wp.M = M; wp.N = N;
+        wp.bn_mean = bn_mean; wp.bn_invstd = bn_invstd; wp.bn_gamma = bn_gamma; wp.bn_beta = bn_beta;
+        wp.gw = grad_w; wp.gb = grad_b;
+        static bool attr_done[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+            if (cudaFuncSetAttribute(k_wgrad_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wg_smem_bytes()) != cudaSuccess)
+                return RPC_ERR_CUDA;
+            attr_done[dev] = true;
+        }
+        const int64_t stages = (K + kWgRows - 1) / kWgRows;
+        const int sms = device_sms();
+        k_wgrad_tc<<<(int)(stages < sms ? stages : sms), kWgThreads, wg_smem_bytes(), st>>>(wp);
+        return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+    }
     if (M <= 8 || N <= 8) {
         // skinny layer: a stream over the wide operand; the wider of the two is "wide" (ties: g)
         const bool wide_is_g = M >= N;

@@ -443,9 +443,11 @@ def attention_gate_bwd(g_out: torch.Tensor, xn: torch.Tensor, t: torch.Tensor, w
     return grad_t, grad_xn, gw1, gb1, gw2, gb2
 
 
-def linear_wgrad(g: torch.Tensor, a: torch.Tensor, want_bias: bool = True):
+def linear_wgrad(g: torch.Tensor, a: torch.Tensor, want_bias: bool = True, bn=None):
     """(grad_weight [M, N], grad_bias [M] or None) of ``out = a @ W.T + b`` from ``g = dL/d(out)`` [K, M] and the layer
-    input ``a`` [K, N]; M, N <= 128 (the Linear layers of /root/reference/models/adversarial/voxel_perturber.py:82-101)."""
+    input ``a`` [K, N]; M, N <= 128 (the Linear layers of /root/reference/models/adversarial/voxel_perturber.py:82-101).
+    ``bn=(mean, invstd, gamma, beta)``: ``a`` is the previous layer's pre-activation and the input is recomputed as
+    relu(batch_norm(a)) while it is staged (``rpc_linear_wgrad_bn``).  128 x 64 / 64 x 128 layers run on the tensor cores."""
     dev = _need_cuda(g, a)
     g, a = _f32c(g), _f32c(a)
     K, M = g.shape
@@ -454,8 +456,10 @@ def linear_wgrad(g: torch.Tensor, a: torch.Tensor, want_bias: bool = True):
         raise ValueError("linear_wgrad: g and a must have the same number of rows")
     gw = torch.empty((M, N), dtype=torch.float32, device=dev)
     gb = torch.empty((M,), dtype=torch.float32, device=dev) if want_bias else None
-    st = _lib.lib().rpc_linear_wgrad(_ptr(g), _ptr(a), K, M, N, _ptr(gw), _ptr(gb), _stream(dev))
-    _lib.check(st, "rpc_linear_wgrad")
+    b4 = [None] * 4 if bn is None else [_f32c(t) for t in bn]
+    st = _lib.lib().rpc_linear_wgrad_bn(_ptr(g), _ptr(a), _ptr(b4[0]), _ptr(b4[1]), _ptr(b4[2]), _ptr(b4[3]), K, M, N, _ptr(gw),
+                                        _ptr(gb), _stream(dev))
+    _lib.check(st, "rpc_linear_wgrad_bn")
     return gw, gb
 
 

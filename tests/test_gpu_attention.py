@@ -166,6 +166,8 @@ def test_module_large_batch_forward_path(train):
         torch.manual_seed(3)
         adv = VoxelPerturber(hidden_channels=[64, 128, 64], fused_wgrad=fused, fused_trunk=False, nan_guards=False).build(4, DEV).train(train)
         if train:
+            for q in adv.parameters():
+                q._backward_hooks = None                       # compare the sums themselves, in front of the +-0.1 clamp
             y, _ = adv(x)
             y.sum().backward()
             ys.append((y.detach(), adv.model[3].weight.grad.clone()))
@@ -174,7 +176,10 @@ def test_module_large_batch_forward_path(train):
                 ys.append((adv(x)[0], None))
     torch.testing.assert_close(ys[0][0], ys[1][0], rtol=1e-5, atol=1e-5)
     if train:
-        torch.testing.assert_close(ys[0][1], ys[1][1], rtol=1e-3, atol=1e-5)
+        # two fp32 summations over 600 k rows (cuBLAS split-K against this library's kernel -- 3 x TF32 on the tensor cores
+        # for this 128 x 64 layer, ~5e-7 of scale against fp64): 1e-4 of the tensor's scale
+        scale = float(ys[1][1].abs().max())
+        torch.testing.assert_close(ys[0][1], ys[1][1], rtol=0, atol=1e-4 * scale)
 
 
 # ------------------------------------------------------------------ rpc_bn_relu_fwd/bwd (third slice of SURVEY 8f row 2)
