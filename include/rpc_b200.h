@@ -379,6 +379,17 @@ int rpc_bn_finalize(const double *moments, int64_t K, const int32_t *k_dev, int 
                     float *running_mean, float *running_var, float *save_mean, float *save_invstd, void *stream);
 int rpc_bn_relu_apply(const float *y, int64_t K, const int32_t *k_dev, int H, const float *mean, const float *invstd,
                       const float *gamma, const float *beta, float *z, void *stream);
+/* Input gradient of a Linear layer (grad_in [K, NO] = g [K, NI] * w, w [NI, NO] = the nn.Linear weight) whose epilogue also
+ * reduces the backward of the BatchNorm + ReLU BELOW it: v [K, NO] is that layer's pre-activation with statistics v_mean /
+ * v_invstd / v_gamma / v_beta, and red (fp64 [2 * NO], zeroed by the call) receives sum g' and sum g' * vhat with g' =
+ * grad_in where relu(bn(v)) was open -- what rpc_bn_relu_bwd's first pass computes.  rpc_bn_relu_bwd_sums is
+ * rpc_bn_relu_bwd with those sums given (its reduction pass over g and y is skipped).  NI > 8 (tensor-core kernel only). */
+int rpc_linear_dgrad_bnred(const float *g, int64_t K, int NI, int NO, const float *w, const float *v, const float *v_mean,
+                           const float *v_invstd, const float *v_gamma, const float *v_beta, double *red, float *grad_in,
+                           void *stream);
+int rpc_bn_relu_bwd_sums(const float *g, const float *y, const float *save_mean, const float *save_invstd, const float *gamma,
+                         const float *beta, int64_t K, int H, const double *sums, float *grad_y, float *grad_gamma,
+                         float *grad_beta, void *stream);
 
 /* The whole training-mode trunk in one call each way (the same launches as the per-layer entry points, issued from C):
  * `self.model(voxel_features_normalized)` of models/adversarial/voxel_perturber.py:176 and its autograd.

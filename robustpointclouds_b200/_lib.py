@@ -27,7 +27,7 @@ SYMBOLS = (
     "rpc_voxel_centers", "rpc_points_range_filter", "rpc_points_range_filter_static", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
     "rpc_attention_scratch_bytes", "rpc_attention_gate_fwd", "rpc_attention_gate_bwd", "rpc_linear_wgrad",
     "rpc_bn_scratch_bytes", "rpc_bn_relu_fwd", "rpc_bn_relu_bwd",
-    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply", "rpc_trunk_fwd", "rpc_trunk_bwd", "rpc_linear_wgrad_bn",
+    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply", "rpc_trunk_fwd", "rpc_trunk_bwd", "rpc_linear_wgrad_bn", "rpc_linear_dgrad_bnred", "rpc_bn_relu_bwd_sums",
 )
 
 
@@ -140,6 +140,8 @@ def lib() -> ctypes.CDLL:
     L.rpc_attention_gate_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp]
     L.rpc_attention_gate_bwd.argtypes = [vp] * 7 + [i64, i32] + [vp] * 8
     L.rpc_linear_wgrad.argtypes = [vp, vp, i64, i32, i32, vp, vp, vp]
+    L.rpc_linear_dgrad_bnred.argtypes = [vp, i64, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.rpc_bn_relu_bwd_sums.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, vp, vp, vp, vp, vp]
     L.rpc_linear_wgrad_bn.argtypes = [vp, vp, vp, vp, vp, vp, i64, i32, i32, vp, vp, vp]
     L.rpc_bn_scratch_bytes.restype = ctypes.c_size_t
     L.rpc_bn_scratch_bytes.argtypes = []

@@ -1016,35 +1016,51 @@ RPC_API int rpc_bn_relu_fwd(const float *y, int64_t K, int H, const float *gamma
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
-RPC_API int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, const float *save_invstd,
-                            const float *gamma, const float *beta, int64_t K, int H, double *scratch, float *grad_y,
-                            float *grad_gamma, float *grad_beta, void *stream)
+static int bn_relu_bwd_impl(const float *g, const float *y, const float *save_mean, const float *save_invstd,
+                            const float *gamma, const float *beta, int64_t K, int H, double *scratch, bool have_sums,
+                            float *grad_y, float *grad_gamma, float *grad_beta, void *stream)
 {
     if (K < 1 || H < 1 || H > kBnMaxH) return RPC_ERR_CONFIG;
     if (!g || !y || !save_mean || !save_invstd || !gamma || !beta || !scratch || !grad_y) return RPC_ERR_NULL;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * H, st) != cudaSuccess) return RPC_ERR_CUDA;
+    if (!have_sums && cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * H, st) != cudaSuccess) return RPC_ERR_CUDA;
     const bool vec = bn_vec_pays(K, H) && !misaligned(g) && !misaligned(y) && !misaligned(grad_y);
     const int blocks = bn_blocks(K, H, vec ? 4 : 1);
     if (vec) {
-        k_bn_relu_bwd_reduce<4><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
+        if (!have_sums) k_bn_relu_bwd_reduce<4><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
         k_bn_relu_bwd_elemt<4><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H,
                                                               grad_y, grad_gamma, grad_beta);
     } else {
-        k_bn_relu_bwd_reduce<1><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
+        if (!have_sums) k_bn_relu_bwd_reduce<1><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch);
         k_bn_relu_bwd_elemt<1><<<blocks, kBnThreads, 0, st>>>(g, y, save_mean, save_invstd, gamma, beta, scratch, K, H,
                                                               grad_y, grad_gamma, grad_beta);
     }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
 }
 
+RPC_API int rpc_bn_relu_bwd(const float *g, const float *y, const float *save_mean, const float *save_invstd,
+                            const float *gamma, const float *beta, int64_t K, int H, double *scratch, float *grad_y,
+                            float *grad_gamma, float *grad_beta, void *stream)
+{
+    return bn_relu_bwd_impl(g, y, save_mean, save_invstd, gamma, beta, K, H, scratch, false, grad_y, grad_gamma, grad_beta, stream);
+}
+
+RPC_API int rpc_bn_relu_bwd_sums(const float *g, const float *y, const float *save_mean, const float *save_invstd,
+                                 const float *gamma, const float *beta, int64_t K, int H, const double *sums, float *grad_y,
+                                 float *grad_gamma, float *grad_beta, void *stream)
+{
+    return bn_relu_bwd_impl(g, y, save_mean, save_invstd, gamma, beta, K, H, const_cast<double *>(sums), true, grad_y, grad_gamma,
+                            grad_beta, stream);
+}
+
 }  // extern "C"
 
 extern "C" {
 // ------------------------------------------------------------------ Linear layers of the MLP trunk (tcgen05, 3 x TF32)
-RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int NI, int NO, const float *w, int w_layout,
+static int linear_fwd_impl(const float *x, int64_t K, const int32_t *k_dev, int NI, int NO, const float *w, int w_layout,
                            const float *bias, const float *in_mean, const float *in_invstd, const float *in_gamma,
-                           const float *in_beta, int epi_tanh, double *moments, float *y, void *stream)
+                           const float *in_beta, int epi_tanh, double *moments, const float *red_v, const float *const *red_bn,
+                           float *y, void *stream)
 {
     if (K < 0 || NI < 1 || NO < 1 || NI > kTcMaxDim || NO > kTcMaxDim || (w_layout != 0 && w_layout != 1)) return RPC_ERR_CONFIG;
     if (K == 0) return RPC_OK;
@@ -1058,6 +1074,10 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
     p.x = x; p.w = w; p.bias = bias; p.y = y; p.k_dev = k_dev; p.K = K; p.NI = NI; p.NO = NO; p.w_layout = w_layout;
     p.in_mean = in_mean; p.in_invstd = in_invstd; p.in_gamma = in_gamma; p.in_beta = in_beta;
     p.epi_tanh = epi_tanh; p.moments = moments;
+    if (red_v) {
+        if (NI <= 8 || !moments || !red_bn) return RPC_ERR_CONFIG;      // only the tensor-core kernel has this epilogue
+        p.red_v = red_v; p.red_mean = red_bn[0]; p.red_invstd = red_bn[1]; p.red_gamma = red_bn[2]; p.red_beta = red_bn[3];
+    }
     { static const char *dbg = getenv("RPC_TC_DBG"); p.dbg = dbg ? atoi(dbg) : 0; }
     const int sms = device_sms();
     if (NI <= 8) {                                                   // first layer / input gradient of the last: a stream
@@ -1084,6 +1104,23 @@ RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int 
         k_linear_tc<<<grid, kTcThreads2, smem, st>>>(p);
     }
     return cudaPeekAtLastError() == cudaSuccess ? RPC_OK : RPC_ERR_CUDA;
+}
+
+RPC_API int rpc_linear_fwd(const float *x, int64_t K, const int32_t *k_dev, int NI, int NO, const float *w, int w_layout,
+                           const float *bias, const float *in_mean, const float *in_invstd, const float *in_gamma,
+                           const float *in_beta, int epi_tanh, double *moments, float *y, void *stream)
+{
+    return linear_fwd_impl(x, K, k_dev, NI, NO, w, w_layout, bias, in_mean, in_invstd, in_gamma, in_beta, epi_tanh, moments,
+                           nullptr, nullptr, y, stream);
+}
+
+RPC_API int rpc_linear_dgrad_bnred(const float *g, int64_t K, int NI, int NO, const float *w, const float *v,
+                                   const float *v_mean, const float *v_invstd, const float *v_gamma, const float *v_beta,
+                                   double *red, float *grad_in, void *stream)
+{
+    if (!v || !v_mean || !v_invstd || !v_gamma || !v_beta || !red) return RPC_ERR_NULL;
+    const float *bn[4] = {v_mean, v_invstd, v_gamma, v_beta};
+    return linear_fwd_impl(g, K, nullptr, NI, NO, w, 1, nullptr, nullptr, nullptr, nullptr, nullptr, 0, red, v, bn, grad_in, stream);
 }
 
 RPC_API int rpc_bn_finalize(const double *moments, int64_t K, const int32_t *k_dev, int H, float eps, float momentum,
@@ -1197,11 +1234,15 @@ RPC_API int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, f
     if (rc != RPC_OK) return rc;
     rc = rpc_linear_fwd(g_y, K, nullptr, C, hl, t->w[nl], 1, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, g_a, stream);
     if (rc != RPC_OK) return rc;
+    bool have_sums = false;                                        // the producer of g_a left this layer's BatchNorm reductions in `scratch`
     for (int l = nl - 1; l >= 0; --l) {
         const int h = t->width[l], hin = l > 0 ? t->width[l - 1] : C;
-        rc = rpc_bn_relu_bwd(g_a, y[l], st_of[l], st_of[l] + h, t->gamma[l], t->beta[l], K, h, scratch, g_y, grad_gamma[l],
-                             grad_beta[l], stream);
+        rc = have_sums ? rpc_bn_relu_bwd_sums(g_a, y[l], st_of[l], st_of[l] + h, t->gamma[l], t->beta[l], K, h, scratch, g_y,
+                                              grad_gamma[l], grad_beta[l], stream)
+                       : rpc_bn_relu_bwd(g_a, y[l], st_of[l], st_of[l] + h, t->gamma[l], t->beta[l], K, h, scratch, g_y,
+                                         grad_gamma[l], grad_beta[l], stream);
         if (rc != RPC_OK) return rc;
+        have_sums = false;
         // (the layer input relu(bn(y[l-1])) is recomputed while the weight-gradient kernel stages it)
         if (l > 0)
             rc = rpc_linear_wgrad_bn(g_y, y[l - 1], st_of[l - 1], st_of[l - 1] + hin, t->gamma[l - 1], t->beta[l - 1], K, h, hin,
@@ -1209,10 +1250,23 @@ RPC_API int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, f
         else
             rc = rpc_linear_wgrad(g_y, xn, K, h, C, grad_w[l], grad_b[l], stream);
         if (rc != RPC_OK) return rc;
-        float *dst = l > 0 ? g_a : grad_xn;
-        if (dst) {
-            rc = rpc_linear_fwd(g_y, K, nullptr, h, hin, t->w[l], 1, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, dst, stream);
+        // (measured: with the reductions in the epilogue the nuScenes backward is 0.55 ms SLOWER -- the epilogue is what
+        // bounds the tensor-core kernel, and the separate reduction kernel streams at 4.5 TB/s -- so it is opt-in)
+        static const bool bnred = getenv("RPC_BNRED") != nullptr;
+        if (l > 0 && h > 8 && bnred) {
+            // input gradient on the tensor cores; its epilogue also reduces the BatchNorm backward of layer l - 1 (sum g',
+            // sum g' * xhat), so that layer's rpc_bn_relu_bwd skips its reduction pass.  (`scratch` is free again: the
+            // elementwise kernel of layer l above has been enqueued and everything here is stream-ordered.)
+            rc = rpc_linear_dgrad_bnred(g_y, K, h, hin, t->w[l], y[l - 1], st_of[l - 1], st_of[l - 1] + hin, t->gamma[l - 1],
+                                        t->beta[l - 1], scratch, g_a, stream);
             if (rc != RPC_OK) return rc;
+            have_sums = true;
+        } else {
+            float *dst = l > 0 ? g_a : grad_xn;
+            if (dst) {
+                rc = rpc_linear_fwd(g_y, K, nullptr, h, hin, t->w[l], 1, nullptr, nullptr, nullptr, nullptr, nullptr, 0, nullptr, dst, stream);
+                if (rc != RPC_OK) return rc;
+            }
         }
     }
     return RPC_OK;

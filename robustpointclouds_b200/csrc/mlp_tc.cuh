@@ -49,6 +49,9 @@ struct TcParams {
     int dbg;                                     // experiments (RPC_TC_DBG): 1 = one MMA per K step instead of three, 2 = none,
                                                  // 4 = role cycle counters (tools/dbg_tc_stats.py), 5 = no global stores
     double *moments;                             // [2 * NO] or NULL: += column sums and sums of squares of y
+    // input-gradient mode: y is dL/d(relu(bn(v))) of the layer below and `moments` receives that BatchNorm's backward
+    // reductions instead -- sum g' and sum g' * vhat with g' = y where the ReLU was open (what k_bn_relu_bwd_reduce computes)
+    const float *red_v, *red_mean, *red_invstd, *red_gamma, *red_beta;   // v [K, NO] and its statistics, or NULL
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -416,7 +419,31 @@ k_linear_tc(const __grid_constant__ TcParams p)
                         live_row ? make_float4(o[0], o[1], o[2], o[3]) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
                 __syncwarp();
-                if (p.moments) {                                   // lane = column: four independent partial sums
+                if (p.moments && p.red_v) {                        // BatchNorm-backward reductions of the layer below
+                    const int col = g * 32 + lane;
+                    const bool okc = col < NO;
+                    const float mean = okc ? __ldg(p.red_mean + col) : 0.f, invstd = okc ? __ldg(p.red_invstd + col) : 0.f;
+                    const float ga = okc ? __ldg(p.red_gamma + col) : 0.f, be = okc ? __ldg(p.red_beta + col) : 0.f;
+                    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int r0 = 0; r0 < 32; r0 += 8) {
+                        float vv[8];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)            // a row of the group is 128 contiguous bytes across the lanes
+                            vv[q] = (okc && r0 + q < nrow) ? __ldg(p.red_v + (row0 + r0 + q) * NO + col) : 0.0f;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float gv = slab[(r0 + q) * kTcSlabStride + lane];
+                            const float xh = __fmul_rn(__fsub_rn(vv[q], mean), invstd);
+                            const float t = __fadd_rn(__fmul_rn(xh, ga), be);
+                            const float gp = t <= 0.0f ? 0.0f : gv;    // threshold_backward's rule, as k_bn_relu_bwd_reduce
+                            s1[q & 3] += gp;
+                            s2[q & 3] = fmaf(gp, xh, s2[q & 3]);
+                        }
+                    }
+                    m_sum[u] += (double)((s1[0] + s1[1]) + (s1[2] + s1[3]));
+                    m_sq[u] += (double)((s2[0] + s2[1]) + (s2[2] + s2[3]));
+                } else if (p.moments) {                            // lane = column: four independent partial sums
                     float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                     for (int rr = 0; rr < 32; ++rr) {

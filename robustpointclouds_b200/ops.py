@@ -606,9 +606,27 @@ def bn_relu_fwd(y: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: f
     return z, mean, invstd
 
 
+def linear_dgrad_bnred(g: torch.Tensor, w: torch.Tensor, v: torch.Tensor, bn):
+    """Input gradient ``g @ w`` (w [NI, NO], the nn.Linear weight) whose epilogue also reduces the backward of the
+    BatchNorm + ReLU below (``v`` [K, NO] = that layer's pre-activation, ``bn`` = its (mean, invstd, gamma, beta)):
+    -> (grad_in [K, NO], sums float64 [2 * NO]) for ``bn_relu_bwd(..., sums=sums)`` (``rpc_linear_dgrad_bnred``)."""
+    dev = _need_cuda(g, w, v)
+    g, w, v = _f32c(g), _f32c(w), _f32c(v)
+    K, NI = g.shape
+    NO = w.shape[1]
+    out = torch.empty((K, NO), dtype=torch.float32, device=dev)
+    sums = torch.empty((2 * NO,), dtype=torch.float64, device=dev)
+    b4 = [_f32c(t) for t in bn]
+    st = _lib.lib().rpc_linear_dgrad_bnred(_ptr(g), K, NI, NO, _ptr(w), _ptr(v), _ptr(b4[0]), _ptr(b4[1]), _ptr(b4[2]), _ptr(b4[3]),
+                                           _ptr(sums), _ptr(out), _stream(dev))
+    _lib.check(st, "rpc_linear_dgrad_bnred")
+    return out, sums
+
+
 def bn_relu_bwd(g: torch.Tensor, y: torch.Tensor, mean: torch.Tensor, invstd: torch.Tensor, gamma: torch.Tensor,
-                beta: torch.Tensor):
-    """-> (grad_y, grad_gamma, grad_beta) of ``bn_relu_fwd``; the ReLU mask is recomputed from y."""
+                beta: torch.Tensor, sums: Optional[torch.Tensor] = None):
+    """-> (grad_y, grad_gamma, grad_beta) of ``bn_relu_fwd``; the ReLU mask is recomputed from y.  ``sums``: the reductions
+    already made by the producer of g (``linear_dgrad_bnred``): the reduction pass is skipped."""
     dev = _need_cuda(g, y, mean, invstd, gamma, beta)
     g, y = _f32c(g), _f32c(y)
     K, H = y.shape
@@ -616,6 +634,11 @@ def bn_relu_bwd(g: torch.Tensor, y: torch.Tensor, mean: torch.Tensor, invstd: to
     gg = torch.empty((H,), dtype=torch.float32, device=dev)
     gb = torch.empty((H,), dtype=torch.float32, device=dev)
     scratch = _scratch64(_lib.lib().rpc_bn_scratch_bytes() // 8, dev)
+    if sums is not None:
+        st = _lib.lib().rpc_bn_relu_bwd_sums(_ptr(g), _ptr(y), _ptr(mean), _ptr(invstd), _ptr(_f32c(gamma)), _ptr(_f32c(beta)), K, H,
+                                             _ptr(sums), _ptr(gy), _ptr(gg), _ptr(gb), _stream(dev))
+        _lib.check(st, "rpc_bn_relu_bwd_sums")
+        return gy, gg, gb
     st = _lib.lib().rpc_bn_relu_bwd(_ptr(g), _ptr(y), _ptr(mean), _ptr(invstd), _ptr(_f32c(gamma)), _ptr(_f32c(beta)), K, H,
                                     _ptr(scratch), _ptr(gy), _ptr(gg), _ptr(gb), _stream(dev))
     _lib.check(st, "rpc_bn_relu_bwd")

@@ -81,6 +81,29 @@ def test_linear_wgrad_vs_fp64(K, M, N, with_bn):
     assert _rel(gw, rw) < TOL and _rel(gb, rb) < TOL
 
 
+@pytest.mark.parametrize("K,NI,NO", [(4099, 128, 64), (70001, 64, 128), (300, 64, 32)])
+def test_dgrad_with_fused_bn_backward_reductions(K, NI, NO):
+    """rpc_linear_dgrad_bnred + rpc_bn_relu_bwd_sums == rpc_linear_fwd (transposed) + rpc_bn_relu_bwd, and both == fp64"""
+    g_ = torch.Generator(DEV).manual_seed(K)
+    g = torch.randn(K, NI, device=DEV, generator=g_)
+    w = torch.randn(NI, NO, device=DEV, generator=g_) * 0.2
+    v = torch.randn(K, NO, device=DEV, generator=g_) * 2 + 0.4
+    mean, invstd = v.mean(0), 1.0 / torch.sqrt(v.var(0, unbiased=False) + 1e-3)
+    gamma, beta = torch.randn(NO, device=DEV, generator=g_), torch.randn(NO, device=DEV, generator=g_) * 0.3
+    ga, sums = ops.linear_dgrad_bnred(g, w, v, (mean, invstd, gamma, beta))
+    ga0 = ops.linear_fwd(g, w, transposed=True)
+    assert torch.equal(ga, ga0)
+    gy, gg, gb = ops.bn_relu_bwd(ga, v, mean, invstd, gamma, beta, sums=sums)
+    gy0, gg0, gb0 = ops.bn_relu_bwd(ga0, v, mean, invstd, gamma, beta)
+    for a, b in ((gy, gy0), (gg, gg0), (gb, gb0)):
+        assert _rel(a, b.double()) < TOL
+    # fp64: autograd through relu(batch_norm(v)) with the upstream gradient g @ w
+    vd = v.double().requires_grad_(True)
+    z = torch.relu(torch.nn.functional.batch_norm(vd, None, None, gamma.double(), beta.double(), True, 0.1, 1e-3))
+    z.backward(g.double() @ w.double())
+    assert _rel(gy, vd.grad) < 5e-5                                   # (mean / invstd above are fp32 values)
+
+
 def test_bn_finalize_matches_batch_norm():
     K, H = 5000, 128
     g = torch.Generator(DEV).manual_seed(3)
