@@ -412,6 +412,10 @@ typedef struct rpc_trunk_desc {
 } rpc_trunk_desc;
 int rpc_trunk_fwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, float *stats, double *scratch,
                   float *raw, void *stream);
+/* eval mode (no gradient): BatchNorm uses the running statistics, given per layer as (mean [width], invstd [width]) in
+ * `stats`; work = 2 * K * max(width) floats; nothing is kept */
+int rpc_trunk_fwd_eval(const rpc_trunk_desc *t, const float *xn, int64_t K, const float *stats, float *work, float *raw,
+                       void *stream);
 int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, const float *stats, const float *raw,
                   const float *g_raw, float *work, double *scratch, float *const *grad_w, float *const *grad_b,
                   float *const *grad_gamma, float *const *grad_beta, float *grad_xn, void *stream);

@@ -27,7 +27,7 @@ SYMBOLS = (
     "rpc_voxel_centers", "rpc_points_range_filter", "rpc_points_range_filter_static", "rpc_momentum_apply_fwd", "rpc_momentum_apply_bwd", "rpc_moments_bytes", "rpc_normalize_fwd", "rpc_perturb_losses_fwd", "rpc_perturb_losses_bwd",
     "rpc_attention_scratch_bytes", "rpc_attention_gate_fwd", "rpc_attention_gate_bwd", "rpc_linear_wgrad",
     "rpc_bn_scratch_bytes", "rpc_bn_relu_fwd", "rpc_bn_relu_bwd",
-    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply", "rpc_trunk_fwd", "rpc_trunk_bwd", "rpc_linear_wgrad_bn", "rpc_linear_dgrad_bnred", "rpc_bn_relu_bwd_sums",
+    "rpc_linear_fwd", "rpc_bn_finalize", "rpc_bn_relu_apply", "rpc_trunk_fwd", "rpc_trunk_fwd_eval", "rpc_trunk_bwd", "rpc_linear_wgrad_bn", "rpc_linear_dgrad_bnred", "rpc_bn_relu_bwd_sums",
 )
 
 
@@ -152,6 +152,7 @@ def lib() -> ctypes.CDLL:
     L.rpc_bn_relu_apply.argtypes = [vp, i64, vp, i32, vp, vp, vp, vp, vp, vp]
     tdp, vpp = ctypes.POINTER(TrunkDesc), ctypes.POINTER(vp)
     L.rpc_trunk_fwd.argtypes = [tdp, vp, i64, vpp, vp, vp, vp, vp]
+    L.rpc_trunk_fwd_eval.argtypes = [tdp, vp, i64, vp, vp, vp, vp]
     L.rpc_trunk_bwd.argtypes = [tdp, vp, i64, vpp, vp, vp, vp, vp, vp, vpp, vpp, vpp, vpp, vp, vp]
     L.rpc_profile_enable.restype = None
     L.rpc_profile_enable.argtypes = [i32]

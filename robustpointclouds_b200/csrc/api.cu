@@ -1204,6 +1204,32 @@ RPC_API int rpc_trunk_fwd(const rpc_trunk_desc *t, const float *xn, int64_t K, f
     return rpc_linear_fwd(x, K, nullptr, ni, t->C, t->w[t->nl], 0, t->b[t->nl], mean, invstd, ga, be, 1, nullptr, raw, stream);
 }
 
+RPC_API int rpc_trunk_fwd_eval(const rpc_trunk_desc *t, const float *xn, int64_t K, const float *stats, float *work, float *raw,
+                               void *stream)
+{
+    // eval mode: BatchNorm normalises with the running statistics the caller turned into (mean, invstd) per layer (`stats`,
+    // laid out like rpc_trunk_fwd's); nothing is kept, two [K, max width] areas of `work` are used in turn
+    int rc = trunk_check(t);
+    if (rc != RPC_OK) return rc;
+    if (K < 1) return RPC_ERR_CONFIG;
+    if (!xn || !stats || !work || !raw) return RPC_ERR_NULL;
+    int maxw = t->C;
+    for (int l = 0; l < t->nl; ++l) maxw = t->width[l] > maxw ? t->width[l] : maxw;
+    const float *x = xn, *st_l = stats;
+    int ni = t->C;
+    const float *mean = nullptr, *invstd = nullptr, *ga = nullptr, *be = nullptr;
+    for (int l = 0; l < t->nl; ++l) {
+        const int no = t->width[l];
+        float *y = work + (size_t)(l & 1) * K * maxw;
+        rc = rpc_linear_fwd(x, K, nullptr, ni, no, t->w[l], 0, t->b[l], mean, invstd, ga, be, 0, nullptr, y, stream);
+        if (rc != RPC_OK) return rc;
+        mean = st_l; invstd = st_l + no; ga = t->gamma[l]; be = t->beta[l];
+        st_l += 2 * no;
+        x = y; ni = no;
+    }
+    return rpc_linear_fwd(x, K, nullptr, ni, t->C, t->w[t->nl], 0, t->b[t->nl], mean, invstd, ga, be, 1, nullptr, raw, stream);
+}
+
 RPC_API int rpc_trunk_bwd(const rpc_trunk_desc *t, const float *xn, int64_t K, float *const *y, const float *stats,
                           const float *raw, const float *g_raw, float *work, double *scratch, float *const *grad_w,
                           float *const *grad_b, float *const *grad_gamma, float *const *grad_beta, float *grad_xn, void *stream)

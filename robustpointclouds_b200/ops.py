@@ -556,6 +556,18 @@ def trunk_fwd(desc, xn: torch.Tensor, widths: Sequence[int]):
     return raw, ybuf, ys, stats
 
 
+def trunk_fwd_eval(desc, xn: torch.Tensor, widths: Sequence[int], stats: torch.Tensor) -> torch.Tensor:
+    """Eval-mode forward of the whole trunk (``rpc_trunk_fwd_eval``): ``stats`` = per layer (running_mean, 1 / sqrt(running_var
+    + eps)) concatenated; -> raw [K, C].  No autograd."""
+    dev = _need_cuda(xn, stats)
+    K, C = xn.shape
+    work = torch.empty((2 * K * max(max(widths), C),), dtype=torch.float32, device=dev)
+    raw = torch.empty((K, C), dtype=torch.float32, device=dev)
+    st = _lib.lib().rpc_trunk_fwd_eval(ctypes.byref(desc), _ptr(xn), K, _ptr(stats), _ptr(work), _ptr(raw), _stream(dev))
+    _lib.check(st, "rpc_trunk_fwd_eval")
+    return raw
+
+
 def trunk_bwd(desc, xn: torch.Tensor, widths: Sequence[int], ys, stats: torch.Tensor, raw: torch.Tensor, g_raw: torch.Tensor,
               param_shapes, want_grad_xn: bool = False):
     """Backward of ``trunk_fwd`` (``rpc_trunk_bwd``): -> (grad_w list, grad_b list, grad_gamma list, grad_beta list, grad_xn,

@@ -479,6 +479,17 @@ class VoxelPerturber(nn.Module):
                     params += [l.weight, l.bias, b.weight, b.bias]
                 params += [lin[-1].weight, lin[-1].bias]
                 return _TrunkFn.apply(xn, bns, *params)
+        if (self.fused_trunk and not self.training and not torch.is_grad_enabled() and _trunk_supported(self.model, xn)):
+            # the attack at evaluation time: same kernels, BatchNorm with the running statistics, nothing kept
+            lin = [m for m in self.model if isinstance(m, nn.Linear)]
+            bns = [m for m in self.model if isinstance(m, nn.BatchNorm1d)]
+            if len(bns) == 5 and all(m.affine and m.track_running_stats and not m.training for m in bns):
+                widths = [l.out_features for l in lin[:-1]]
+                desc = ops.trunk_desc(xn.shape[1], widths, [l.weight for l in lin], [l.bias for l in lin],
+                                      [m.weight for m in bns], [m.bias for m in bns], [None] * 5, [None] * 5,
+                                      [m.eps for m in bns], [0.0 if m.momentum is None else m.momentum for m in bns])
+                stats = torch.cat([t for m in bns for t in (m.running_mean, torch.rsqrt(m.running_var + m.eps))])
+                return ops.trunk_fwd_eval(desc, xn.contiguous(), widths, stats)
         return self.model(xn)
 
     @staticmethod

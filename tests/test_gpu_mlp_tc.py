@@ -208,3 +208,26 @@ def test_fused_trunk_matches_module_path(C, hidden, K, strict):
             np.testing.assert_allclose(b.cpu().numpy(), rb.cpu().numpy(), rtol=2e-5, atol=1e-6, err_msg=k)
         else:
             assert int(b) == int(rb), k
+
+
+@pytest.mark.parametrize("C,hidden", [(4, [64, 128, 64]), (5, [16, 32, 64])])
+def test_eval_mode_trunk_no_grad(C, hidden):
+    """eval mode under no_grad (the attack at evaluation time): rpc_trunk_fwd_eval with the running statistics against the
+    nn.Module path of the same weights"""
+    import copy
+    from robustpointclouds_b200 import VoxelPerturber
+    torch.manual_seed(C)
+    vs = [0.05, 0.05, 0.1] if C == 4 else [0.075, 0.075, 0.2]
+    adv = VoxelPerturber(hidden_channels=hidden, voxel_size=vs, nan_guards=False).build(C, DEV).train()
+    g = torch.Generator(DEV).manual_seed(2)
+    x = torch.rand(3001, C, device=DEV, generator=g) * torch.tensor([70.0, 80.0, 4.0, 1.0, 0.5][:C], device=DEV)
+    adv(x)                                                         # one training step moves the running statistics
+    adv.eval()
+    ref = copy.deepcopy(adv)
+    ref.fused_trunk = False
+    with torch.no_grad():
+        y, ld = adv(x)
+        yr, lr = ref(x)
+    assert _rel(y, yr.double()) < TOL
+    for k in ld:
+        assert abs(float(ld[k]) - float(lr[k])) <= 1e-5 * max(abs(float(lr[k])), 1e-3), k
