@@ -263,7 +263,7 @@ class _TrunkFn(torch.autograd.Function):
             torch.clamp_(torch.nan_to_num_(flat, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
             _PRECLAMPED.clear()
             for t in grads:
-                _PRECLAMPED[t.data_ptr()] = t.numel()
+                _PRECLAMPED[t.data_ptr()] = flat
         return (g_xn, None, *grads)
 
 
@@ -285,13 +285,14 @@ def _trunk_supported(model: nn.Sequential, x: torch.Tensor) -> bool:
 # buffer they are views of): the per-parameter hook recognises them and returns without launching anything.  With 22
 # trunk parameters the reference's hook is 44 tiny launches and their Python overhead per step -- a quarter of the KITTI
 # step's wall time (profiles/r02_mlp_in_loop_launches.txt).
-_PRECLAMPED: Dict[int, int] = {}
+_PRECLAMPED: Dict[int, torch.Tensor] = {}                   # data_ptr of a gradient view -> the flat buffer it is a view of
 
 
 def _gradient_hook(grad):
     if grad is None:
         return grad
-    if _PRECLAMPED.pop(grad.data_ptr(), None) == grad.numel():
+    flat = _PRECLAMPED.pop(grad.data_ptr(), None)
+    if flat is not None and grad._base is flat:              # (identity of the buffer, not just an address that may be reused)
         return None                                          # same values the two ops below would produce
     return torch.clamp(torch.nan_to_num(grad, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
 
