@@ -30,7 +30,9 @@ def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
 
 
 def _stream(dev: torch.device) -> int:
-    return torch.cuda.current_stream(dev).cuda_stream
+    # (the raw handle of the current stream; torch.cuda.current_stream(dev).cuda_stream builds a Stream object first and
+    # costs ~7 us a call -- 23 calls per training step)
+    return torch._C._cuda_getCurrentRawStream(dev.index if dev.index is not None else torch.cuda.current_device())
 
 
 def _f32c(t: torch.Tensor) -> torch.Tensor:
@@ -75,8 +77,8 @@ class Workspace:
         self.headroom = headroom
 
     def _key(self, dev: torch.device):
-        return (dev.index if dev.index is not None else torch.cuda.current_device(),
-                torch.cuda.current_stream(dev).cuda_stream)
+        i = dev.index if dev.index is not None else torch.cuda.current_device()
+        return (i, torch._C._cuda_getCurrentRawStream(i))
 
     def get(self, nbytes: int, dev: torch.device) -> torch.Tensor:
         k = self._key(dev)
@@ -434,12 +436,19 @@ def attention_gate_bwd(g_out: torch.Tensor, xn: torch.Tensor, t: torch.Tensor, w
     K, C = xn.shape
     grad_t = torch.empty_like(t)
     grad_xn = torch.empty_like(xn) if want_grad_xn else None
-    gw1, gb1, gw2, gb2 = (torch.empty_like(q) for q in (w1, b1, w2, b2))
+    # the four parameter gradients are views of one buffer (the caller clamps them in one pass)
+    flat = torch.empty((sum(q.numel() for q in (w1, b1, w2, b2)),), dtype=torch.float32, device=dev)
+    views, o = [], 0
+    for q in (w1, b1, w2, b2):
+        views.append(flat[o:o + q.numel()].view(q.shape))
+        o += q.numel()
+    gw1, gb1, gw2, gb2 = views
     scratch = _scratch64(_lib.lib().rpc_attention_scratch_bytes() // 8, dev)
     st = _lib.lib().rpc_attention_gate_bwd(_ptr(g_out), _ptr(xn), _ptr(t), _ptr(w1), _ptr(b1), _ptr(w2), _ptr(b2), K, C,
                                            _ptr(scratch), _ptr(grad_t), _ptr(grad_xn), _ptr(gw1), _ptr(gb1), _ptr(gw2),
                                            _ptr(gb2), _stream(dev))
     _lib.check(st, "rpc_attention_gate_bwd")
+    attention_gate_bwd.flat = flat                                # (the buffer behind the four views, for the one-pass clamp)
     return grad_t, grad_xn, gw1, gb1, gw2, gb2
 
 

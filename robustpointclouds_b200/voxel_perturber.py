@@ -112,6 +112,14 @@ class _AttentionGate(torch.autograd.Function):
         xn, t, w1, b1, w2, b2 = ctx.saved_tensors
         grad_t, grad_xn, gw1, gb1, gw2, gb2 = ops.attention_gate_bwd(g_out.contiguous(), xn, t, w1, b1, w2, b2,
                                                                      want_grad_xn=ctx.needs_input_grad[0])
+        if all(getattr(q, "_backward_hooks", None) for q in (w1, b1, w2, b2)):
+            # the reference's gradient hook on the four of them in one pass (see _TrunkFn.backward)
+            flat = ops.attention_gate_bwd.flat
+            torch.clamp_(torch.nan_to_num_(flat, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
+            if len(_PRECLAMPED) > 256:                       # (entries whose hook never fired)
+                _PRECLAMPED.clear()
+            for q in (gw1, gb1, gw2, gb2):
+                _PRECLAMPED[q.data_ptr()] = flat
         return grad_xn, grad_t, gw1, gb1, gw2, gb2
 
 
@@ -261,7 +269,8 @@ class _TrunkFn(torch.autograd.Function):
         if ctx.hooked:
             # the reference's gradient hook (nan_to_num, clamp +-0.1; voxel_perturber.py:465-475) on all of them at once
             torch.clamp_(torch.nan_to_num_(flat, nan=0.0, posinf=0.0, neginf=0.0), -0.1, 0.1)
-            _PRECLAMPED.clear()
+            if len(_PRECLAMPED) > 256:                       # (entries whose hook never fired)
+                _PRECLAMPED.clear()
             for t in grads:
                 _PRECLAMPED[t.data_ptr()] = flat
         return (g_xn, None, *grads)
