@@ -23,4 +23,4 @@ torch.cuda.synchronize()
 pr = cProfile.Profile(); pr.enable()
 for _ in range(30): step()
 torch.cuda.synchronize(); pr.disable()
-st = pstats.Stats(pr); st.sort_stats("cumulative").print_stats(45)
+st = pstats.Stats(pr); st.sort_stats("tottime").print_stats(28)
